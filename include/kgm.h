@@ -1,0 +1,174 @@
+/* kgm.h -- C ABI of libkgm.so: the B200-native replacement for the body of the reference's
+ * poll function.
+ *
+ * The reference (ma2331550908/k8s-gpu-monitor) has no plugin or FFI surface: it is one
+ * script whose `main()` (gpu.py:90-256) turns subprocess texts into InfluxDB line
+ * protocol and POSTs it.  This library replaces exactly the part of `main()` between
+ * "texts acquired" and "lines POSTed" for a whole batch of polls ("documents") at once.
+ * The Python shim a maintainer would bind it with is shown in INTEGRATION.md.
+ *
+ * Everything here is plain C: opaque context, pointers and sizes, no C++ or torch types.
+ * All functions return KGM_OK (0) or a negative KGM_E_* code; they never throw, abort or
+ * print.  One host thread per context at a time (the reference is single-threaded,
+ * gpu.py:258-265).  There is no CPU implementation behind this ABI: without a CUDA
+ * device kgm_create fails with KGM_E_CUDA.
+ */
+#ifndef KGM_H
+#define KGM_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KGM_ABI_VERSION 1
+
+/* ---- call status ---------------------------------------------------------------- */
+#define KGM_OK          0
+#define KGM_E_INVALID  (-1)  /* bad argument (NULL, inconsistent offsets, unknown node id)  */
+#define KGM_E_CUDA     (-2)  /* CUDA runtime / driver error; kgm_last_cuda_error has detail */
+#define KGM_E_NOMEM    (-3)  /* host or device allocation failed                            */
+#define KGM_E_LIMIT    (-4)  /* input beyond a documented limit (see DESIGN.md "Limits")    */
+#define KGM_E_STATE    (-5)  /* call order: no fleet loaded / no batch resident             */
+
+/* ---- per-document status ------------------------------------------------------------
+ * The reference has no try/except: a malformed input raises and kills the poll, and the
+ * lines POSTed before the raise stay written.  The library reproduces
+ * that per document: it emits exactly the lines the reference would have POSTed and
+ * reports the class of the exception here instead of dying. */
+#define KGM_DOC_OK              0
+#define KGM_DOC_KEY_ERROR       1   /* KeyError            gpu.py:51,53,82,133-143,151,172,204 */
+#define KGM_DOC_VALUE_ERROR     2   /* ValueError          gpu.py:133-134 (int(''))            */
+#define KGM_DOC_ZERO_DIVISION   3   /* ZeroDivisionError   gpu.py:135                          */
+#define KGM_DOC_ATTRIBUTE_ERROR 4   /* AttributeError      gpu.py:186 (Labels: null)           */
+#define KGM_DOC_INDEX_ERROR     5   /* IndexError          gpu.py:199,233                      */
+#define KGM_DOC_CSV_ERROR       6   /* _csv.Error          gpu.py:48 (stray CR in a row)       */
+#define KGM_DOC_JSON_ERROR      7   /* JSONDecodeError     gpu.py:88                           */
+#define KGM_DOC_TYPE_ERROR      8   /* TypeError           gpu.py:88,184                       */
+#define KGM_DOC_OTHER_ERROR     9   /* any other exception class raised host-side             */
+/* Inputs outside the supported dialect: no lines are emitted for the document from the
+ * point of detection on, and the status says why (documented divergences). */
+#define KGM_DOC_UNSUPPORTED_QUOTE   20  /* a CSV cell starts with '"' (quoted-field syntax)   */
+#define KGM_DOC_UNSUPPORTED_BYTE    21  /* byte >= 0x80 in an nvidia-smi text                 */
+#define KGM_DOC_UNSUPPORTED_RANGE   22  /* >19-digit memory value, row > 65535 B, line > 8 KiB */
+
+typedef struct kgm_ctx kgm_ctx;
+
+/* n strings stored back to back: string i is bytes[off[i] .. off[i+1]). */
+typedef struct kgm_strings {
+  const uint8_t  *bytes;
+  const uint32_t *off;        /* n + 1 entries */
+} kgm_strings;
+
+/* ---- fleet state: the docker-side inputs of the join ---------------------------------
+ * Slow-changing dimension data, built by the host shim with the reference's own parsing
+ * of `docker ps/stats/top/inspect` and `nvidia-smi -L` text (gpu.py:86-103,172-199,
+ * 221-233) and kept resident in HBM.  A "node" here is one snapshot of one host's docker
+ * state; documents refer to it by index.  Containers of node i are
+ * [cont_begin[i], cont_begin[i+1]) in `docker stats` row order (gpu.py:172,174).       */
+typedef struct kgm_fleet {
+  uint32_t        n_nodes;
+  kgm_strings     node_name;      /* NODE_NAME as printed by '%s' (gpu.py:131; "None" if unset) */
+  const uint32_t *cont_begin;     /* n_nodes + 1                                                */
+  const uint8_t  *node_err_parse; /* KGM_DOC_* raised while parsing docker ps/stats (gpu.py:92-103), else 0 */
+  const uint8_t  *node_err_join;  /* KGM_DOC_* raised at gpu.py:172 (stats id not in ps), else 0 */
+
+  uint32_t        n_containers;
+  const uint8_t  *gated;          /* labels['mlgpu'] == 'mlgpu'          (gpu.py:185-188)      */
+  const uint8_t  *err_inspect;    /* KGM_DOC_* raised at gpu.py:184-187 for this container, else 0 */
+  const uint8_t  *err_emit;       /* KGM_DOC_* raised at gpu.py:193-199 / 227-233 when its first
+                                     line is about to be formatted, else 0                      */
+  kgm_strings     cid;            /* container id as in docker stats                            */
+  kgm_strings     ns;             /* namespace tag value  ("-" without k8s labels)              */
+  kgm_strings     pod;            /* podname field value  ("-" ...)                             */
+  kgm_strings     user;           /* user_name derived per gpu.py:196-199 ("-" ...)             */
+
+  const uint32_t *pid_begin;      /* n_containers + 1: pid strings of container c               */
+  kgm_strings     pid;            /* lines 2..n-1 of `docker top c -eo pid` (gpu.py:177); each
+                                     at most 15 bytes (KGM_E_LIMIT otherwise)                   */
+  const uint32_t *vis_begin;      /* n_containers + 1: uuids visible inside container c         */
+  kgm_strings     vis;            /* whitespace-split output of gpu.py:221-224                  */
+} kgm_fleet;
+
+/* ---- one batch of documents ------------------------------------------------------------
+ * Document d = one poll of one node: the two nvidia-smi texts of gpu.py:104-116, stored
+ * concatenated.  gpu_off / apps_off have n_docs + 1 entries; each text total < 4 GiB.   */
+typedef struct kgm_batch {
+  uint32_t        n_docs;
+  const uint8_t  *gpu_csv;
+  const uint64_t *gpu_off;
+  const uint8_t  *apps_csv;
+  const uint64_t *apps_off;
+  const uint32_t *doc_node;       /* n_docs: index into the loaded fleet's nodes               */
+  const uint32_t *doc_tick;       /* n_docs or NULL: tick index, used only by kgm_window_*     */
+} kgm_batch;
+
+/* Result of one encode.  `lines` is every emitted line followed by '\n', documents in
+ * batch order, lines of a document in the reference's POST order.  All pointers belong to
+ * the context and stay valid until the next kgm_upload_batch / kgm_encode_* / kgm_destroy
+ * on it.  They are HOST pointers from kgm_encode_batch(..., want_host_copy=1) and DEVICE
+ * pointers otherwise.                                                                     */
+typedef struct kgm_result {
+  const uint8_t  *lines;
+  uint64_t        n_bytes;
+  const uint64_t *line_off;       /* n_lines + 1 byte offsets into `lines`                     */
+  uint64_t        n_lines;
+  const uint64_t *doc_line_off;   /* n_docs + 1: first line of each document                   */
+  const int32_t  *doc_status;     /* n_docs: KGM_DOC_*                                         */
+  uint32_t        n_docs;
+} kgm_result;
+
+/* Device time of the last encode, measured with CUDA events on the context's stream.   */
+typedef struct kgm_timing {
+  float h2d_ms;        /* host->device copies of the batch (0 for a resident batch)          */
+  float tokenize_ms;   /* stage 1 kernel                                                     */
+  float join_ms;       /* stage 2 kernel                                                     */
+  float scan_ms;       /* device-wide exclusive scan of per-document sizes                   */
+  float encode_ms;     /* stage 4 byte-writing kernel                                        */
+  float d2h_ms;        /* device->host copies of the result (0 without host copy)            */
+  float total_ms;      /* first event to last event                                          */
+  uint32_t launches;   /* kernels launched by the library in that region                     */
+} kgm_timing;
+
+int  kgm_abi_version(void);
+const char *kgm_strerror(int status);            /* static string for KGM_E_* / KGM_DOC_*  */
+
+/* Replaces the process set-up of gpu.py:258-260.  `device` is a CUDA ordinal.           */
+int  kgm_create(kgm_ctx **out, int device);
+void kgm_destroy(kgm_ctx *ctx);
+const char *kgm_last_cuda_error(kgm_ctx *ctx);
+
+/* Replaces the docker-side reads of gpu.py:92-103,172,177,184-199,221-233 with a
+ * resident table (see kgm_fleet).  Copies everything; the caller's arrays may be freed. */
+int  kgm_load_fleet(kgm_ctx *ctx, const kgm_fleet *fleet);
+
+/* Replaces gpu.py:104-256 (parse both nvidia-smi texts, node lines, join, pod lines) for
+ * a batch held in HOST memory: copies the batch to the device, runs the pipeline and, if
+ * want_host_copy != 0, copies lines / offsets / statuses back into pinned host buffers.  */
+int  kgm_encode_batch(kgm_ctx *ctx, const kgm_batch *batch, int want_host_copy, kgm_result *out);
+
+/* The same in two steps, for callers that keep a batch resident in HBM and run it more
+ * than once (bench.py's device-timed region).  kgm_encode_resident returns device
+ * pointers.                                                                               */
+int  kgm_upload_batch(kgm_ctx *ctx, const kgm_batch *batch);
+int  kgm_encode_resident(kgm_ctx *ctx, kgm_result *out);
+
+/* Copies the last result of kgm_encode_resident to pinned host memory.                  */
+int  kgm_fetch_result(kgm_ctx *ctx, kgm_result *out_host);
+
+int  kgm_get_timing(kgm_ctx *ctx, kgm_timing *out);
+
+/* Writes `bytes` of device scratch on the context's stream so that the L2 holds none of
+ * the batch afterwards (timing hygiene between benchmark iterations).                    */
+int  kgm_flush_l2(kgm_ctx *ctx, uint64_t bytes);
+
+/* Page-locked host memory for batch texts, so that the host->device copies inside
+ * kgm_encode_batch run at full PCIe rate (plain malloc'ed memory also works, slower).     */
+void *kgm_host_alloc(uint64_t bytes);
+void  kgm_host_free(void *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KGM_H */

@@ -1,0 +1,576 @@
+// C ABI of libkgm.so (include/kgm.h): context, fleet tables, batch plumbing, launches.
+//
+// Host code only; every byte of the poll path itself is produced by the kernels in
+// kgm_kernels.cu.  There is deliberately no CPU implementation behind these entry points.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/kgm.h"
+#include "kgm_device.cuh"
+#include "kgm_skeleton.h"
+
+using namespace kgm;
+
+namespace {
+
+struct DevBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    bytes = (bytes + 255) & ~(size_t)255;
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    cudaError_t e = cudaMalloc(&p, bytes + 256);     // +256: aligned 16-byte over-reads stay inside
+    if (e == cudaSuccess) cap = bytes;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct HostBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFreeHost(p);
+    p = nullptr; cap = 0;
+    bytes = (bytes + 4095) & ~(size_t)4095;
+    cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocDefault);
+    if (e == cudaSuccess) cap = bytes;
+    return e;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+  template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+enum { EV_START = 0, EV_H2D, EV_TOK, EV_JOIN, EV_SCAN, EV_ENC, EV_D2H, EV_COUNT };
+
+}  // namespace
+
+struct kgm_ctx {
+  int device = 0;
+  int sms = 148;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[EV_COUNT] = {};
+  std::string cuda_err;
+
+  // fleet
+  bool fleet_loaded = false;
+  FleetDev fleet{};
+  std::vector<uint64_t> node_idle_cap;     // per node: total visible uuids of gated containers
+  DevBuf f_cont_begin, f_nerr_parse, f_nerr_join, f_gated, f_err_inspect, f_err_emit, f_vis_begin,
+      f_vis_off, f_vis_bytes, f_vis_hash, f_node_piece, f_node_fixed, f_cont_piece, f_cont_fixed,
+      f_skel, f_pid_table;
+
+  // batch
+  bool batch_resident = false;
+  BatchDev batch{};
+  uint64_t gpu_bytes = 0, apps_bytes = 0, idle_cap = 0;
+  DevBuf b_gpu, b_gpu_off, b_apps, b_apps_off, b_node, b_tick;
+
+  // workspace
+  WorkDev work{};
+  DevBuf w_grow, w_prow, w_uniq, w_fstr, w_desc, w_len, w_loff, w_counters, w_doc32, w_status,
+      w_doc_line_off, w_doc_byte_off, w_totals, w_line_off, w_out, w_flush;
+  uint32_t grow_cap = 0, prow_cap = 0, desc_cap = 0;
+  uint64_t out_cap = 0;
+
+  // results
+  bool have_result = false;
+  uint64_t n_lines = 0, n_bytes = 0;
+  HostBuf h_small, h_lines, h_line_off, h_doc_line_off, h_status;
+  kgm_timing timing{};
+  bool timed_h2d = false, timed_d2h = false;
+};
+
+namespace {
+
+int cuda_fail(kgm_ctx *c, cudaError_t e, const char *what) {
+  c->cuda_err = std::string(what) + ": " + cudaGetErrorString(e);
+  cudaGetLastError();
+  return e == cudaErrorMemoryAllocation ? KGM_E_NOMEM : KGM_E_CUDA;
+}
+
+#define CU(call)                                              \
+  do {                                                        \
+    cudaError_t e__ = (call);                                 \
+    if (e__ != cudaSuccess) return cuda_fail(ctx, e__, #call); \
+  } while (0)
+
+template <class T>
+int upload(kgm_ctx *ctx, DevBuf &buf, const T *src, size_t n) {
+  CU(buf.ensure(std::max<size_t>(n, 1) * sizeof(T)));
+  if (n) CU(cudaMemcpyAsync(buf.p, src, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+  return KGM_OK;
+}
+
+uint64_t hash_bytes(const uint8_t *p, uint32_t n) {
+  uint64_t h = hash_init();
+  for (uint32_t i = 0; i < n; ++i) h = hash_step(h, p[i]);
+  return h;
+}
+
+bool offsets_ok(const uint32_t *off, uint32_t n) {
+  if (!off) return false;
+  for (uint32_t i = 0; i < n; ++i)
+    if (off[i + 1] < off[i]) return false;
+  return true;
+}
+
+std::string str_of(const kgm_strings &s, uint32_t i) {
+  return std::string(reinterpret_cast<const char *>(s.bytes) + s.off[i], s.off[i + 1] - s.off[i]);
+}
+
+int ensure_workspace(kgm_ctx *ctx) {
+  const uint32_t n = ctx->batch.n_docs;
+  WorkDev &w = ctx->work;
+  CU(ctx->w_grow.ensure((size_t)ctx->grow_cap * sizeof(GpuRow)));
+  CU(ctx->w_uniq.ensure((size_t)ctx->grow_cap * sizeof(uint32_t)));
+  CU(ctx->w_fstr.ensure((size_t)ctx->grow_cap * FSTR_STRIDE));
+  CU(ctx->w_prow.ensure((size_t)ctx->prow_cap * sizeof(ProcRow)));
+  CU(ctx->w_desc.ensure((size_t)ctx->desc_cap * sizeof(LineDesc)));
+  CU(ctx->w_len.ensure((size_t)ctx->desc_cap * sizeof(uint32_t)));
+  CU(ctx->w_loff.ensure((size_t)ctx->desc_cap * sizeof(uint32_t)));
+  CU(ctx->w_line_off.ensure(((size_t)ctx->desc_cap + 1) * sizeof(uint64_t)));
+  CU(ctx->w_counters.ensure(CTR_COUNT * sizeof(uint32_t)));
+  CU(ctx->w_doc32.ensure((size_t)std::max(n, 1u) * 8 * sizeof(uint32_t)));
+  CU(ctx->w_status.ensure((size_t)std::max(n, 1u) * sizeof(int32_t)));
+  CU(ctx->w_doc_line_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
+  CU(ctx->w_doc_byte_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
+  CU(ctx->w_totals.ensure(2 * sizeof(uint64_t)));
+  CU(ctx->w_out.ensure((size_t)ctx->out_cap + 16));
+  w.grow = ctx->w_grow.as<GpuRow>(); w.grow_cap = ctx->grow_cap;
+  w.prow = ctx->w_prow.as<ProcRow>(); w.prow_cap = ctx->prow_cap;
+  w.uniq = ctx->w_uniq.as<uint32_t>();
+  w.fstr = ctx->w_fstr.as<uint8_t>();
+  w.desc = ctx->w_desc.as<LineDesc>(); w.desc_cap = ctx->desc_cap;
+  w.line_len = ctx->w_len.as<uint32_t>();
+  w.line_loff = ctx->w_loff.as<uint32_t>();
+  w.counters = ctx->w_counters.as<uint32_t>();
+  uint32_t *d32 = ctx->w_doc32.as<uint32_t>();
+  const size_t st = std::max(n, 1u);
+  w.doc_g0 = d32; w.doc_ng = d32 + st; w.doc_p0 = d32 + 2 * st; w.doc_np = d32 + 3 * st;
+  w.doc_perr = d32 + 4 * st; w.doc_desc0 = d32 + 5 * st; w.doc_nlines = d32 + 6 * st;
+  w.doc_nbytes = d32 + 7 * st;
+  w.doc_status = ctx->w_status.as<int32_t>();
+  w.doc_line_off = ctx->w_doc_line_off.as<uint64_t>();
+  w.doc_byte_off = ctx->w_doc_byte_off.as<uint64_t>();
+  w.totals = ctx->w_totals.as<uint64_t>();
+  w.line_off = ctx->w_line_off.as<uint64_t>();
+  w.out = ctx->w_out.as<uint8_t>(); w.out_cap = ctx->out_cap;
+  return KGM_OK;
+}
+
+// Launches the four kernels on the context's stream (events around each).
+int launch_pipeline(kgm_ctx *ctx) {
+  CU(cudaMemsetAsync(ctx->work.counters, 0, CTR_COUNT * sizeof(uint32_t), ctx->stream));
+  CU(cudaEventRecord(ctx->ev[EV_H2D], ctx->stream));
+  launch_tokenize(ctx->batch, ctx->work, ctx->sms, ctx->stream);
+  CU(cudaEventRecord(ctx->ev[EV_TOK], ctx->stream));
+  launch_join(ctx->batch, ctx->fleet, ctx->work, ctx->sms, ctx->stream);
+  CU(cudaEventRecord(ctx->ev[EV_JOIN], ctx->stream));
+  launch_scan(ctx->batch, ctx->work, ctx->stream);
+  CU(cudaEventRecord(ctx->ev[EV_SCAN], ctx->stream));
+  launch_encode(ctx->batch, ctx->fleet, ctx->work, ctx->sms, ctx->stream);
+  CU(cudaEventRecord(ctx->ev[EV_ENC], ctx->stream));
+  CU(cudaGetLastError());
+  return KGM_OK;
+}
+
+// Runs the pipeline, growing the workspace and re-running when a capacity guess was low.
+int run_resident(kgm_ctx *ctx, bool with_h2d_event) {
+  if (!ctx->fleet_loaded || !ctx->batch_resident) return KGM_E_STATE;
+  CU(ctx->h_small.ensure(64));
+  for (int attempt = 0; attempt < 6; ++attempt) {
+    int rc = ensure_workspace(ctx);
+    if (rc) return rc;
+    if (!with_h2d_event || attempt) CU(cudaEventRecord(ctx->ev[EV_START], ctx->stream));
+    rc = launch_pipeline(ctx);
+    if (rc) return rc;
+    uint32_t *hc = ctx->h_small.as<uint32_t>();
+    uint64_t *ht = reinterpret_cast<uint64_t *>(hc + CTR_COUNT);
+    CU(cudaMemcpyAsync(hc, ctx->work.counters, CTR_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(ht, ctx->work.totals, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    const uint32_t ovf = hc[CTR_OVERFLOW];
+    if (!ovf) {
+      ctx->n_lines = ht[0];
+      ctx->n_bytes = ht[1];
+      ctx->have_result = true;
+      return KGM_OK;
+    }
+    if (ovf & OVF_GROW) ctx->grow_cap = std::max(ctx->grow_cap * 2, hc[CTR_GROW] + 64);
+    if (ovf & OVF_PROW) ctx->prow_cap = std::max(ctx->prow_cap * 2, hc[CTR_PROW] + 64);
+    if (ovf & OVF_DESC) ctx->desc_cap = std::max(ctx->desc_cap * 2, hc[CTR_DESC] + 64);
+    if (ovf & OVF_OUT) ctx->out_cap = ht[1] + ht[1] / 8 + 4096;
+  }
+  return KGM_E_LIMIT;
+}
+
+void fill_timing(kgm_ctx *ctx, bool h2d, bool d2h) {
+  kgm_timing &t = ctx->timing;
+  t = kgm_timing{};
+  if (h2d) cudaEventElapsedTime(&t.h2d_ms, ctx->ev[EV_START], ctx->ev[EV_H2D]);
+  cudaEventElapsedTime(&t.tokenize_ms, ctx->ev[EV_H2D], ctx->ev[EV_TOK]);
+  cudaEventElapsedTime(&t.join_ms, ctx->ev[EV_TOK], ctx->ev[EV_JOIN]);
+  cudaEventElapsedTime(&t.scan_ms, ctx->ev[EV_JOIN], ctx->ev[EV_SCAN]);
+  cudaEventElapsedTime(&t.encode_ms, ctx->ev[EV_SCAN], ctx->ev[EV_ENC]);
+  if (d2h) cudaEventElapsedTime(&t.d2h_ms, ctx->ev[EV_ENC], ctx->ev[EV_D2H]);
+  cudaEventElapsedTime(&t.total_ms, ctx->ev[EV_START], ctx->ev[d2h ? EV_D2H : EV_ENC]);
+  t.launches = 4;
+  cudaGetLastError();
+}
+
+void fill_result_dev(kgm_ctx *ctx, kgm_result *out) {
+  out->lines = ctx->work.out;
+  out->n_bytes = ctx->n_bytes;
+  out->line_off = ctx->work.line_off;
+  out->n_lines = ctx->n_lines;
+  out->doc_line_off = ctx->work.doc_line_off;
+  out->doc_status = ctx->work.doc_status;
+  out->n_docs = ctx->batch.n_docs;
+}
+
+int fetch(kgm_ctx *ctx, kgm_result *out) {
+  const uint32_t n = ctx->batch.n_docs;
+  CU(ctx->h_lines.ensure(ctx->n_bytes + 16));
+  CU(ctx->h_line_off.ensure((ctx->n_lines + 1) * sizeof(uint64_t)));
+  CU(ctx->h_doc_line_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
+  CU(ctx->h_status.ensure(std::max<size_t>(n, 1) * sizeof(int32_t)));
+  if (ctx->n_bytes)
+    CU(cudaMemcpyAsync(ctx->h_lines.p, ctx->work.out, ctx->n_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaMemcpyAsync(ctx->h_line_off.p, ctx->work.line_off, (ctx->n_lines + 1) * sizeof(uint64_t),
+                     cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaMemcpyAsync(ctx->h_doc_line_off.p, ctx->work.doc_line_off, ((size_t)n + 1) * sizeof(uint64_t),
+                     cudaMemcpyDeviceToHost, ctx->stream));
+  if (n)
+    CU(cudaMemcpyAsync(ctx->h_status.p, ctx->work.doc_status, (size_t)n * sizeof(int32_t),
+                       cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaEventRecord(ctx->ev[EV_D2H], ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  if (ctx->n_lines == 0) ctx->h_line_off.as<uint64_t>()[0] = 0;
+  out->lines = ctx->h_lines.as<uint8_t>();
+  out->n_bytes = ctx->n_bytes;
+  out->line_off = ctx->h_line_off.as<uint64_t>();
+  out->n_lines = ctx->n_lines;
+  out->doc_line_off = ctx->h_doc_line_off.as<uint64_t>();
+  out->doc_status = ctx->h_status.as<int32_t>();
+  out->n_docs = n;
+  return KGM_OK;
+}
+
+int upload_batch(kgm_ctx *ctx, const kgm_batch *b) {
+  if (!ctx->fleet_loaded) return KGM_E_STATE;
+  if (!b || (b->n_docs && (!b->gpu_off || !b->apps_off || !b->doc_node))) return KGM_E_INVALID;
+  const uint32_t n = b->n_docs;
+  static const uint64_t zero_off[1] = {0};
+  const uint64_t *goff = n ? b->gpu_off : zero_off, *aoff = n ? b->apps_off : zero_off;
+  if (goff[0] != 0 || aoff[0] != 0) return KGM_E_INVALID;
+  uint64_t idle_cap = 0;
+  for (uint32_t d = 0; d < n; ++d) {
+    if (goff[d + 1] < goff[d] || aoff[d + 1] < aoff[d]) return KGM_E_INVALID;
+    if (b->doc_node[d] >= ctx->fleet.n_nodes) return KGM_E_INVALID;
+    idle_cap += ctx->node_idle_cap[b->doc_node[d]];
+  }
+  const uint64_t gb = goff[n], ab = aoff[n];
+  if (gb >= 0xfff00000ull || ab >= 0xfff00000ull) return KGM_E_LIMIT;
+  if ((gb && !b->gpu_csv) || (ab && !b->apps_csv)) return KGM_E_INVALID;
+  ctx->batch_resident = false;
+  ctx->have_result = false;
+  CU(cudaEventRecord(ctx->ev[EV_START], ctx->stream));
+  int rc;
+  if ((rc = upload(ctx, ctx->b_gpu, b->gpu_csv, gb))) return rc;
+  if ((rc = upload(ctx, ctx->b_apps, b->apps_csv, ab))) return rc;
+  if ((rc = upload(ctx, ctx->b_gpu_off, goff, (size_t)n + 1))) return rc;
+  if ((rc = upload(ctx, ctx->b_apps_off, aoff, (size_t)n + 1))) return rc;
+  if ((rc = upload(ctx, ctx->b_node, b->doc_node, n))) return rc;
+  if (b->doc_tick && (rc = upload(ctx, ctx->b_tick, b->doc_tick, n))) return rc;
+  ctx->batch.n_docs = n;
+  ctx->batch.gpu_csv = ctx->b_gpu.as<uint8_t>();
+  ctx->batch.gpu_off = ctx->b_gpu_off.as<uint64_t>();
+  ctx->batch.apps_csv = ctx->b_apps.as<uint8_t>();
+  ctx->batch.apps_off = ctx->b_apps_off.as<uint64_t>();
+  ctx->batch.doc_node = ctx->b_node.as<uint32_t>();
+  ctx->batch.doc_tick = b->doc_tick ? ctx->b_tick.as<uint32_t>() : nullptr;
+  ctx->gpu_bytes = gb; ctx->apps_bytes = ab; ctx->idle_cap = idle_cap;
+  // capacity guesses; a kernel that runs out says so and the pipeline is re-run larger
+  ctx->grow_cap = std::max<uint64_t>(ctx->grow_cap, gb / 48 + n + 64);
+  ctx->prow_cap = std::max<uint64_t>(ctx->prow_cap, ab / 40 + n + 64);
+  ctx->desc_cap = std::max<uint64_t>(ctx->desc_cap, gb / 48 + ab / 40 + idle_cap + n + 64);
+  ctx->out_cap = std::max<uint64_t>(ctx->out_cap, 4 * (gb + ab) + 400 * idle_cap + (1u << 20));
+  ctx->batch_resident = true;
+  return KGM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int kgm_abi_version(void) { return KGM_ABI_VERSION; }
+
+const char *kgm_strerror(int s) {
+  switch (s) {
+    case KGM_OK: return "ok";
+    case KGM_E_INVALID: return "invalid argument";
+    case KGM_E_CUDA: return "CUDA error";
+    case KGM_E_NOMEM: return "out of memory";
+    case KGM_E_LIMIT: return "input beyond a documented limit";
+    case KGM_E_STATE: return "call order: fleet or batch not loaded";
+    case KGM_DOC_KEY_ERROR: return "KeyError";
+    case KGM_DOC_VALUE_ERROR: return "ValueError";
+    case KGM_DOC_ZERO_DIVISION: return "ZeroDivisionError";
+    case KGM_DOC_ATTRIBUTE_ERROR: return "AttributeError";
+    case KGM_DOC_INDEX_ERROR: return "IndexError";
+    case KGM_DOC_CSV_ERROR: return "Error";
+    case KGM_DOC_JSON_ERROR: return "JSONDecodeError";
+    case KGM_DOC_TYPE_ERROR: return "TypeError";
+    case KGM_DOC_OTHER_ERROR: return "Exception";
+    case KGM_DOC_UNSUPPORTED_QUOTE: return "unsupported: quoted CSV cell";
+    case KGM_DOC_UNSUPPORTED_BYTE: return "unsupported: non-ASCII byte";
+    case KGM_DOC_UNSUPPORTED_RANGE: return "unsupported: value or line out of range";
+    default: return "unknown status";
+  }
+}
+
+int kgm_create(kgm_ctx **out, int device) {
+  if (!out) return KGM_E_INVALID;
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) {
+    cudaGetLastError();
+    return KGM_E_CUDA;
+  }
+  kgm_ctx *ctx = new (std::nothrow) kgm_ctx();
+  if (!ctx) return KGM_E_NOMEM;
+  ctx->device = device;
+  cudaError_t e = cudaSetDevice(device);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+  for (int i = 0; i < EV_COUNT && e == cudaSuccess; ++i) e = cudaEventCreate(&ctx->ev[i]);
+  cudaDeviceProp prop;
+  if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
+  if (e != cudaSuccess) { kgm_destroy(ctx); cudaGetLastError(); return KGM_E_CUDA; }
+  ctx->sms = prop.multiProcessorCount;
+  *out = ctx;
+  return KGM_OK;
+}
+
+void kgm_destroy(kgm_ctx *ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  DevBuf *dev[] = {&ctx->f_cont_begin, &ctx->f_nerr_parse, &ctx->f_nerr_join, &ctx->f_gated,
+                   &ctx->f_err_inspect, &ctx->f_err_emit, &ctx->f_vis_begin, &ctx->f_vis_off,
+                   &ctx->f_vis_bytes, &ctx->f_vis_hash, &ctx->f_node_piece, &ctx->f_node_fixed,
+                   &ctx->f_cont_piece, &ctx->f_cont_fixed, &ctx->f_skel, &ctx->f_pid_table,
+                   &ctx->b_gpu, &ctx->b_gpu_off, &ctx->b_apps, &ctx->b_apps_off, &ctx->b_node,
+                   &ctx->b_tick, &ctx->w_grow, &ctx->w_prow, &ctx->w_uniq, &ctx->w_fstr,
+                   &ctx->w_desc, &ctx->w_len, &ctx->w_loff, &ctx->w_counters, &ctx->w_doc32,
+                   &ctx->w_status, &ctx->w_doc_line_off, &ctx->w_doc_byte_off, &ctx->w_totals,
+                   &ctx->w_line_off, &ctx->w_out, &ctx->w_flush};
+  for (DevBuf *b : dev) b->release();
+  HostBuf *host[] = {&ctx->h_small, &ctx->h_lines, &ctx->h_line_off, &ctx->h_doc_line_off, &ctx->h_status};
+  for (HostBuf *b : host) b->release();
+  for (int i = 0; i < EV_COUNT; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  cudaGetLastError();
+  delete ctx;
+}
+
+const char *kgm_last_cuda_error(kgm_ctx *ctx) { return ctx ? ctx->cuda_err.c_str() : ""; }
+
+int kgm_load_fleet(kgm_ctx *ctx, const kgm_fleet *fl) {
+  if (!ctx || !fl) return KGM_E_INVALID;
+  CU(cudaSetDevice(ctx->device));
+  const uint32_t nn = fl->n_nodes, nc = fl->n_containers;
+  if (!offsets_ok(fl->node_name.off, nn) || !fl->cont_begin || !fl->node_err_parse || !fl->node_err_join)
+    return KGM_E_INVALID;
+  if (fl->cont_begin[0] != 0 || fl->cont_begin[nn] != nc) return KGM_E_INVALID;
+  for (uint32_t i = 0; i < nn; ++i)
+    if (fl->cont_begin[i + 1] < fl->cont_begin[i]) return KGM_E_INVALID;
+  if (nc && (!fl->gated || !fl->err_inspect || !fl->err_emit)) return KGM_E_INVALID;
+  if (!offsets_ok(fl->cid.off, nc) || !offsets_ok(fl->ns.off, nc) || !offsets_ok(fl->pod.off, nc) ||
+      !offsets_ok(fl->user.off, nc) || !fl->pid_begin || !fl->vis_begin)
+    return KGM_E_INVALID;
+  for (uint32_t c = 0; c < nc; ++c)
+    if (fl->pid_begin[c + 1] < fl->pid_begin[c] || fl->vis_begin[c + 1] < fl->vis_begin[c]) return KGM_E_INVALID;
+  if (fl->pid_begin[0] != 0 || fl->vis_begin[0] != 0) return KGM_E_INVALID;
+  const uint32_t npid = fl->pid_begin[nc], nvis = fl->vis_begin[nc];
+  if (!offsets_ok(fl->pid.off, npid) || !offsets_ok(fl->vis.off, nvis)) return KGM_E_INVALID;
+  if (nc >= (1u << 30)) return KGM_E_LIMIT;
+
+  // ---- constant chunks of the two line templates (gpu.py:136-143, 206-216) ----
+  SkelPool pool;
+  std::vector<Piece> node_piece((size_t)nn * NODE_PIECES), cont_piece((size_t)nc * POD_PIECES);
+  std::vector<uint32_t> node_fixed(nn), cont_fixed(nc);
+  ctx->node_idle_cap.assign(nn, 0);
+  uint32_t max_nc = 1;
+  for (uint32_t n = 0; n < nn; ++n) {
+    const std::string host = str_of(fl->node_name, n);
+    node_fixed[n] = pool.node_pieces(host, &node_piece[(size_t)n * NODE_PIECES]);
+    const uint32_t cb = fl->cont_begin[n], ce = fl->cont_begin[n + 1];
+    max_nc = std::max(max_nc, ce - cb);
+    for (uint32_t c = cb; c < ce; ++c) {
+      const std::string cid = str_of(fl->cid, c), ns = str_of(fl->ns, c), pod = str_of(fl->pod, c),
+                        user = str_of(fl->user, c);
+      cont_fixed[c] = pool.pod_pieces(host, ns, cid, user, pod, &cont_piece[(size_t)c * POD_PIECES]);
+      if (fl->gated[c]) ctx->node_idle_cap[n] += fl->vis_begin[c + 1] - fl->vis_begin[c];
+    }
+    if (pool.bytes.size() >= 0xf0000000ull) return KGM_E_LIMIT;
+  }
+  if (max_nc > 4096) return KGM_E_LIMIT;
+  while (pool.bytes.size() & 15) pool.bytes.push_back(0);
+
+  // ---- pid -> container table (gpu.py:177-178: `proc in pids`, exact string match) ----
+  uint32_t tsize = 16;
+  while (tsize < 2ull * npid + 1) tsize <<= 1;
+  std::vector<PidSlot> table(tsize);
+  for (PidSlot &s : table) { s.lo = s.hi = 0; s.node = NONE32; s.crank = 0; s.pad[0] = s.pad[1] = 0; }
+  for (uint32_t n = 0; n < nn; ++n) {
+    for (uint32_t c = fl->cont_begin[n]; c < fl->cont_begin[n + 1]; ++c) {
+      for (uint32_t k = fl->pid_begin[c]; k < fl->pid_begin[c + 1]; ++k) {
+        const uint32_t len = fl->pid.off[k + 1] - fl->pid.off[k];
+        if (len > 15) return KGM_E_LIMIT;
+        const uint8_t *s = fl->pid.bytes + fl->pid.off[k];
+        uint64_t lo = 0, hi = (uint64_t)len << 56;
+        for (uint32_t i = 0; i < len; ++i) {
+          if (i < 8) lo |= (uint64_t)s[i] << (8 * i);
+          else hi |= (uint64_t)s[i] << (8 * (i - 8));
+        }
+        const uint32_t crank = c - fl->cont_begin[n];
+        uint32_t h = (uint32_t)pid_hash(lo, hi, n) & (tsize - 1);
+        bool dup = false;
+        while (table[h].node != NONE32) {
+          if (table[h].node == n && table[h].lo == lo && table[h].hi == hi && table[h].crank == crank) { dup = true; break; }
+          h = (h + 1) & (tsize - 1);
+        }
+        if (!dup) { table[h].lo = lo; table[h].hi = hi; table[h].node = n; table[h].crank = crank; }
+      }
+    }
+  }
+  std::vector<uint64_t> vis_hash(std::max(nvis, 1u));
+  for (uint32_t v = 0; v < nvis; ++v)
+    vis_hash[v] = hash_bytes(fl->vis.bytes + fl->vis.off[v], fl->vis.off[v + 1] - fl->vis.off[v]);
+
+  ctx->fleet_loaded = false;
+  ctx->batch_resident = false;
+  ctx->have_result = false;
+  int rc;
+  if ((rc = upload(ctx, ctx->f_cont_begin, fl->cont_begin, (size_t)nn + 1))) return rc;
+  if ((rc = upload(ctx, ctx->f_nerr_parse, fl->node_err_parse, nn))) return rc;
+  if ((rc = upload(ctx, ctx->f_nerr_join, fl->node_err_join, nn))) return rc;
+  if ((rc = upload(ctx, ctx->f_gated, fl->gated, nc))) return rc;
+  if ((rc = upload(ctx, ctx->f_err_inspect, fl->err_inspect, nc))) return rc;
+  if ((rc = upload(ctx, ctx->f_err_emit, fl->err_emit, nc))) return rc;
+  if ((rc = upload(ctx, ctx->f_vis_begin, fl->vis_begin, (size_t)nc + 1))) return rc;
+  if ((rc = upload(ctx, ctx->f_vis_off, fl->vis.off, (size_t)nvis + 1))) return rc;
+  if ((rc = upload(ctx, ctx->f_vis_bytes, fl->vis.bytes, fl->vis.off[nvis]))) return rc;
+  if ((rc = upload(ctx, ctx->f_vis_hash, vis_hash.data(), nvis))) return rc;
+  if ((rc = upload(ctx, ctx->f_node_piece, node_piece.data(), node_piece.size()))) return rc;
+  if ((rc = upload(ctx, ctx->f_node_fixed, node_fixed.data(), nn))) return rc;
+  if ((rc = upload(ctx, ctx->f_cont_piece, cont_piece.data(), cont_piece.size()))) return rc;
+  if ((rc = upload(ctx, ctx->f_cont_fixed, cont_fixed.data(), nc))) return rc;
+  if ((rc = upload(ctx, ctx->f_skel, pool.bytes.data(), pool.bytes.size()))) return rc;
+  if ((rc = upload(ctx, ctx->f_pid_table, table.data(), table.size()))) return rc;
+  CU(cudaStreamSynchronize(ctx->stream));        // the host vectors above go out of scope
+  FleetDev &f = ctx->fleet;
+  f.n_nodes = nn; f.n_containers = nc; f.max_nc = max_nc;
+  f.cont_begin = ctx->f_cont_begin.as<uint32_t>();
+  f.node_err_parse = ctx->f_nerr_parse.as<uint8_t>();
+  f.node_err_join = ctx->f_nerr_join.as<uint8_t>();
+  f.gated = ctx->f_gated.as<uint8_t>();
+  f.err_inspect = ctx->f_err_inspect.as<uint8_t>();
+  f.err_emit = ctx->f_err_emit.as<uint8_t>();
+  f.vis_begin = ctx->f_vis_begin.as<uint32_t>();
+  f.vis_off = ctx->f_vis_off.as<uint32_t>();
+  f.vis_bytes = ctx->f_vis_bytes.as<uint8_t>();
+  f.vis_hash = ctx->f_vis_hash.as<uint64_t>();
+  f.node_piece = ctx->f_node_piece.as<Piece>();
+  f.node_fixed = ctx->f_node_fixed.as<uint32_t>();
+  f.cont_piece = ctx->f_cont_piece.as<Piece>();
+  f.cont_fixed = ctx->f_cont_fixed.as<uint32_t>();
+  f.skel = ctx->f_skel.as<uint8_t>();
+  f.pid_table = ctx->f_pid_table.as<PidSlot>();
+  f.pid_mask = tsize - 1;
+  ctx->fleet_loaded = true;
+  return KGM_OK;
+}
+
+int kgm_upload_batch(kgm_ctx *ctx, const kgm_batch *b) {
+  if (!ctx) return KGM_E_INVALID;
+  CU(cudaSetDevice(ctx->device));
+  int rc = upload_batch(ctx, b);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(ctx->stream));
+  return KGM_OK;
+}
+
+int kgm_encode_resident(kgm_ctx *ctx, kgm_result *out) {
+  if (!ctx || !out) return KGM_E_INVALID;
+  CU(cudaSetDevice(ctx->device));
+  int rc = run_resident(ctx, false);
+  if (rc) return rc;
+  fill_timing(ctx, false, false);
+  fill_result_dev(ctx, out);
+  return KGM_OK;
+}
+
+int kgm_fetch_result(kgm_ctx *ctx, kgm_result *out) {
+  if (!ctx || !out) return KGM_E_INVALID;
+  if (!ctx->have_result) return KGM_E_STATE;
+  CU(cudaSetDevice(ctx->device));
+  return fetch(ctx, out);
+}
+
+int kgm_encode_batch(kgm_ctx *ctx, const kgm_batch *b, int want_host_copy, kgm_result *out) {
+  if (!ctx || !out) return KGM_E_INVALID;
+  CU(cudaSetDevice(ctx->device));
+  int rc = upload_batch(ctx, b);          // records EV_START, copies are asynchronous
+  if (rc) return rc;
+  rc = run_resident(ctx, true);
+  if (rc) return rc;
+  if (want_host_copy) {
+    rc = fetch(ctx, out);
+    if (rc) return rc;
+  } else {
+    fill_result_dev(ctx, out);
+  }
+  fill_timing(ctx, true, want_host_copy != 0);
+  return KGM_OK;
+}
+
+int kgm_get_timing(kgm_ctx *ctx, kgm_timing *out) {
+  if (!ctx || !out) return KGM_E_INVALID;
+  *out = ctx->timing;
+  return KGM_OK;
+}
+
+int kgm_flush_l2(kgm_ctx *ctx, uint64_t bytes) {
+  if (!ctx) return KGM_E_INVALID;
+  CU(cudaSetDevice(ctx->device));
+  bytes = (bytes + 15) & ~15ull;
+  CU(ctx->w_flush.ensure(bytes));
+  launch_flush(ctx->w_flush.as<uint8_t>(), bytes, ctx->sms, ctx->stream);
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(ctx->stream));
+  return KGM_OK;
+}
+
+void *kgm_host_alloc(uint64_t bytes) {
+  void *p = nullptr;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return p;
+}
+
+void kgm_host_free(void *p) {
+  if (p) cudaFreeHost(p);
+}
+
+}  // extern "C"

@@ -1,0 +1,68 @@
+// Device-side parameter blocks shared by the kernels (kgm_kernels.cu) and the C ABI
+// implementation (kgm_api.cu).
+#pragma once
+#include "kgm_common.cuh"
+
+namespace kgm {
+
+struct BatchDev {
+  uint32_t n_docs;
+  const uint8_t *gpu_csv;        // 16-byte aligned, padded
+  const uint64_t *gpu_off;       // n_docs + 1
+  const uint8_t *apps_csv;
+  const uint64_t *apps_off;
+  const uint32_t *doc_node;
+  const uint32_t *doc_tick;      // may be null
+};
+
+// Fleet tables resident in HBM (built by kgm_load_fleet).
+struct FleetDev {
+  uint32_t n_nodes, n_containers, max_nc;
+  const uint32_t *cont_begin;    // n_nodes + 1
+  const uint8_t *node_err_parse, *node_err_join;
+  const uint8_t *gated, *err_inspect, *err_emit;
+  const uint32_t *vis_begin;     // n_containers + 1
+  const uint32_t *vis_off;       // n_vis + 1 into vis_bytes
+  const uint8_t *vis_bytes;
+  const uint64_t *vis_hash;      // same hash as GpuRow::key_hash
+  const Piece *node_piece;       // NODE_PIECES per node
+  const uint32_t *node_fixed;    // sum of the node's piece lengths
+  const Piece *cont_piece;       // POD_PIECES per container
+  const uint32_t *cont_fixed;
+  const uint8_t *skel;           // skeleton pool, pieces 16-byte aligned
+  const PidSlot *pid_table;
+  uint32_t pid_mask;             // table size - 1 (power of two)
+};
+
+enum : int { CTR_GROW = 0, CTR_PROW = 1, CTR_DESC = 2, CTR_OVERFLOW = 3, CTR_COUNT = 8 };
+enum : uint32_t { OVF_GROW = 1, OVF_PROW = 2, OVF_DESC = 4, OVF_OUT = 8 };
+
+// Per-batch workspace ("scratch"): token tables, join state, line plan.
+struct WorkDev {
+  GpuRow *grow;   uint32_t grow_cap;
+  ProcRow *prow;  uint32_t prow_cap;
+  uint32_t *uniq;                // [grow_cap] k-th unique gpu of a doc -> local row index
+  uint8_t *fstr;                 // [grow_cap * FSTR_STRIDE] repr(mem_util) per values row
+  LineDesc *desc; uint32_t desc_cap;
+  uint32_t *line_len;            // [desc_cap]
+  uint32_t *line_loff;           // [desc_cap] byte offset of the line inside its document
+  uint32_t *counters;            // [CTR_COUNT]
+  uint32_t *doc_g0, *doc_ng, *doc_p0, *doc_np, *doc_perr;   // stage 1 -> stage 2
+  uint32_t *doc_desc0, *doc_nlines, *doc_nbytes;            // stage 2 -> scan / stage 4
+  int32_t *doc_status;
+  uint64_t *doc_line_off;        // n_docs + 1 (result)
+  uint64_t *doc_byte_off;        // n_docs + 1
+  uint64_t *totals;              // [0] lines, [1] bytes
+  uint64_t *line_off;            // [desc_cap + 1] (result)
+  uint8_t *out;                  // encoded bytes (result)
+  uint64_t out_cap;
+};
+
+void launch_tokenize(const BatchDev &b, const WorkDev &w, int sms, cudaStream_t s);
+void launch_join(const BatchDev &b, const FleetDev &f, const WorkDev &w, int sms, cudaStream_t s);
+void launch_scan(const BatchDev &b, const WorkDev &w, cudaStream_t s);
+void launch_encode(const BatchDev &b, const FleetDev &f, const WorkDev &w, int sms, cudaStream_t s);
+void launch_flush(uint8_t *buf, uint64_t bytes, int sms, cudaStream_t s);
+int encode_smem_bytes();
+
+}  // namespace kgm

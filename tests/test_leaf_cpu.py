@@ -1,0 +1,188 @@
+"""CPU: the kernels' per-thread leaf functions (host build of the same headers) against
+Python's csv / re / repr and against the oracle's line templates."""
+import csv
+import io
+import random
+import re
+
+import numpy as np
+import pytest
+
+import golden_io
+import hostcheck as hc
+from oracle import poll_oracle
+
+GOLD = golden_io.load()
+
+
+def test_float_repr_matches_python_repr():
+    rng = np.random.default_rng(5)
+    bits = rng.integers(1, 0x7FF0000000000000, size=60000, dtype=np.uint64).view(np.float64)
+    u = rng.integers(0, 200000, size=60000)
+    t = rng.integers(1, 200000, size=60000)
+    special = [1.0, 10.0, 1e15, 1e16, 1e17, 1e22, 1e23, 5e-324, 2.2250738585072014e-308,
+               1.7976931348623157e308, 1e-4, 1e-5, 1e-3, 9007199254740993.0, 0.1 + 0.2, 2.0 ** 63,
+               2.0 ** 64, 123456789012345680.0] + [float(i) for i in range(300)] + \
+              [10.0 ** k for k in range(-25, 25)] + [2.0 ** k for k in range(-70, 70)]
+    for xs in (bits, u * 100.0 / t, np.asarray(special)):
+        got = hc.float_repr_many(xs)
+        want = [repr(float(x)) for x in xs]
+        assert got == want
+
+
+def test_mem_util_is_pythons_arithmetic():
+    rng = random.Random(3)
+    pairs = [(1, 183359), (183359, 183359), (1, 3), (7, 9), (61120, 81920), (1, 1000001),
+             (0, 9), (2 ** 63 + 12345, 7), (9007199254740993, 1), (18446744073709551615, 3)]
+    pairs += [(rng.randrange(0, 2 ** 64), rng.randrange(1, 2 ** 64)) for _ in range(2000)]
+    pairs += [(rng.randrange(0, 200000), rng.randrange(1, 200000)) for _ in range(5000)]
+    for used, total in pairs:
+        assert hc.mem_util_repr(used, total) == repr(used * 100.0 / total), (used, total)
+
+
+def _py_cells(row: str):
+    rows = list(csv.reader(io.StringIO(row)))
+    return rows[0] if rows else []
+
+
+ROW_POOL = []
+for g in GOLD:
+    for text in (g["gpu_csv"], g["apps_csv"]):
+        ROW_POOL.extend(r for r in text.split("\n")[1:] if "\r" not in r and '"' not in r)
+
+
+def _mutate(rng, row):
+    for _ in range(rng.randrange(3)):
+        if not row:
+            break
+        i = rng.randrange(len(row))
+        k = rng.randrange(5)
+        if k == 0:
+            row = row[:i] + row[i + 1:]
+        elif k == 1:
+            row = row[:i] + rng.choice(", 7x\t[") + row[i:]
+        elif k == 2:
+            row = row[:i] + row[i + rng.randrange(1, 12):]
+        elif k == 3:
+            row = row[:i] + rng.choice("0123456789") * rng.randrange(1, 25) + row[i:]
+        else:
+            row = " " * rng.randrange(3) + row
+    return row
+
+
+def test_gpu_row_scanner_matches_csv_and_re():
+    rng = random.Random(11)
+    rows = [r for r in ROW_POOL if r.startswith(("GPU", "\t"))][:200]
+    rows += [_mutate(rng, rng.choice(rows)) for _ in range(3000)] + ["", " ", ",", ",,,,,,,", "a" * 300]
+    for row in rows:
+        cells = _py_cells(row)
+        got = hc.scan_gpu_row(row.encode())
+        assert got["ncells"] == min(len(cells), 255), row
+        assert got["parse_error"] == (1 if not cells else 0)
+        lo = 0
+        for i, cell in enumerate(cells[:6]):
+            assert row[lo:got["cell_end"][i]] == cell
+            lo = got["cell_end"][i] + 1
+        if cells:
+            key = cells[0].lstrip()
+            assert row[got["key_lo"]:got["cell_end"][0]] == key
+            assert got["key_hash"] == hc.hash_bytes(key.encode())
+        for slot, col in enumerate((1, 3, 4, 5)):
+            if col < len(cells):
+                digits = re.sub(r"\D", "", cells[col])
+                assert got["nd"][slot] == min(len(digits), 255)
+                if col in (3, 4) and 0 < len(digits) <= 19:
+                    assert got["mem_total" if col == 3 else "mem_used"] == int(digits)
+
+
+def test_proc_row_scanner_matches_csv_and_re():
+    rng = random.Random(12)
+    rows = [r for r in ROW_POOL if not r.startswith(("GPU", "\t"))][:300]
+    rows += [_mutate(rng, rng.choice(rows)) for _ in range(3000)] + ["", "1", "1,2", "1,2,3", ",,,"]
+    for row in rows:
+        cells = _py_cells(row)
+        got = hc.scan_proc_row(row.encode())
+        assert got["ncells"] == min(len(cells), 255), row
+        assert got["parse_error"] == (1 if len(cells) < 3 else 0)
+        if len(cells) >= 1:
+            pid = cells[0].encode()
+            assert got["pid_len"] == min(len(pid), 255)
+            if len(pid) <= 15:
+                packed = got["pid_lo"].to_bytes(8, "little") + got["pid_hi"].to_bytes(8, "little")
+                assert packed[:len(pid)] == pid and packed[15] == len(pid)
+                assert packed[len(pid):15] == b"\0" * (15 - len(pid))
+            else:
+                assert got["flags"] & 16
+        if len(cells) >= 2:
+            assert got["name_len"] == len(cells[1].replace(" ", ""))
+        if len(cells) >= 3:
+            key = cells[2].lstrip()
+            lo = got["cell_end"][1] + 1
+            assert row[got["key_lo"]:got["cell_end"][2]] == key
+            assert row[lo:got["cell_end"][2]] == cells[2]
+            assert got["uuid_hash"] == hc.hash_bytes(key.encode())
+        if len(cells) >= 4:
+            assert got["nd_mem"] == min(len(re.sub(r"\D", "", cells[3])), 255)
+
+
+def test_row_flags():
+    assert hc.scan_gpu_row(b"GPU-a, 1 %\r")["flags"] == 0                 # line-terminator CR
+    assert hc.scan_gpu_row(b"GPU-a, 1 %\r\r")["ncells"] == 2
+    assert hc.scan_gpu_row(b"\r")["ncells"] == 0                          # blank "\r\n" line
+    assert hc.scan_gpu_row(b"GPU-a, 1\r %")["parse_error"] == 6           # csv.Error
+    assert hc.scan_gpu_row(b'"GPU-a", 1 %')["parse_error"] == 20
+    assert hc.scan_gpu_row(b'GPU-a,"1 %"')["parse_error"] == 20
+    assert hc.scan_gpu_row(b'GPU-a, "1 %"')["parse_error"] == 0           # quote not at cell start
+    assert hc.scan_gpu_row("GPU-é, 1 %".encode())["parse_error"] == 21
+    assert hc.scan_gpu_row(b"g,1,2," + b"9" * 20 + b",5,6")["node_error"] == 22
+    assert hc.scan_gpu_row(b"g,1,2,0,5,6")["node_error"] == 3
+    assert hc.scan_gpu_row(b"g,1,2,x,5,6")["node_error"] == 2
+    assert hc.scan_gpu_row(b"g,1,2,3,5")["node_error"] == 1
+
+
+def _gold_rows(g):
+    return g["gpu_csv"].split("\n")[1:], g["apps_csv"].split("\n")[1:]
+
+
+def test_node_lines_match_the_oracle_template():
+    n = 0
+    for g in GOLD:
+        if g["err"] or "\r" in g["gpu_csv"]:
+            continue
+        rows = [r for r in _gold_rows(g)[0] if r]
+        for sid, row in enumerate(rows):
+            cells = _py_cells(row)
+            if len(cells) < 6:
+                continue
+            rec = dict(zip(["gpu_uuid", "used_gpu", "utilization.memory", "memory.total",
+                            "memory.used", "memory.free"], cells))
+            try:
+                want = poll_oracle.node_line(g["node_name"], str(sid), rec)
+            except Exception:
+                continue
+            got, planned, _ = hc.node_line(str(g["node_name"]), row.encode(), sid)
+            assert got == (want + "\n").encode()
+            assert planned == len(got)
+            n += 1
+    assert n > 300
+
+
+def test_pod_lines_match_the_oracle_template():
+    rng = random.Random(2)
+    grow = "GPU-aaaa, 4.9 %, 28 %, 16160 MiB, 15524 MiB, 636 MiB"
+    prows = ["34443, /opt/conda/envs/py2/bin/python, GPU-aaaa, 15524 MiB", "1, a b  c, GPU-aaaa, [N/A]",
+             " 7 ,x, GPU-aaaa,1,5", "123456789012345, n, u, 00 7MiB"]
+    for prow in prows:
+        for sid in (0, 7, 10, 123):
+            host, ns, cid, user, pod = "node-%d" % rng.randrange(99), "ns", "16ee8a182726", "alice-bob", \
+                "turing-gpu-notebook-alice-bob-5d9f-xk2p"
+            c = _py_cells(prow)
+            want = poll_oracle.pod_line(host, ns, str(sid), cid, c[0], re.sub(r"\D", "", " 4.9 %"), user,
+                                        c[1].replace(" ", ""), pod, re.sub(r"\D", "", c[3]))
+            got, planned, _ = hc.busy_line(host, ns, cid, user, pod, prow.encode(), grow.encode(), sid)
+            assert got == (want + "\n").encode()
+            assert planned == len(got)
+    for sid in (None, 0, 12):
+        want = poll_oracle.pod_line("h", "-", sid, "cid", "-", 0, "-", "-", "-", 0)
+        got, planned = hc.idle_line("h", "-", "cid", "-", "-", sid)
+        assert got == (want + "\n").encode() and planned == len(got)
