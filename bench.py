@@ -1,0 +1,368 @@
+#!/usr/bin/env python3
+"""Benchmark of the poll path: samples/s parsed -> line protocol (BASELINE.json `metric`).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl kgm|reference] [--config config2]
+
+A *step* is one pass of the whole hot path (tokenize -> join -> scan -> encode) over one
+batch of synthetic replayed nvidia-smi text.  At N=1 the workload is BASELINE.json
+`configs[1]`: 64 nodes x 8 GPUs x 60 ticks = 3840 documents, 30720 samples, 2048 pods.
+At N>1 (torchrun, one rank per GPU) every rank holds its own 64-node shard ("weak"
+scaling; hosts are the partition unit) and the step additionally all-gathers
+the per-rank byte/line counts and concatenates the encoded buffers over NCCL.
+
+Printed JSON (one line, rank 0):
+  value   whole-job samples/s with the batch already resident in HBM, device time from
+          CUDA events on the library's stream, max over ranks; L2 flushed before each step
+  e2e     the same through kgm_encode_batch with pinned HOST buffers: H2D of the texts and
+          D2H of lines/offsets/statuses inside the timed region (wall clock around the call)
+  roofline  the encode kernel (dominant): algorithmic bytes per launch / its CUDA-event time
+  cpu_baseline  the oracle port of gpu.py timed on this box's host cores (N=1, rank 0)
+
+`--impl reference` times the reference's CPU implementation of the path (the oracle port of
+gpu.py: the reference itself cannot travel to the GPU box) on all host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "k8s-gpu-monitor_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "samples/sec parsed->line protocol"
+FLUSH_BYTES = 512 << 20          # > 126 MB L2
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.rows, self.proc = device, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except Exception:
+                continue
+            for name, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def build_workload(config, rank):
+    from kgm import replay
+    from kgm.fleet import node_entry
+    kw = dict(replay.CONFIGS[config])
+    rp = replay.make_replay(seed=0, node_base=rank * kw["nodes"], **kw)
+    entries = [node_entry(s.name, s.ps_text, s.stats_text, s.top, s.inspect, s.smi_list) for s in rp.nodes]
+    return rp, entries
+
+
+# ---------------------------------------------------------------------------------------
+# CPU legs (the only places bench.py touches oracle/)
+# ---------------------------------------------------------------------------------------
+_RP = None
+
+
+def _oracle_docs(idx):
+    from oracle import poll_oracle
+    n = 0
+    for d in idx:
+        s = _RP.nodes[int(_RP.doc_node[d])]
+        lines, err = poll_oracle.poll(s.name, _RP.gpu_texts[d], _RP.apps_texts[d], s.ps_text, s.stats_text,
+                                      s.top, s.inspect, s.smi_list)
+        n += len(lines)
+    return n
+
+
+def cpu_baseline_single_core(rp, gpu_result, budget_s=12.0):
+    """Oracle port on ONE host core over a bounded prefix of the same workload (only the
+    oracle call is timed); doubles as a parity spot check of the GPU result on those
+    documents."""
+    from oracle import poll_oracle
+    spent = 0.0
+    docs = samples = mismatches = 0
+    for d in range(rp.n_docs):
+        s = rp.nodes[int(rp.doc_node[d])]
+        t0 = time.perf_counter()
+        lines, err = poll_oracle.poll(s.name, rp.gpu_texts[d], rp.apps_texts[d], s.ps_text, s.stats_text,
+                                      s.top, s.inspect, s.smi_list)
+        spent += time.perf_counter() - t0
+        docs += 1
+        samples += rp.gpu_texts[d].count("\n") - 1
+        if gpu_result is not None and (err is not None or gpu_result.lines(d) != lines):
+            mismatches += 1
+        if spent > budget_s:
+            break
+    return {"value": samples / spent if spent else 0.0, "unit": "samples/s", "cores": 1, "kind": "port",
+            "sample": "first %d of %d documents of the same workload (%.1f s), oracle/poll_oracle.py "
+                      "(CPython port of gpu.py main()), 1 process" % (docs, rp.n_docs, spent),
+            "parity_docs_checked": docs if gpu_result is not None else 0,
+            "parity_mismatches": mismatches}
+
+
+def run_reference_arm(args):
+    """`--impl reference`: the reference's CPU implementation of the path on all host cores."""
+    global _RP
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import multiprocessing as mp
+    rp, _ = build_workload(args.config, 0)
+    _RP = rp
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    sample_docs = min(rp.n_docs, max(cores * 16, 240))
+    per_doc_samples = rp.n_samples() / rp.n_docs
+    chunks = [list(range(i, sample_docs, cores)) for i in range(cores)]
+    ctx = mp.get_context("fork")
+    times = []
+    with ctx.Pool(cores) as pool:
+        for step in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            pool.map(_oracle_docs, chunks)
+            dt = time.perf_counter() - t0
+            if step >= args.warmup:
+                times.append(dt)
+    ms = 1e3 * sum(times) / len(times)
+    value = sample_docs * per_doc_samples / (ms / 1e3)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "samples/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic",
+        "config": {"workload": workload_name(args.config), "docs_per_step": sample_docs,
+                   "note": "each step is a bounded sample of the workload"},
+        "cpu_baseline": {"value": value, "unit": "samples/s", "cores": cores, "kind": "port",
+                         "sample": "%d of %d documents per step, oracle/poll_oracle.py (CPython port of "
+                                   "gpu.py main(); the reference script itself is not on this box), "
+                                   "%d processes" % (sample_docs, rp.n_docs, cores)},
+        "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def workload_name(config):
+    return {"config1": "configs[0]: 1 node, 8 GPUs, 32 processes, 1 tick",
+            "config2": "configs[1]: 64-node fleet batch, 512 GPUs, 2048 pods, 60 ticks at 1 Hz "
+                       "(3840 documents, 30720 samples) per GPU",
+            "config3": "configs[2]: 1k-node fleet, 8k GPUs, 40k processes, 600 ticks"}[config]
+
+
+# ---------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------
+def run_kgm_arm(args):
+    import torch
+    import torch.distributed as dist
+    from kgm import monitor, shard
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    device = torch.device("cuda", local_rank)
+
+    rp, entries = build_workload(args.config, rank)
+    mon = monitor.Monitor(local_rank)
+    mon.load_fleet(entries)
+    batch = mon.make_batch(rp.gpu_texts, rp.apps_texts, rp.doc_node, rp.doc_tick, pinned=True)
+    samples_rank = rp.n_samples()
+
+    def sync_all():
+        torch.cuda.synchronize(device)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(device)
+
+    # ---- device-resident region ----
+    mon.upload(batch)
+    res = mon.encode_resident()                      # sizes the workspace
+    n_bytes, n_lines = int(res.n_bytes), int(res.n_lines)
+    keys = ("tokenize_ms", "join_ms", "scan_ms", "encode_ms", "total_ms")
+    acc = {k: [] for k in keys}
+    coll_ms = []
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    concat = None
+
+    def step(timed):
+        nonlocal concat
+        mon.flush_l2(FLUSH_BYTES)                    # outside the timed events
+        if world > 1:
+            dist.barrier()
+        r = mon.encode_resident()                    # CUDA events inside, on the library's stream
+        t = mon.timing()
+        c_ms = 0.0
+        if world > 1:
+            local = shard.tensor_of_device_buffer(r.lines, r.n_bytes, device)
+            ev0.record()
+            counts = shard.gather_counts(int(r.n_bytes), int(r.n_lines), device)
+            concat, _ = shard.concat_encoded(local, counts, out=concat if concat is not None and
+                                             concat.numel() >= int(counts[:, 0].sum()) else None)
+            ev1.record()
+            torch.cuda.synchronize(device)
+            c_ms = ev0.elapsed_time(ev1)
+        if timed:
+            for k in keys:
+                acc[k].append(t[k])
+            coll_ms.append(c_ms)
+
+    for _ in range(args.warmup):
+        step(False)
+    sync_all()
+    wall0 = time.perf_counter()
+    with ClockSampler(local_rank) as clocks:
+        for _ in range(args.steps):
+            step(True)
+        sync_all()
+    wall_ms = 1e3 * (time.perf_counter() - wall0) / args.steps
+    mean = {k: sum(v) / len(v) for k, v in acc.items()}
+    step_ms = mean["total_ms"] + (sum(coll_ms) / len(coll_ms) if coll_ms else 0.0)
+
+    # ---- end to end through the C ABI with host buffers ----
+    e2e_times = []
+    for i in range(args.warmup + args.steps):
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        r = mon.encode_raw(batch, want_host_copy=True)
+        dt = time.perf_counter() - t0
+        if i >= args.warmup:
+            e2e_times.append(dt)
+    e2e_ms = 1e3 * sum(e2e_times) / len(e2e_times)
+    h2d = batch.gpu_bytes + batch.apps_bytes + 2 * 8 * (batch.n_docs + 1) + 2 * 4 * batch.n_docs
+    d2h = n_bytes + 8 * (n_lines + 1) + 8 * (batch.n_docs + 1) + 4 * batch.n_docs + 48
+    host_result = mon.fetch() if rank == 0 and world == 1 else None
+
+    # ---- max over ranks ----
+    if world > 1:
+        t = torch.tensor([step_ms, e2e_ms, mean["encode_ms"]], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        step_ms, e2e_ms, enc_ms = (float(x) for x in t.tolist())
+        tot = torch.tensor([samples_rank], dtype=torch.float64, device=device)
+        dist.all_reduce(tot)
+        samples_total = float(tot.item())
+    else:
+        enc_ms = mean["encode_ms"]
+        samples_total = float(samples_rank)
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        algo_bytes = batch.gpu_bytes + batch.apps_bytes + n_bytes       # per launch, this rank
+        achieved = algo_bytes / (enc_ms * 1e-3) / 1e9
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "encode_traffic.json")
+        if os.path.isfile(tpath):
+            try:
+                traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+            except Exception:
+                traffic = None
+        line = {
+            "metric": METRIC, "value": samples_total / (step_ms * 1e-3), "unit": "samples/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+            "data": "synthetic",
+            "config": {"workload": workload_name(args.config), "docs_per_gpu": batch.n_docs,
+                       "samples_per_gpu": samples_rank, "lines_per_gpu": n_lines,
+                       "input_bytes_per_gpu": batch.gpu_bytes + batch.apps_bytes,
+                       "output_bytes_per_gpu": n_bytes,
+                       "l2": "flushed before every step (%d MiB scratch write, outside the events)"
+                             % (FLUSH_BYTES >> 20),
+                       "parallelism": "hosts sharded over %d rank(s); counts all-gather + concatenation "
+                                      "over NCCL inside the step when N>1" % world},
+            "kernel_ms": {k: round(mean[k], 5) for k in keys},
+            "collective_ms": (sum(coll_ms) / len(coll_ms)) if coll_ms else 0.0,
+            "wall_ms_per_step_incl_flush": wall_ms,
+            "pipeline_frac_of_peak": algo_bytes / (mean["total_ms"] * 1e-3) / 1e9 / peak,
+            "roofline": {"bound": "hbm", "kernel": "k_encode", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                         "algorithmic_bytes_per_launch": algo_bytes, "peak_source": peak_src,
+                         "frac_of_nominal_8TBs": achieved / 8000.0},
+            "e2e": {"value": samples_total / (e2e_ms * 1e-3), "unit": "samples/s",
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms},
+            "gpu_launches": 4 * args.steps,
+            "clocks": clocks.summary(),
+        }
+        if world == 1 and not args.no_cpu:
+            line["cpu_baseline"] = cpu_baseline_single_core(rp, host_result)
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    mon.close()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=int(os.environ.get("WORLD_SIZE", "1")))
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="kgm", choices=["kgm", "reference"])
+    ap.add_argument("--config", default="config2", choices=["config1", "config2", "config3"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_kgm_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
