@@ -168,6 +168,43 @@ int  kgm_flush_l2(kgm_ctx *ctx, uint64_t bytes);
 void *kgm_host_alloc(uint64_t bytes);
 void  kgm_host_free(void *p);
 
+/* Stage-1 tokenizer for callers that may not allocate device memory.  (No counterpart in
+ * the reference; it exists for deployment reasons only.)
+ *
+ * Who needs it: a collector that shares a GPU with a job that has reserved all of its HBM,
+ * or one that runs under a memory manager which owns every allocation -- there a
+ * cudaMalloc either fails or stalls the other tenant while the driver synchronises the
+ * device.  This entry point calls no cudaMalloc/cudaFree and no allocating library routine:
+ * the caller passes every input and output as DEVICE pointers on the current device, and
+ * the kernel's working storage (row cursor, overflow flag, row table) is a fixed array
+ * inside the library, sized for KGM_NOALLOC_MAX_ROWS rows (about 1.3 MB; every GPU that
+ * loads the library holds it until the process exits).
+ *
+ * It tokenizes the --query-gpu text of a batch (gpu.py:104-109 semantics, as
+ * kgm_encode_batch does internally) and writes, for the rows of document d at
+ * [doc_row0[d], doc_row0[d] + doc_nrows[d]) (documents land in no particular order):
+ * util = int(digits(utilization.gpu)), mem_used / mem_total = int(digits(memory.used/total)),
+ * and per document doc_err = KGM_DOC_* of a parse-level failure (0 if none).
+ *
+ *   gpu_csv   16-byte aligned, with at least 16 readable bytes after n_bytes
+ *   gpu_off   n_docs + 1 offsets;  n_bytes = gpu_off[n_docs] < 4 GiB
+ *   max_rows  capacity of util / mem_used / mem_total; at most KGM_NOALLOC_MAX_ROWS,
+ *             larger values are refused with KGM_E_LIMIT before anything runs; KGM_E_LIMIT
+ *             is also returned if the text turns out to hold more rows than max_rows
+ *   stream    a cudaStream_t (NULL = default stream); the call returns after the work
+ *             on it has finished
+ *
+ * The first call on a device looks up the device address of the fixed array
+ * (cudaGetSymbolAddress); make that first call before any stream capture begins.  All
+ * calls on a device share the one array and it keeps the previous call's contents: the
+ * entry point clears what has to start at zero itself, but two calls whose GPU work
+ * overlaps (different streams or threads) race on it -- serialise them.                  */
+#define KGM_NOALLOC_MAX_ROWS 16384
+int  kgm_tokenize_gpu_noalloc(const uint8_t *gpu_csv, const uint64_t *gpu_off, uint32_t n_docs,
+                              uint64_t n_bytes, uint32_t max_rows, uint32_t *doc_row0,
+                              uint32_t *doc_nrows, uint32_t *doc_err, uint32_t *util,
+                              uint64_t *mem_used, uint64_t *mem_total, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -11,6 +11,7 @@
 // memory and streaming them out with aligned 16-byte stores.
 #include <cuda_runtime.h>
 
+#include "../../include/kgm.h"
 #include "kgm_device.cuh"
 
 namespace kgm {
@@ -736,3 +737,93 @@ void launch_flush(uint8_t *buf, uint64_t bytes, int sms, cudaStream_t s) {
 }
 
 }  // namespace kgm
+
+// ======================================================================================
+// Allocation-free tokenizer entry point (kgm_tokenize_gpu_noalloc, include/kgm.h)
+// ======================================================================================
+// Some processes that want the per-GPU samples of a batch are not allowed to take device
+// memory of their own: a monitoring sidecar sharing a GPU whose HBM a training job has
+// reserved to the last byte (cudaMalloc fails there, or stalls the tenant while the driver
+// synchronises the device), or a collector running under a memory manager that owns every
+// allocation.  For them the stage-1 tokenizer is offered once more with nothing to
+// allocate: the caller brings the input text and the output arrays, and the kernel's own
+// working storage -- the row cursor, the overflow flag and the row table it builds between
+// its passes -- lives in the fixed array below, which every GPU that loads this library
+// carries until the process exits.
+namespace kgm {
+namespace {
+
+constexpr uint32_t NOALLOC_MAX_ROWS = KGM_NOALLOC_MAX_ROWS;
+constexpr size_t NOALLOC_HEADER = 256;          // [0] row cursor, [1] overflow flag
+constexpr size_t NOALLOC_BYTES = NOALLOC_HEADER + (size_t)NOALLOC_MAX_ROWS * sizeof(GpuRow);
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static void *g_noalloc_ptr[NOALLOC_MAX_DEVICES];   // device address of the array, per device
+
+__global__ void __launch_bounds__(TOK_THREADS)
+k_tokenize_gpu_noalloc(const uint8_t *text, const uint64_t *off, uint32_t n_docs,
+                       unsigned char *scratch, uint32_t cap, uint32_t *doc_row0,
+                       uint32_t *doc_nrows, uint32_t *doc_err, uint32_t *util,
+                       uint64_t *mem_used, uint64_t *mem_total) {
+  uint32_t *counters = reinterpret_cast<uint32_t *>(scratch);
+  GpuRow *rows = reinterpret_cast<GpuRow *>(scratch + NOALLOC_HEADER);
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  for (uint32_t d = warp; d < n_docs; d += warps) {
+    uint32_t g0, ng, gerr;
+    tokenize_text<GpuRow, GpuRowScan, 1>(text, (uint32_t)off[d], (uint32_t)off[d + 1], rows, cap,
+                                         counters, counters + 1, 1u, &g0, &ng, &gerr);
+    __syncwarp();
+    for (uint32_t r = lane_id(); r < ng; r += 32) {
+      const GpuRow &g = rows[g0 + r];
+      util[g0 + r] = g.util;
+      mem_used[g0 + r] = g.mem_used;
+      mem_total[g0 + r] = g.mem_total;
+    }
+    if (lane_id() == 0) { doc_row0[d] = g0; doc_nrows[d] = ng; doc_err[d] = gerr; }
+  }
+}
+
+}  // namespace
+}  // namespace kgm
+
+extern "C" int kgm_tokenize_gpu_noalloc(const uint8_t *gpu_csv, const uint64_t *gpu_off,
+                                        uint32_t n_docs, uint64_t n_bytes, uint32_t max_rows,
+                                        uint32_t *doc_row0, uint32_t *doc_nrows, uint32_t *doc_err,
+                                        uint32_t *util, uint64_t *mem_used, uint64_t *mem_total,
+                                        void *stream) {
+  using namespace kgm;
+  if (!gpu_off || !doc_row0 || !doc_nrows || !doc_err || !util || !mem_used || !mem_total ||
+      (n_bytes && !gpu_csv) || (reinterpret_cast<uintptr_t>(gpu_csv) & 15))
+    return KGM_E_INVALID;
+  if (max_rows > NOALLOC_MAX_ROWS || n_bytes >= 0xfff00000ull) return KGM_E_LIMIT;   // beyond the fixed array
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= NOALLOC_MAX_DEVICES) return KGM_E_CUDA;
+  if (!g_noalloc_ptr[dev]) {
+    // first call on this device: look the array's device address up.  `g_noalloc_scratch`
+    // as written in host code is only a handle; the kernel needs the address behind it.
+    void *p = nullptr;
+    if (cudaGetSymbolAddress(&p, g_noalloc_scratch) != cudaSuccess || !p) { cudaGetLastError(); return KGM_E_CUDA; }
+    g_noalloc_ptr[dev] = p;
+  }
+  unsigned char *scratch = static_cast<unsigned char *>(g_noalloc_ptr[dev]);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // the cursor and the overflow flag must start at zero; the row table is fully rewritten
+  if (cudaMemsetAsync(scratch, 0, NOALLOC_HEADER, s) != cudaSuccess) { cudaGetLastError(); return KGM_E_CUDA; }
+  if (n_docs) {
+    int blocks = (int)((n_docs + TOK_THREADS / 32 - 1) / (TOK_THREADS / 32));
+    blocks = blocks > 148 * 16 ? 148 * 16 : blocks;
+    k_tokenize_gpu_noalloc<<<blocks, TOK_THREADS, 0, s>>>(gpu_csv, gpu_off, n_docs, scratch, max_rows,
+                                                          doc_row0, doc_nrows, doc_err, util, mem_used,
+                                                          mem_total);
+  }
+  uint32_t head[2] = {0, 0};
+  if (cudaMemcpyAsync(head, scratch, sizeof(head), cudaMemcpyDeviceToHost, s) != cudaSuccess ||
+      cudaStreamSynchronize(s) != cudaSuccess) {
+    cudaGetLastError();
+    return KGM_E_CUDA;
+  }
+  return head[1] ? KGM_E_LIMIT : KGM_OK;        // more rows in the text than max_rows
+}

@@ -98,7 +98,11 @@ SIGNATURES = {
     "kgm_flush_l2": (C.c_int, [C.c_void_p, C.c_uint64]),
     "kgm_host_alloc": (C.c_void_p, [C.c_uint64]),
     "kgm_host_free": (None, [C.c_void_p]),
+    "kgm_tokenize_gpu_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint32,
+                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.c_void_p]),
 }
+NOALLOC_MAX_ROWS = 16384
 
 _lib = None
 
