@@ -1,0 +1,111 @@
+"""CPU: the multi-GPU plumbing (kgm/shard.py) with two gloo ranks.
+
+Shards are whole hosts: every rank encodes its own hosts and the only
+exchange is the all-gather of {bytes, lines} plus the rank-major concatenation of the
+encoded buffers.  Here the per-rank "encoded buffer" comes from the oracle (no GPU in this
+container); what is under test is the partition and the assembly, which are the same code
+the NCCL run uses.
+"""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from fleet_util import oracle_of_replay_doc
+from kgm import replay, shard
+from oracle import poll_oracle
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _shard_bodies(world):
+    """Oracle bodies of a small fleet, split by assign_hosts: (per-rank bytes, per-rank lines)."""
+    rp = replay.make_replay(seed=21, nodes=5, ticks=3, gpus=4, containers=6, procs_per_container=2,
+                            idle_every=3)
+    names = [s.name for s in rp.nodes]
+    weights = [sum(len(rp.gpu_texts[d]) + len(rp.apps_texts[d]) for d in range(rp.n_docs)
+                   if rp.doc_node[d] == n) for n in range(len(names))]
+    owner = shard.assign_hosts(names, weights, world)
+    bodies, lines = [b""] * world, [0] * world
+    for d in range(rp.n_docs):
+        got, err = oracle_of_replay_doc(rp, d)
+        assert err is None
+        r = owner[int(rp.doc_node[d])]
+        bodies[r] += poll_oracle.body_of(got)
+        lines[r] += len(got)
+    return bodies, lines, owner, names, weights
+
+
+def _worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        bodies, lines, owner, names, weights = _shard_bodies(world)
+        # every rank derives the same host -> rank map without talking
+        assert owner == shard.assign_hosts(list(names), list(weights), world)
+        mine = np.frombuffer(bodies[rank] + b"\0" * 7, np.uint8).copy()
+        local = torch.from_numpy(mine)
+        counts = shard.gather_counts(len(bodies[rank]), lines[rank], torch.device("cpu"))
+        assert counts[:, 0].tolist() == [len(b) for b in bodies]
+        assert counts[:, 1].tolist() == lines
+        off = shard.slice_offsets(counts)
+        assert off[:, 0].tolist() == list(np.cumsum([0] + [len(b) for b in bodies]))
+        whole, off2 = shard.concat_encoded(local, counts)
+        assert torch.equal(off, off2)
+        assert bytes(whole.numpy().tobytes()) == b"".join(bodies)
+        # second round into a caller-provided buffer (bench.py reuses it every step)
+        out = torch.zeros(len(b"".join(bodies)) + 64, dtype=torch.uint8)
+        whole2, _ = shard.concat_encoded(local, counts, out=out)
+        assert bytes(whole2.numpy().tobytes()) == b"".join(bodies)
+        q.put((rank, "ok"))
+    except Exception as exc:  # pragma: no cover - reported to the parent
+        q.put((rank, "%s: %s" % (type(exc).__name__, exc)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(180)
+def test_two_ranks_gather_counts_and_concatenate_rank_major():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = dict(q.get(timeout=150) for _ in range(world))
+    for p in procs:
+        p.join(timeout=30)
+    assert results == {0: "ok", 1: "ok"}
+
+
+def test_assign_hosts_is_balanced_and_deterministic():
+    names = ["k8s-node-gpu-%05d" % i for i in range(37)]
+    weights = [1000 + (i * 7919) % 5000 for i in range(37)]
+    weights[3] = 60000                                # one dominant host (config 5 skew)
+    for world in (1, 2, 4, 8):
+        a = shard.assign_hosts(names, weights, world)
+        assert a == shard.assign_hosts(list(names), list(weights), world)
+        assert set(a) <= set(range(world))
+        load = [sum(w for w, r in zip(weights, a) if r == k) for k in range(world)]
+        # largest-first onto the least loaded rank: no rank exceeds the mean by more than the largest host
+        assert max(load) <= sum(weights) / world + max(weights)
+    perm = list(reversed(range(37)))                  # order of presentation does not matter
+    b = shard.assign_hosts([names[i] for i in perm], [weights[i] for i in perm], 4)
+    a = shard.assign_hosts(names, weights, 4)
+    assert [b[perm.index(i)] for i in range(37)] == a
+
+
+def test_shards_cover_every_document_once():
+    bodies, lines, owner, names, _ = _shard_bodies(2)
+    assert len(owner) == len(names) and set(owner) == {0, 1}
+    assert sum(lines) > 0 and all(len(b) > 0 for b in bodies)
