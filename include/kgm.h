@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define KGM_ABI_VERSION 1
+#define KGM_ABI_VERSION 2
 
 /* ---- call status ---------------------------------------------------------------- */
 #define KGM_OK          0
@@ -129,6 +129,9 @@ typedef struct kgm_timing {
   float d2h_ms;        /* device->host copies of the result (0 without host copy)            */
   float total_ms;      /* first event to last event                                          */
   uint32_t launches;   /* kernels launched by the library in that region                     */
+  uint32_t fused;      /* 1: the batch went through the fused single-pass kernel; its time is
+                          reported as encode_ms and tokenize/join/scan are 0                  */
+  uint32_t slow_docs;  /* fused kernel: documents that took the generic per-byte path inside it */
 } kgm_timing;
 
 int  kgm_abi_version(void);
@@ -158,6 +161,18 @@ int  kgm_encode_resident(kgm_ctx *ctx, kgm_result *out);
 int  kgm_fetch_result(kgm_ctx *ctx, kgm_result *out_host);
 
 int  kgm_get_timing(kgm_ctx *ctx, kgm_timing *out);
+
+/* Which kernels run a batch (no counterpart in the reference; results are identical):
+ *   AUTO           one fused single-pass kernel when the batch fits its shared-memory slices,
+ *                  the staged kernels otherwise (default)
+ *   STAGED         always tokenize -> join -> scan -> encode as four kernels
+ *   FUSED_GENERIC  the fused kernel with its fast path switched off: every document takes
+ *                  the generic per-byte path inside it (testing)
+ * The environment variable KGM_PIPELINE=staged|fused-generic sets the initial mode.        */
+#define KGM_PIPELINE_AUTO          0
+#define KGM_PIPELINE_STAGED        1
+#define KGM_PIPELINE_FUSED_GENERIC 2
+int  kgm_set_pipeline(kgm_ctx *ctx, int mode);
 
 /* Writes `bytes` of device scratch on the context's stream so that the L2 holds none of
  * the batch afterwards (timing hygiene between benchmark iterations).                    */

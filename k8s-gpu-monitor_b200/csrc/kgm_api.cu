@@ -4,6 +4,7 @@
 // kgm_kernels.cu.  There is deliberately no CPU implementation behind these entry points.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -83,6 +84,20 @@ struct kgm_ctx {
   uint32_t grow_cap = 0, prow_cap = 0, desc_cap = 0;
   uint64_t out_cap = 0;
 
+  // fused kernel (k_poll)
+  int pipeline = 0;                        // KGM_PIPELINE_*
+  bool fused_ok = false;                   // the current batch fits the fused kernel's shared-memory slices
+  FusedParams fused{};
+  int fused_ctas_per_sm = 2;
+  uint32_t epoch = 0;
+  bool counters_clean = false;             // the counter set of the next fused launch is known to be zero
+  unsigned long long ticket_next = 0;      // value of the ticket counter when the next launch starts
+  DevBuf w_ticket, w_scan;
+  DevBuf f_node_fast, f_tb_off, f_tb_len, f_tb_pool, f_pid16, f_vis_hash2;
+  uint32_t fast_max_nc = 1, fast_max_tb = 0, fast_max_idle = 0, any_fast = 0;
+  uint32_t slow_docs = 0;
+  bool last_fused = false;
+
   // results
   bool have_result = false;
   uint64_t n_lines = 0, n_bytes = 0;
@@ -140,7 +155,23 @@ int ensure_workspace(kgm_ctx *ctx) {
   CU(ctx->w_len.ensure((size_t)ctx->desc_cap * sizeof(uint32_t)));
   CU(ctx->w_loff.ensure((size_t)ctx->desc_cap * sizeof(uint32_t)));
   CU(ctx->w_line_off.ensure(((size_t)ctx->desc_cap + 1) * sizeof(uint64_t)));
-  CU(ctx->w_counters.ensure(CTR_COUNT * sizeof(uint32_t)));
+  {
+    const size_t before = ctx->w_counters.cap;
+    CU(ctx->w_counters.ensure(2 * CTR_COUNT * sizeof(uint32_t)));
+    if (ctx->w_counters.cap != before) {
+      CU(cudaMemsetAsync(ctx->w_counters.p, 0, 2 * CTR_COUNT * sizeof(uint32_t), ctx->stream));
+      ctx->counters_clean = true;
+    }
+    const size_t tb = ctx->w_ticket.cap;
+    CU(ctx->w_ticket.ensure(64));
+    if (ctx->w_ticket.cap != tb) {
+      CU(cudaMemsetAsync(ctx->w_ticket.p, 0, 64, ctx->stream));
+      ctx->ticket_next = 0;
+    }
+    const size_t sb = ctx->w_scan.cap;
+    CU(ctx->w_scan.ensure((size_t)std::max(n, 1u) * 16));
+    if (ctx->w_scan.cap != sb) CU(cudaMemsetAsync(ctx->w_scan.p, 0, ctx->w_scan.cap, ctx->stream));
+  }
   CU(ctx->w_doc32.ensure((size_t)std::max(n, 1u) * 8 * sizeof(uint32_t)));
   CU(ctx->w_status.ensure((size_t)std::max(n, 1u) * sizeof(int32_t)));
   CU(ctx->w_doc_line_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
@@ -154,7 +185,7 @@ int ensure_workspace(kgm_ctx *ctx) {
   w.desc = ctx->w_desc.as<LineDesc>(); w.desc_cap = ctx->desc_cap;
   w.line_len = ctx->w_len.as<uint32_t>();
   w.line_loff = ctx->w_loff.as<uint32_t>();
-  w.counters = ctx->w_counters.as<uint32_t>();
+  w.counters = ctx->w_counters.as<uint32_t>();   // launch_pipeline picks the set
   uint32_t *d32 = ctx->w_doc32.as<uint32_t>();
   const size_t st = std::max(n, 1u);
   w.doc_g0 = d32; w.doc_ng = d32 + st; w.doc_p0 = d32 + 2 * st; w.doc_np = d32 + 3 * st;
@@ -169,8 +200,52 @@ int ensure_workspace(kgm_ctx *ctx) {
   return KGM_OK;
 }
 
-// Launches the four kernels on the context's stream (events around each).
+// The batch goes through the fused kernel unless it was switched off or does not fit.
+bool use_fused(const kgm_ctx *ctx) {
+  return ctx->pipeline != KGM_PIPELINE_STAGED && ctx->fused_ok;
+}
+
+// Launches the pipeline on the context's stream: the fused kernel (one launch), or the four
+// staged kernels (events around each).
 int launch_pipeline(kgm_ctx *ctx) {
+  uint32_t *cbase = ctx->w_counters.as<uint32_t>();
+  if (use_fused(ctx)) {
+    ++ctx->epoch;
+    if ((ctx->epoch & 0xffffu) == 0) {             // tags wrapped: stale state could alias
+      ++ctx->epoch;
+      ctx->counters_clean = false;
+      CU(cudaMemsetAsync(ctx->w_scan.p, 0, ctx->w_scan.cap, ctx->stream));
+    }
+    if (!ctx->counters_clean)
+      CU(cudaMemsetAsync(cbase, 0, 2 * CTR_COUNT * sizeof(uint32_t), ctx->stream));
+    const uint32_t cur = ctx->epoch & 1u;
+    ctx->work.counters = cbase + cur * CTR_COUNT;
+    FusedParams P = ctx->fused;
+    P.epoch = ctx->epoch;
+    P.allow_fast = ctx->pipeline == KGM_PIPELINE_FUSED_GENERIC ? 0u : ctx->any_fast;
+    P.ticket = ctx->w_ticket.as<unsigned long long>();
+    P.ticket_base = ctx->ticket_next;
+    P.scan_state = ctx->w_scan.as<unsigned long long>();
+    P.next_counters = cbase + (1u - cur) * CTR_COUNT;
+    const uint32_t n = ctx->batch.n_docs;
+    const int wpb = 4;
+    int blocks = (int)((n + wpb - 1) / wpb);
+    blocks = std::max(1, std::min(blocks, ctx->sms * ctx->fused_ctas_per_sm));
+    ctx->ticket_next += (unsigned long long)n + (unsigned long long)blocks * wpb;
+    CU(cudaEventRecord(ctx->ev[EV_H2D], ctx->stream));
+    CU(cudaEventRecord(ctx->ev[EV_TOK], ctx->stream));
+    CU(cudaEventRecord(ctx->ev[EV_JOIN], ctx->stream));
+    CU(cudaEventRecord(ctx->ev[EV_SCAN], ctx->stream));
+    launch_poll(ctx->batch, ctx->fleet, ctx->work, P, blocks, ctx->stream);
+    CU(cudaEventRecord(ctx->ev[EV_ENC], ctx->stream));
+    CU(cudaGetLastError());
+    ctx->counters_clean = true;                     // k_poll zeroed the other set
+    ctx->last_fused = true;
+    return KGM_OK;
+  }
+  ctx->work.counters = cbase;
+  ctx->counters_clean = false;
+  ctx->last_fused = false;
   CU(cudaMemsetAsync(ctx->work.counters, 0, CTR_COUNT * sizeof(uint32_t), ctx->stream));
   CU(cudaEventRecord(ctx->ev[EV_H2D], ctx->stream));
   launch_tokenize(ctx->batch, ctx->work, ctx->sms, ctx->stream);
@@ -201,6 +276,7 @@ int run_resident(kgm_ctx *ctx, bool with_h2d_event) {
     CU(cudaMemcpyAsync(ht, ctx->work.totals, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     const uint32_t ovf = hc[CTR_OVERFLOW];
+    ctx->slow_docs = ctx->last_fused ? hc[CTR_SLOW] : 0;
     if (!ovf) {
       ctx->n_lines = ht[0];
       ctx->n_bytes = ht[1];
@@ -225,7 +301,9 @@ void fill_timing(kgm_ctx *ctx, bool h2d, bool d2h) {
   cudaEventElapsedTime(&t.encode_ms, ctx->ev[EV_SCAN], ctx->ev[EV_ENC]);
   if (d2h) cudaEventElapsedTime(&t.d2h_ms, ctx->ev[EV_ENC], ctx->ev[EV_D2H]);
   cudaEventElapsedTime(&t.total_ms, ctx->ev[EV_START], ctx->ev[d2h ? EV_D2H : EV_ENC]);
-  t.launches = 4;
+  t.launches = ctx->last_fused ? 1 : 4;
+  t.fused = ctx->last_fused ? 1 : 0;
+  t.slow_docs = ctx->slow_docs;
   cudaGetLastError();
 }
 
@@ -267,6 +345,56 @@ int fetch(kgm_ctx *ctx, kgm_result *out) {
   return KGM_OK;
 }
 
+// Lays out a warp's shared-memory slice for this batch (FusedParams) and decides whether the
+// fused kernel can run it: two CTAs of four warps per SM if the slices fit, else one.
+// Documents larger than the slice still work (they take the generic path inside the kernel);
+// the sizes are therefore clamped, not rejected.
+void plan_fused(kgm_ctx *ctx, uint32_t n_docs, uint64_t max_g, uint64_t max_a) {
+  auto r16 = [](uint64_t v) { return (uint32_t)((v + 15) & ~15ull); };
+  ctx->fused_ok = false;
+  if (n_docs == 0) return;
+  const uint32_t const_pad = (fast::ConstArea::BYTES + 15u) & ~15u;
+  for (int ctas = 2; ctas >= 1; --ctas) {
+    const uint32_t dyn_max = ctas == 2 ? 115712u : 232448u;
+    const uint32_t warp_bytes = ((dyn_max - const_pad) / 4) & ~15u;
+    // at most ~45% of a slice for the two text windows; larger documents take the generic path
+    const uint32_t text_budget = warp_bytes * 45 / 100;
+    uint64_t g = std::min<uint64_t>(max_g, 8192), a = std::min<uint64_t>(max_a, 32768);
+    if (r16(g + 15) + r16(a + 15) + 96 > text_budget) {
+      a = text_budget > r16(g + 15) + 96 + 1024 ? text_budget - r16(g + 15) - 96 - 16 : 1024;
+    }
+    FusedParams P{};
+    P.cap_g = r16(g + 15) + 48;
+    P.cap_a = r16(a + 15) + 48;
+    P.cap_ng = (uint32_t)std::min<uint64_t>(32, std::max<uint64_t>(8, g / 64 + 2));
+    P.cap_np = (uint32_t)std::min<uint64_t>(2048, std::max<uint64_t>(8, a / 64 + 2));
+    P.cap_c = std::max(1u, ctx->fast_max_nc);
+    P.cap_t = r16(ctx->fast_max_tb) + 32;
+    P.cap_lines = P.cap_ng + P.cap_np + ctx->fast_max_idle;
+    uint32_t o = 0;
+    P.off_tg = o; o += P.cap_g;
+    P.off_ta = o; o += P.cap_a;
+    P.off_gstart = o; o += r16(2ull * (P.cap_ng + 2));
+    P.off_pstart = o; o += r16(2ull * (P.cap_np + 2));
+    P.off_grec = o; o += r16(sizeof(fast::GRec) * (uint64_t)P.cap_ng);
+    P.off_prec = o; o += r16(sizeof(fast::PRec) * (uint64_t)P.cap_np);
+    P.off_cnt = o; o += r16(4ull * P.cap_c);
+    P.off_cstart = o; o += r16(4ull * P.cap_c);
+    P.off_plan = o; o += r16(4ull * P.cap_lines);
+    P.off_loff = o; o += r16(4ull * (P.cap_lines + 1));
+    P.off_tb = o; o += P.cap_t;
+    P.off_stage = o;
+    const uint64_t need_stage = std::max<uint64_t>(MAX_LINE_BYTES + 64, 12ull * ctx->fleet.max_nc + 16);
+    if ((uint64_t)o + need_stage > warp_bytes) continue;
+    P.warp_bytes = warp_bytes;
+    P.stage_bytes = warp_bytes - o;
+    ctx->fused = P;
+    ctx->fused_ctas_per_sm = ctas;
+    ctx->fused_ok = true;
+    return;
+  }
+}
+
 int upload_batch(kgm_ctx *ctx, const kgm_batch *b) {
   if (!ctx->fleet_loaded) return KGM_E_STATE;
   if (!b || (b->n_docs && (!b->gpu_off || !b->apps_off || !b->doc_node))) return KGM_E_INVALID;
@@ -274,12 +402,15 @@ int upload_batch(kgm_ctx *ctx, const kgm_batch *b) {
   static const uint64_t zero_off[1] = {0};
   const uint64_t *goff = n ? b->gpu_off : zero_off, *aoff = n ? b->apps_off : zero_off;
   if (goff[0] != 0 || aoff[0] != 0) return KGM_E_INVALID;
-  uint64_t idle_cap = 0;
+  uint64_t idle_cap = 0, max_g = 0, max_a = 0;
   for (uint32_t d = 0; d < n; ++d) {
     if (goff[d + 1] < goff[d] || aoff[d + 1] < aoff[d]) return KGM_E_INVALID;
     if (b->doc_node[d] >= ctx->fleet.n_nodes) return KGM_E_INVALID;
     idle_cap += ctx->node_idle_cap[b->doc_node[d]];
+    max_g = std::max(max_g, goff[d + 1] - goff[d]);
+    max_a = std::max(max_a, aoff[d + 1] - aoff[d]);
   }
+  plan_fused(ctx, n, max_g, max_a);
   const uint64_t gb = goff[n], ab = aoff[n];
   if (gb >= 0xfff00000ull || ab >= 0xfff00000ull) return KGM_E_LIMIT;
   if ((gb && !b->gpu_csv) || (ab && !b->apps_csv)) return KGM_E_INVALID;
@@ -358,6 +489,10 @@ int kgm_create(kgm_ctx **out, int device) {
   if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
   if (e != cudaSuccess) { kgm_destroy(ctx); cudaGetLastError(); return KGM_E_CUDA; }
   ctx->sms = prop.multiProcessorCount;
+  if (const char *env = getenv("KGM_PIPELINE")) {
+    if (!strcmp(env, "staged")) ctx->pipeline = KGM_PIPELINE_STAGED;
+    else if (!strcmp(env, "fused-generic")) ctx->pipeline = KGM_PIPELINE_FUSED_GENERIC;
+  }
   *out = ctx;
   return KGM_OK;
 }
@@ -374,7 +509,9 @@ void kgm_destroy(kgm_ctx *ctx) {
                    &ctx->b_tick, &ctx->w_grow, &ctx->w_prow, &ctx->w_uniq, &ctx->w_fstr,
                    &ctx->w_desc, &ctx->w_len, &ctx->w_loff, &ctx->w_counters, &ctx->w_doc32,
                    &ctx->w_status, &ctx->w_doc_line_off, &ctx->w_doc_byte_off, &ctx->w_totals,
-                   &ctx->w_line_off, &ctx->w_out, &ctx->w_flush};
+                   &ctx->w_line_off, &ctx->w_out, &ctx->w_flush, &ctx->w_ticket, &ctx->w_scan,
+                   &ctx->f_node_fast, &ctx->f_tb_off, &ctx->f_tb_len, &ctx->f_tb_pool, &ctx->f_pid16,
+                   &ctx->f_vis_hash2};
   for (DevBuf *b : dev) b->release();
   HostBuf *host[] = {&ctx->h_small, &ctx->h_lines, &ctx->h_line_off, &ctx->h_doc_line_off, &ctx->h_status};
   for (HostBuf *b : host) b->release();
@@ -455,9 +592,74 @@ int kgm_load_fleet(kgm_ctx *ctx, const kgm_fleet *fl) {
       }
     }
   }
-  std::vector<uint64_t> vis_hash(std::max(nvis, 1u));
-  for (uint32_t v = 0; v < nvis; ++v)
+  std::vector<uint64_t> vis_hash(std::max(nvis, 1u)), vis_hash2(std::max(nvis, 1u));
+  for (uint32_t v = 0; v < nvis; ++v) {
     vis_hash[v] = hash_bytes(fl->vis.bytes + fl->vis.off[v], fl->vis.off[v + 1] - fl->vis.off[v]);
+    vis_hash2[v] = fast::key_hash_bytes(fl->vis.bytes + fl->vis.off[v], fl->vis.off[v + 1] - fl->vis.off[v]);
+  }
+
+  // ---- tables of the fused kernel's fast path: per node one template block (header,
+  //      container directory, the variable pieces of its line templates) and a compact
+  //      pid table.  A node with any raise point on the docker side, a pid string longer
+  //      than 7 bytes or an oversized block is left to the generic path. ----
+  std::vector<uint8_t> node_fast(std::max(nn, 1u), 0), tb_pool;
+  std::vector<uint32_t> tb_off(std::max(nn, 1u), 0), tb_len(std::max(nn, 1u), 0);
+  uint32_t fast_max_nc = 1, fast_max_tb = 0, fast_max_idle = 0, any_fast = 0;
+  uint64_t n_short_pids = 0;
+  for (uint32_t n = 0; n < nn; ++n) {
+    const uint32_t cb = fl->cont_begin[n], ce = fl->cont_begin[n + 1], ncn = ce - cb;
+    bool ok = !fl->node_err_parse[n] && !fl->node_err_join[n] && ncn <= 512;
+    for (uint32_t c = cb; c < ce && ok; ++c) {
+      if (fl->err_inspect[c] || fl->err_emit[c]) ok = false;
+      for (uint32_t k = fl->pid_begin[c]; k < fl->pid_begin[c + 1] && ok; ++k)
+        if (fl->pid.off[k + 1] - fl->pid.off[k] > 7) ok = false;
+    }
+    if (ctx->node_idle_cap[n] > 2048) ok = false;
+    if (!ok) continue;
+    std::vector<TbContIn> conts(ncn);
+    for (uint32_t c = cb; c < ce; ++c) {
+      TbContIn &in = conts[c - cb];
+      in.gated = fl->gated[c] != 0;
+      in.cid = str_of(fl->cid, c); in.ns = str_of(fl->ns, c); in.pod = str_of(fl->pod, c);
+      in.user = str_of(fl->user, c);
+      in.vis_begin = fl->vis_begin[c];
+      in.nvis = fl->vis_begin[c + 1] - fl->vis_begin[c];
+      in.fixed = cont_fixed[c];
+    }
+    size_t start = 0, total = 0;
+    if (!build_template_block(str_of(fl->node_name, n), node_fixed[n], conts, tb_pool, &start, &total)) continue;
+    if (tb_pool.size() >= 0xf0000000ull) return KGM_E_LIMIT;
+    node_fast[n] = 1; any_fast = 1;
+    tb_off[n] = (uint32_t)start; tb_len[n] = (uint32_t)total;
+    fast_max_nc = std::max(fast_max_nc, ncn);
+    fast_max_tb = std::max<uint32_t>(fast_max_tb, (uint32_t)total);
+    fast_max_idle = std::max<uint32_t>(fast_max_idle, (uint32_t)ctx->node_idle_cap[n]);
+    for (uint32_t c = cb; c < ce; ++c) n_short_pids += fl->pid_begin[c + 1] - fl->pid_begin[c];
+  }
+  for (int i = 0; i < 64; ++i) tb_pool.push_back(0);            // over-read slack
+  uint32_t t16 = 16;
+  while (t16 < 2ull * n_short_pids + 1) t16 <<= 1;
+  std::vector<fast::PidSlot16> table16(t16);
+  for (fast::PidSlot16 &s16 : table16) { s16.key = 0; s16.node = NONE32; s16.crank = 0; }
+  for (uint32_t n = 0; n < nn; ++n) {
+    if (!node_fast[n]) continue;
+    for (uint32_t c = fl->cont_begin[n]; c < fl->cont_begin[n + 1]; ++c) {
+      for (uint32_t k = fl->pid_begin[c]; k < fl->pid_begin[c + 1]; ++k) {
+        const uint32_t len = fl->pid.off[k + 1] - fl->pid.off[k];
+        const uint8_t *ps = fl->pid.bytes + fl->pid.off[k];
+        uint64_t key = (uint64_t)len << 56;
+        for (uint32_t i = 0; i < len; ++i) key |= (uint64_t)ps[i] << (8 * i);
+        const uint32_t crank = c - fl->cont_begin[n];
+        uint32_t h = fast::pid16_hash(key, n) & (t16 - 1);
+        bool dup = false;
+        while (table16[h].node != NONE32) {
+          if (table16[h].node == n && table16[h].key == key && table16[h].crank == crank) { dup = true; break; }
+          h = (h + 1) & (t16 - 1);
+        }
+        if (!dup) { table16[h].key = key; table16[h].node = n; table16[h].crank = crank; }
+      }
+    }
+  }
 
   ctx->fleet_loaded = false;
   ctx->batch_resident = false;
@@ -479,6 +681,12 @@ int kgm_load_fleet(kgm_ctx *ctx, const kgm_fleet *fl) {
   if ((rc = upload(ctx, ctx->f_cont_fixed, cont_fixed.data(), nc))) return rc;
   if ((rc = upload(ctx, ctx->f_skel, pool.bytes.data(), pool.bytes.size()))) return rc;
   if ((rc = upload(ctx, ctx->f_pid_table, table.data(), table.size()))) return rc;
+  if ((rc = upload(ctx, ctx->f_node_fast, node_fast.data(), node_fast.size()))) return rc;
+  if ((rc = upload(ctx, ctx->f_tb_off, tb_off.data(), tb_off.size()))) return rc;
+  if ((rc = upload(ctx, ctx->f_tb_len, tb_len.data(), tb_len.size()))) return rc;
+  if ((rc = upload(ctx, ctx->f_tb_pool, tb_pool.data(), tb_pool.size()))) return rc;
+  if ((rc = upload(ctx, ctx->f_pid16, table16.data(), table16.size()))) return rc;
+  if ((rc = upload(ctx, ctx->f_vis_hash2, vis_hash2.data(), nvis))) return rc;
   CU(cudaStreamSynchronize(ctx->stream));        // the host vectors above go out of scope
   FleetDev &f = ctx->fleet;
   f.n_nodes = nn; f.n_containers = nc; f.max_nc = max_nc;
@@ -499,6 +707,16 @@ int kgm_load_fleet(kgm_ctx *ctx, const kgm_fleet *fl) {
   f.skel = ctx->f_skel.as<uint8_t>();
   f.pid_table = ctx->f_pid_table.as<PidSlot>();
   f.pid_mask = tsize - 1;
+  f.node_fast = ctx->f_node_fast.as<uint8_t>();
+  f.tb_off = ctx->f_tb_off.as<uint32_t>();
+  f.tb_len = ctx->f_tb_len.as<uint32_t>();
+  f.tb_pool = ctx->f_tb_pool.as<uint8_t>();
+  f.pid16 = ctx->f_pid16.as<fast::PidSlot16>();
+  f.pid16_mask = t16 - 1;
+  f.vis_hash2 = ctx->f_vis_hash2.as<uint64_t>();
+  ctx->fast_max_nc = fast_max_nc; ctx->fast_max_tb = fast_max_tb; ctx->fast_max_idle = fast_max_idle;
+  ctx->any_fast = any_fast;
+  ctx->fused_ok = false;
   ctx->fleet_loaded = true;
   return KGM_OK;
 }
@@ -543,6 +761,12 @@ int kgm_encode_batch(kgm_ctx *ctx, const kgm_batch *b, int want_host_copy, kgm_r
     fill_result_dev(ctx, out);
   }
   fill_timing(ctx, true, want_host_copy != 0);
+  return KGM_OK;
+}
+
+int kgm_set_pipeline(kgm_ctx *ctx, int mode) {
+  if (!ctx || mode < KGM_PIPELINE_AUTO || mode > KGM_PIPELINE_FUSED_GENERIC) return KGM_E_INVALID;
+  ctx->pipeline = mode;
   return KGM_OK;
 }
 

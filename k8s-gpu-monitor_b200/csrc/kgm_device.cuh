@@ -2,6 +2,7 @@
 // implementation (kgm_api.cu).
 #pragma once
 #include "kgm_common.cuh"
+#include "kgm_fast.cuh"
 
 namespace kgm {
 
@@ -32,9 +33,17 @@ struct FleetDev {
   const uint8_t *skel;           // skeleton pool, pieces 16-byte aligned
   const PidSlot *pid_table;
   uint32_t pid_mask;             // table size - 1 (power of two)
+  // tables of the fused kernel's fast path (kgm_fast.cuh)
+  const uint8_t *node_fast;      // 1 = no raise point and nothing unusual on the docker side of this node
+  const uint32_t *tb_off;        // per node: its template block in tb_pool (16-byte aligned)
+  const uint32_t *tb_len;
+  const uint8_t *tb_pool;
+  const fast::PidSlot16 *pid16;  // pids of up to 7 bytes
+  uint32_t pid16_mask;
+  const uint64_t *vis_hash2;     // fast::key_hash_bytes of every visible uuid
 };
 
-enum : int { CTR_GROW = 0, CTR_PROW = 1, CTR_DESC = 2, CTR_OVERFLOW = 3, CTR_COUNT = 8 };
+enum : int { CTR_GROW = 0, CTR_PROW = 1, CTR_DESC = 2, CTR_OVERFLOW = 3, CTR_SLOW = 4, CTR_COUNT = 8 };
 enum : uint32_t { OVF_GROW = 1, OVF_PROW = 2, OVF_DESC = 4, OVF_OUT = 8 };
 
 // Per-batch workspace ("scratch"): token tables, join state, line plan.
@@ -57,6 +66,29 @@ struct WorkDev {
   uint8_t *out;                  // encoded bytes (result)
   uint64_t out_cap;
 };
+
+// Launch parameters of k_poll (kgm_fused.cuh): the layout of a warp's shared-memory slice
+// (byte offsets from the slice start, all 16-byte aligned) and the scan / ticket state.
+struct FusedParams {
+  uint32_t cap_g, cap_a;         // text windows (bytes, incl. slack)
+  uint32_t cap_ng, cap_np;       // rows per document
+  uint32_t cap_c;                // containers per node
+  uint32_t cap_t;                // template block
+  uint32_t cap_lines;            // lines per document
+  uint32_t warp_bytes, stage_bytes;
+  uint32_t off_tg, off_ta, off_gstart, off_pstart, off_grec, off_prec, off_cnt, off_cstart, off_plan,
+      off_loff, off_tb, off_stage;
+  uint32_t epoch;                // tags the look-back state of this launch
+  uint32_t allow_fast;           // 0 = every document takes the generic path (testing)
+  unsigned long long ticket_base;
+  unsigned long long *ticket;    // monotonic document ticket counter
+  unsigned long long *scan_state;   // 2 words per document
+  uint32_t *next_counters;       // the counter set of the next launch (zeroed by this one)
+};
+
+void launch_poll(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P, int blocks,
+                 cudaStream_t s);
+int poll_smem_bytes(const FusedParams &P);
 
 void launch_tokenize(const BatchDev &b, const WorkDev &w, int sms, cudaStream_t s);
 void launch_join(const BatchDev &b, const FleetDev &f, const WorkDev &w, int sms, cudaStream_t s);

@@ -1,0 +1,547 @@
+// k_poll: the whole poll path of one batch in ONE persistent kernel (included by
+// kgm_kernels.cu, after the staged kernels whose device functions it reuses).
+//
+// One warp owns one document at a time (documents are handed out in batch order by a
+// ticket counter).  For a regular document everything happens in the warp's slice of
+// shared memory:
+//   text windows  <- coalesced 16-byte loads of the two nvidia-smi texts      (gpu.py:104-116)
+//   rows          <- SWAR line-feed scan, one lane per row: cells, digit runs, keys
+//   join          <- uuid dictionary in registers/shared memory, pid -> container probe of
+//                    the HBM-resident table, container-major placement     (gpu.py:119-128,151,172-178)
+//   lengths       <- per line, warp scan -> offsets inside the document
+//   device-wide exclusive scan over documents by decoupled look-back (lines and bytes)
+//   bytes         <- one lane per line appends its segments with aligned 32-bit stores into
+//                    the stage, the warp streams the stage out with 16-byte stores
+//                                                                          (gpu.py:136-143,206-216,240-250)
+// so the texts are read from HBM once and the line protocol is written once, with no
+// intermediate tables.  A document the fast path cannot take (any raise point of the
+// reference, unusual bytes, duplicate keys, sizes beyond the warp's slice) is re-done from
+// scratch by the generic per-byte code of the staged pipeline inside the same warp, and
+// joins the same look-back chain -- the output is identical either way.
+#pragma once
+
+namespace kgm {
+namespace {
+
+using namespace fast;
+
+constexpr int POLL_THREADS = 128;                   // 4 independent warps per CTA
+constexpr uint32_t CONST_PAD = (ConstArea::BYTES + 15u) & ~15u;
+constexpr uint32_t KIND_NODE = 0, KIND_BUSY = 1, KIND_IDLE = 2;
+constexpr uint32_t IDLE_NONE = 0xfffu;
+
+// ---- look-back state: two tagged 64-bit words per document -----------------------------------
+// tag = epoch (16 bits) | status (2 bits); value in the low 46 bits
+constexpr uint64_t ST_AGG = 1, ST_INC = 2;
+__device__ __forceinline__ uint64_t st_tag(uint32_t epoch, uint64_t status) {
+  return ((uint64_t)(epoch & 0xffffu) << 48) | (status << 46);
+}
+__device__ __forceinline__ void st_relaxed(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void st_release(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long ld_acquire(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__device__ __forceinline__ uint64_t warp_sum64(uint64_t v) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+
+// Publishes the document's (lines, bytes) and returns its exclusive prefix over all
+// earlier documents.  Every lane of the warp calls it.
+__device__ void doc_exclusive_scan(const FusedParams &P, uint32_t d, uint64_t nl, uint64_t nb,
+                                   uint64_t *line0, uint64_t *byte0) {
+  const uint32_t l = lane_id();
+  unsigned long long *st = P.scan_state;
+  const uint64_t agg = st_tag(P.epoch, ST_AGG), inc = st_tag(P.epoch, ST_INC);
+  const uint64_t VAL = (1ull << 46) - 1ull;
+  uint64_t ex_l = 0, ex_b = 0;
+  if (d == 0) {
+    if (l == 0) { st_relaxed(st + 1, inc | nb); st_release(st, inc | nl); }
+    *line0 = 0; *byte0 = 0;
+    return;
+  }
+  if (l == 0) { st_relaxed(st + 2ull * d + 1, agg | nb); st_release(st + 2ull * d, agg | nl); }
+  long long j = (long long)d - 1;
+  for (;;) {
+    const long long idx = j - (long long)l;
+    uint64_t vl = 0, vb = 0;
+    bool is_inc = true;                              // positions before document 0: prefix 0
+    if (idx >= 0) {
+      for (;;) {
+        const uint64_t w0 = ld_acquire(st + 2ull * idx);
+        const uint64_t t0 = w0 & ~VAL;
+        if (t0 == agg || t0 == inc) {
+          const uint64_t w1 = ld_relaxed(st + 2ull * idx + 1);
+          if ((w1 & ~VAL) == t0) { vl = w0 & VAL; vb = w1 & VAL; is_inc = t0 == inc; break; }
+        }
+        __nanosleep(40);
+      }
+    }
+    const uint32_t incs = __ballot_sync(FULL, is_inc);
+    const uint32_t first = incs ? (uint32_t)__ffs(incs) - 1u : 32u;
+    if (l > first) { vl = 0; vb = 0; }
+    ex_l += warp_sum64(vl);
+    ex_b += warp_sum64(vb);
+    if (incs) break;
+    j -= 32;
+  }
+  if (l == 0) {
+    st_relaxed(st + 2ull * d + 1, inc | (ex_b + nb));
+    st_release(st + 2ull * d, inc | (ex_l + nl));
+  }
+  *line0 = ex_l;
+  *byte0 = ex_b;
+}
+
+// ---- fast path -------------------------------------------------------------------------------
+struct WarpSlice {                                   // byte offsets from the CTA's shared memory base
+  uint32_t tg, ta, gstart, pstart, grec, prec, cnt, cstart, plan, loff, tb, stage;
+};
+
+// Coalesced copy of the 16-byte aligned window that covers text[lo, hi) into shared memory.
+__device__ __forceinline__ void load_window(const uint8_t *text, uint64_t lo, uint64_t hi, uint8_t *dst,
+                                            uint32_t *s, uint32_t *e) {
+  const uint64_t w0 = lo & ~15ull;
+  const uint32_t n = (uint32_t)(((hi + 15ull) & ~15ull) - w0);
+  for (uint32_t i = lane_id() * 16u; i < n; i += 512u)
+    *reinterpret_cast<uint4 *>(dst + i) = __ldg(reinterpret_cast<const uint4 *>(text + w0 + i));
+  *s = (uint32_t)(lo - w0);
+  *e = *s + (uint32_t)(hi - lo);
+}
+
+// Line feeds of the window bytes [s, e) -> row_start[0..nrows]; row r = [row_start[r],
+// row_start[r+1]-1).  The first line is the header (gpu.py:67-68).  False if the text has no
+// line feed, does not end with one, or holds more than `cap` rows.
+__device__ bool find_rows(const uint32_t *T, uint32_t s, uint32_t e, uint16_t *row_start, uint32_t cap,
+                          uint32_t *nrows) {
+  const uint32_t l = lane_id();
+  uint32_t running = 0;
+  for (uint32_t it = s & ~15u; it < e; it += 512u) {
+    const uint32_t pos = it + 16u * l;
+    uint32_t m[4] = {0, 0, 0, 0};
+    if (pos < e) {
+      const uint4 v = *reinterpret_cast<const uint4 *>(T + (pos >> 2));
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t z = w[k] ^ 0x0a0a0a0au;                         // exact zero-byte test
+        m[k] = ~(((z & 0x7f7f7f7fu) + 0x7f7f7f7fu) | z) & 0x80808080u;
+      }
+      if (pos < s || pos + 16u > e) {                                  // boundary chunk: drop outside bytes
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint32_t b = pos + 4u * k;
+          uint32_t keep = 0xffffffffu;
+          if (b < s) keep &= ~low_mask(min(s - b, 4u));
+          if (b + 4u > e) keep &= low_mask(e > b ? e - b : 0u);
+          m[k] &= keep;
+        }
+      }
+    }
+    const uint32_t c = __popc(m[0]) + __popc(m[1]) + __popc(m[2]) + __popc(m[3]);
+    const uint32_t incl = warp_incl_scan(c);
+    uint32_t idx = running + incl - c;
+    if (c) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        uint32_t mk = m[k];
+        while (mk) {
+          const uint32_t bit = __ffs(mk) - 1;
+          mk &= mk - 1;
+          if (idx <= cap) row_start[idx] = (uint16_t)(pos + 4u * k + (bit >> 3) + 1u);
+          ++idx;
+        }
+      }
+    }
+    running += __shfl_sync(FULL, incl, 31);
+  }
+  __syncwarp();
+  if (running == 0 || running - 1 > cap) return false;
+  if (row_start[running - 1] != e) return false;                        // last row without terminator
+  *nrows = running - 1;
+  return true;
+}
+
+// Plans a regular document.  On success the warp's slice holds the row records, the line
+// plan and the in-document offsets, and (*nl, *nb) are its line and byte counts.
+__device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, const FusedParams &P,
+                          uint32_t *S, uint8_t *Sb, const WarpSlice &ws, uint32_t *o_ng, uint32_t *o_nl,
+                          uint32_t *o_nb) {
+  const uint32_t l = lane_id();
+  const uint32_t n = b.doc_node[d];
+  if (!f.node_fast[n]) return false;
+  const uint64_t g_lo = b.gpu_off[d], g_hi = b.gpu_off[d + 1], a_lo = b.apps_off[d], a_hi = b.apps_off[d + 1];
+  const uint32_t tb_len = f.tb_len[n];
+  if (((g_hi + 15ull) & ~15ull) - (g_lo & ~15ull) + 32ull > P.cap_g) return false;
+  if (((a_hi + 15ull) & ~15ull) - (a_lo & ~15ull) + 32ull > P.cap_a) return false;
+  if (tb_len + 16u > P.cap_t || g_hi == g_lo || a_hi == a_lo) return false;
+
+  // ---- texts and the node's template block -> shared memory ----
+  uint32_t gs, ge, as, ae;
+  load_window(b.gpu_csv, g_lo, g_hi, Sb + ws.tg, &gs, &ge);
+  load_window(b.apps_csv, a_lo, a_hi, Sb + ws.ta, &as, &ae);
+  {
+    const uint8_t *src = f.tb_pool + f.tb_off[n];
+    for (uint32_t i = l * 16u; i < tb_len; i += 512u)
+      *reinterpret_cast<uint4 *>(Sb + ws.tb + i) = __ldg(reinterpret_cast<const uint4 *>(src + i));
+  }
+  __syncwarp();
+  const uint32_t *TG = S + (ws.tg >> 2), *TA = S + (ws.ta >> 2);
+  const TbHeader &hd = *reinterpret_cast<const TbHeader *>(Sb + ws.tb);
+  const TbCont *tc = reinterpret_cast<const TbCont *>(Sb + ws.tb + sizeof(TbHeader));
+  const uint32_t nc = hd.nc;
+  if (nc > P.cap_c) return false;
+
+  uint16_t *gstart = reinterpret_cast<uint16_t *>(Sb + ws.gstart);
+  uint16_t *pstart = reinterpret_cast<uint16_t *>(Sb + ws.pstart);
+  uint32_t ng, np;
+  if (!find_rows(TG, gs, ge, gstart, P.cap_ng, &ng)) return false;
+  if (!find_rows(TA, as, ae, pstart, P.cap_np, &np)) return false;
+  if (ng > 32u) return false;
+
+  // ---- gpu rows: one lane per row (gpu.py:104-109,119-143) ----
+  GRec *grec = reinterpret_cast<GRec *>(Sb + ws.grec);
+  uint64_t my_hash = 0;
+  uint32_t node_bytes = 0;
+  {
+    bool ok = true;
+    if (l < ng) {
+      GRec g;
+      ok = parse_gpu_row(TG, gstart[l], gstart[l + 1] - 1u, hd.fixed, l, g);
+      if (ok) { grec[l] = g; my_hash = g.hash; node_bytes = g.line_len; }
+    }
+    if (!__all_sync(FULL, ok)) return false;
+    bool dup = false;                               // equal keys: last row wins (gpu.py:54) -> generic path
+    for (uint32_t j = 0; j + 1 < ng; ++j) {
+      const uint64_t hj = __shfl_sync(FULL, my_hash, j);
+      dup |= l < ng && j < l && hj == my_hash;
+    }
+    if (__any_sync(FULL, dup)) return false;
+  }
+  __syncwarp();
+
+  // ---- process rows: parse, uuid -> short id (gpu.py:151), pid -> container (gpu.py:177-178) ----
+  PRec *prec = reinterpret_cast<PRec *>(Sb + ws.prec);
+  uint32_t *cnt = S + (ws.cnt >> 2), *cstart = S + (ws.cstart >> 2);
+  for (uint32_t c = l; c < nc; c += 32) cnt[c] = 0;
+  __syncwarp();
+  for (uint32_t r0 = 0; r0 < np; r0 += 32) {
+    const uint32_t r = r0 + l;
+    const bool valid = r < np;
+    bool ok = true;
+    PRec p;
+    uint32_t emit_c = NONE32;
+    if (valid) {
+      uint32_t kw[KEY_WORDS], klen;
+      uint64_t kh;
+      ok = parse_proc_row(TA, pstart[r], pstart[r + 1] - 1u, p, kw, &klen, &kh);
+      if (ok) {
+        uint32_t sid = NONE32;
+        for (uint32_t j = 0; j < ng && sid == NONE32; ++j) {
+          if (grec[j].hash == kh && grec[j].key.len == klen) {
+            uint32_t gk[KEY_WORDS];
+            load_key(TG, grec[j].key.off, klen, gk);
+            bool eq = true;
+#pragma unroll
+            for (int i = 0; i < KEY_WORDS; ++i) eq &= gk[i] == kw[i];
+            if (eq) sid = j;
+          }
+        }
+        if (sid == NONE32) ok = false;              // KeyError gpu.py:151
+        p.sid = (uint16_t)sid;
+        if (ok && p.pidkey != ~0ull) {
+          uint32_t nm = 0, c_first = NONE32;
+          uint32_t h = pid16_hash(p.pidkey, n) & f.pid16_mask;
+          for (;;) {
+            const uint4 raw = __ldg(reinterpret_cast<const uint4 *>(f.pid16 + h));
+            if (raw.z == NONE32) break;
+            const uint64_t key = ((uint64_t)raw.y << 32) | raw.x;
+            if (raw.z == n && key == p.pidkey) { if (!nm) c_first = raw.w; ++nm; }
+            h = (h + 1) & f.pid16_mask;
+          }
+          if (nm > 1) ok = false;                   // a pid listed by several containers
+          if (nm == 1 && c_first < nc && tc[c_first].gated) emit_c = c_first;
+          p.digest = pair_digest(p.pidkey, p.pid.len, sid);
+        }
+      }
+    }
+    if (!__all_sync(FULL, ok)) return false;
+    // duplicate (pid, gpu) keys keep the first row's place and the last row's values
+    // (gpu.py:54): screened by digest, any hit goes to the generic path
+    const bool screened = valid && p.pidkey != ~0ull;
+    const uint32_t act = __ballot_sync(FULL, screened);
+    bool dup = false;
+    if (screened) {
+      dup = __popc(__match_any_sync(act, p.digest)) > 1;
+      for (uint32_t j = 0; j < r0 && !dup; ++j) dup = prec[j].pidkey != ~0ull && prec[j].digest == p.digest;
+    }
+    if (__any_sync(FULL, dup)) return false;
+    // place inside the container: rank among the earlier rows of the same container
+    const uint32_t emitting = __ballot_sync(FULL, emit_c != NONE32);
+    uint32_t pos = 0;
+    if (emit_c != NONE32) {
+      const uint32_t peers = __match_any_sync(emitting, emit_c);
+      const int leader = __ffs(peers) - 1;
+      uint32_t base = 0;
+      if ((int)l == leader) { base = cnt[emit_c]; cnt[emit_c] = base + __popc(peers); }
+      base = __shfl_sync(peers, base, leader);
+      pos = base + __popc(peers & lanemask_lt());
+    }
+    if (valid) {
+      p.crank = (uint16_t)(emit_c == NONE32 ? 0xffffu : emit_c);
+      p.pos = (uint16_t)pos;
+      prec[r] = p;
+    }
+    __syncwarp();
+  }
+
+  // ---- containers in docker stats order: busy lines, or idle lines (gpu.py:174-253) ----
+  uint32_t total_pod = 0;
+  for (uint32_t c0 = 0; c0 < nc; c0 += 32) {
+    const uint32_t c = c0 + l;
+    uint32_t lines = 0;
+    if (c < nc && tc[c].gated) lines = cnt[c] ? cnt[c] : tc[c].nvis;
+    const uint32_t incl = warp_incl_scan(lines);
+    if (c < nc) cstart[c] = total_pod + incl - lines;
+    total_pod += __shfl_sync(FULL, incl, 31);
+  }
+  const uint32_t nl = ng + total_pod;
+  if (nl > P.cap_lines) return false;
+  __syncwarp();
+  uint32_t *plan = S + (ws.plan >> 2), *loff = S + (ws.loff >> 2);
+  if (l < ng) plan[l] = (KIND_NODE << 30) | l;
+  for (uint32_t r = l; r < np; r += 32) {
+    const PRec &p = prec[r];
+    if (p.crank != 0xffffu) plan[ng + cstart[p.crank] + p.pos] = (KIND_BUSY << 30) | r;
+  }
+  for (uint32_t c = l; c < nc; c += 32) {
+    if (!tc[c].gated || cnt[c]) continue;
+    for (uint32_t v = 0; v < tc[c].nvis; ++v) {      // uuids visible inside an idle container (gpu.py:221-226)
+      const uint32_t gv = tc[c].vis_begin + v;
+      const uint64_t vh = f.vis_hash2[gv];
+      const uint32_t vo = f.vis_off[gv], vlen = f.vis_off[gv + 1] - vo;
+      uint32_t sid = IDLE_NONE;
+      for (uint32_t j = 0; j < ng && sid == IDLE_NONE; ++j) {
+        if (grec[j].hash == vh && grec[j].key.len == vlen) {
+          bool eq = true;
+          for (uint32_t i = 0; i < vlen; ++i) eq &= f.vis_bytes[vo + i] == load1(TG, grec[j].key.off + i);
+          if (eq) sid = j;
+        }
+      }
+      plan[ng + cstart[c] + v] = (KIND_IDLE << 30) | (c << 12) | sid;
+    }
+  }
+  __syncwarp();
+
+  // ---- line lengths -> offsets inside the document ----
+  uint32_t nb = 0;
+  bool too_long = false;
+  for (uint32_t i0 = 0; i0 < nl; i0 += 32) {
+    const uint32_t i = i0 + l;
+    uint32_t len = 0;
+    if (i < nl) {
+      const uint32_t pl = plan[i], kind = pl >> 30;
+      if (kind == KIND_NODE) {
+        len = grec[pl & 0xffffu].line_len;
+      } else if (kind == KIND_BUSY) {
+        const PRec &p = prec[pl & 0x3fffffffu];
+        len = busy_len(tc[p.crank], p, grec[p.sid], p.sid);
+      } else {
+        const uint32_t sid = pl & 0xfffu;
+        len = idle_len(tc[(pl >> 12) & 0x3ffffu], sid == IDLE_NONE ? NONE32 : sid);
+      }
+      too_long |= len > MAX_LINE_BYTES;
+    }
+    const uint32_t incl = warp_incl_scan(len);
+    if (i < nl) loff[i] = nb + incl - len;
+    nb += __shfl_sync(FULL, incl, 31);
+  }
+  if (l == 0) loff[nl] = nb;
+  if (__any_sync(FULL, too_long)) return false;
+  __syncwarp();
+  *o_ng = ng; *o_nl = nl; *o_nb = nb;
+  return true;
+}
+
+// Writes the planned lines of a regular document: stage in shared memory, 16-byte stores out.
+__device__ void fast_emit(const FusedParams &P, const WorkDev &w, uint32_t *S, uint8_t *Sb,
+                          const WarpSlice &ws, uint32_t ng, uint32_t nl, uint64_t line0, uint64_t byte0) {
+  const uint32_t l = lane_id();
+  const TbHeader &hd = *reinterpret_cast<const TbHeader *>(Sb + ws.tb);
+  const TbCont *tc = reinterpret_cast<const TbCont *>(Sb + ws.tb + sizeof(TbHeader));
+  const GRec *grec = reinterpret_cast<const GRec *>(Sb + ws.grec);
+  const PRec *prec = reinterpret_cast<const PRec *>(Sb + ws.prec);
+  const uint32_t *plan = S + (ws.plan >> 2), *loff = S + (ws.loff >> 2);
+  (void)ng;
+  uint32_t i0 = 0;
+  while (i0 < nl) {
+    const uint32_t r_lo = loff[i0];
+    const uint32_t pad = (uint32_t)((byte0 + r_lo) & 15ull);
+    // as many of the next 32 lines as the stage holds
+    const uint32_t cand = i0 + l + 1;
+    const bool fits = cand <= nl && pad + (loff[min(cand, nl)] - r_lo) + 16u <= P.stage_bytes;
+    const uint32_t take = __popc(__ballot_sync(FULL, fits));
+    if (take == 0) return;                          // cannot happen: the stage holds any single line
+    const uint32_t i1 = i0 + take, i = i0 + l;
+    if (i < i1) {
+      const uint32_t pl = plan[i], kind = pl >> 30;
+      Seg segs[MAX_SEGS];
+      if (kind == KIND_NODE) {
+        const uint32_t r = pl & 0xffffu;
+        node_segs(segs, 0u, ws.tb, hd, ws.tg, grec[r], ws.grec + r * (uint32_t)sizeof(GRec) + (uint32_t)offsetof(GRec, fstr), r);
+      } else if (kind == KIND_BUSY) {
+        const PRec &p = prec[pl & 0x3fffffffu];
+        busy_segs(segs, 0u, ws.tb, tc[p.crank], ws.tg, ws.ta, p, grec[p.sid], p.sid);
+      } else {
+        const uint32_t sid = pl & 0xfffu;
+        idle_segs(segs, 0u, ws.tb, tc[(pl >> 12) & 0x3ffffu], sid == IDLE_NONE ? NONE32 : sid);
+      }
+      write_line(S, ws.stage + pad + (loff[i] - r_lo), segs);
+      w.line_off[line0 + i] = byte0 + loff[i];
+    }
+    __syncwarp();
+    // stage -> global: byte stores up to the first 16-byte boundary and after the last one
+    const uint32_t nbytes = loff[i1] - r_lo;
+    uint8_t *g = w.out + byte0 + r_lo;
+    const uint8_t *st = Sb + ws.stage + pad;
+    const uint32_t head = min(nbytes, (16u - pad) & 15u);
+    if (l < head) g[l] = st[l];
+    const uint32_t nvec = (nbytes - head) >> 4;
+    for (uint32_t v = l; v < nvec; v += 32)
+      *reinterpret_cast<uint4 *>(g + head + 16u * v) = *reinterpret_cast<const uint4 *>(st + head + 16u * v);
+    const uint32_t done = head + 16u * nvec;
+    if (l < nbytes - done) g[done + l] = st[done + l];
+    __syncwarp();
+    i0 = i1;
+  }
+}
+
+// ---- generic path for one document (device functions of the staged kernels) -------------------
+__device__ void slow_plan(uint32_t d, const BatchDev &b, const FleetDev &f, const WorkDev &w, uint32_t *scratch,
+                          uint32_t *nl, uint32_t *nb) {
+  uint32_t g0, ng, gerr, p0, np, perr;
+  tokenize_text<GpuRow, GpuRowScan, 1>(b.gpu_csv, (uint32_t)b.gpu_off[d], (uint32_t)b.gpu_off[d + 1], w.grow,
+                                       w.grow_cap, w.counters + CTR_GROW, w.counters + CTR_OVERFLOW, OVF_GROW,
+                                       &g0, &ng, &gerr);
+  tokenize_text<ProcRow, ProcRowScan, 3>(b.apps_csv, (uint32_t)b.apps_off[d], (uint32_t)b.apps_off[d + 1], w.prow,
+                                         w.prow_cap, w.counters + CTR_PROW, w.counters + CTR_OVERFLOW, OVF_PROW,
+                                         &p0, &np, &perr);
+  if (lane_id() == 0) {
+    w.doc_g0[d] = g0; w.doc_ng[d] = ng;
+    w.doc_p0[d] = p0; w.doc_np[d] = np;
+    w.doc_perr[d] = gerr ? gerr : perr;
+  }
+  __threadfence_block();
+  __syncwarp();
+  join_doc(d, b, f, w, scratch, scratch + f.max_nc, scratch + 2 * f.max_nc);
+  __threadfence_block();
+  __syncwarp();
+  *nl = w.doc_nlines[d];
+  *nb = w.doc_nbytes[d];
+}
+
+__device__ void slow_emit(uint32_t d, const BatchDev &b, const FleetDev &f, const WorkDev &w, uint32_t nl,
+                          uint64_t line0, uint64_t byte0) {
+  const uint32_t desc0 = w.doc_desc0[d];
+  for (uint32_t i = lane_id(); i < nl; i += 32) {
+    const uint32_t di = desc0 + i;
+    const LineDesc ds = w.desc[di];
+    const uint64_t goff = byte0 + w.line_loff[di];
+    ByteSink s{w.out + goff};
+    const uint32_t kind = ds.kind_ref >> 30, ref = ds.kind_ref & 0x3fffffffu;
+    if (kind == LINE_NODE) {
+      compose_node_line(s, f.skel, f.node_piece + (size_t)b.doc_node[ds.doc] * NODE_PIECES, b.gpu_csv,
+                        w.grow[ds.a], ds.b, w.fstr + (size_t)ds.a * FSTR_STRIDE);
+    } else if (kind == LINE_BUSY) {
+      const ProcRow &pr = w.prow[ds.a];
+      compose_busy_line(s, f.skel, f.cont_piece + (size_t)ref * POD_PIECES, b.gpu_csv, b.apps_csv, pr,
+                        w.grow[ds.b], pr.sid);
+    } else {
+      compose_idle_line(s, f.skel, f.cont_piece + (size_t)ref * POD_PIECES, ds.a);
+    }
+    w.line_off[line0 + i] = goff;
+  }
+}
+
+__global__ void __launch_bounds__(POLL_THREADS, 2) k_poll(BatchDev b, FleetDev f, WorkDev w, FusedParams P) {
+  extern __shared__ __align__(16) uint32_t S[];
+  uint8_t *Sb = reinterpret_cast<uint8_t *>(S);
+  // constant strings (same for every CTA)
+  for (uint32_t i = threadIdx.x; i < CONST_PAD / 4; i += POLL_THREADS) S[i] = 0;
+  __syncthreads();
+  if (threadIdx.x == 0) fill_const_strings(Sb);
+  for (uint32_t v = threadIdx.x; v <= MAX_FAST_SID; v += POLL_THREADS) fill_const_decimal(Sb, v);
+  // the counters of the NEXT launch start from zero (this launch uses the other set)
+  if (blockIdx.x == 0 && threadIdx.x < CTR_COUNT) P.next_counters[threadIdx.x] = 0;
+  __syncthreads();
+
+  const uint32_t wib = threadIdx.x >> 5, l = lane_id();
+  const uint32_t base = CONST_PAD + wib * P.warp_bytes;
+  WarpSlice ws;
+  ws.tg = base + P.off_tg; ws.ta = base + P.off_ta; ws.gstart = base + P.off_gstart;
+  ws.pstart = base + P.off_pstart; ws.grec = base + P.off_grec; ws.prec = base + P.off_prec;
+  ws.cnt = base + P.off_cnt; ws.cstart = base + P.off_cstart; ws.plan = base + P.off_plan;
+  ws.loff = base + P.off_loff; ws.tb = base + P.off_tb; ws.stage = base + P.off_stage;
+
+  for (;;) {
+    unsigned long long t = 0;
+    if (l == 0) t = atomicAdd(P.ticket, 1ull) - P.ticket_base;
+    t = __shfl_sync(FULL, t, 0);
+    if (t >= b.n_docs) break;
+    const uint32_t d = (uint32_t)t;
+    uint32_t ng = 0, nl = 0, nb = 0;
+    const bool fastdoc = P.allow_fast && fast_plan(d, b, f, P, S, Sb, ws, &ng, &nl, &nb);
+    __syncwarp();
+    if (!fastdoc) {
+      slow_plan(d, b, f, w, S + (ws.stage >> 2), &nl, &nb);
+      if (l == 0) atomicAdd(w.counters + CTR_SLOW, 1u);
+    }
+    uint64_t line0, byte0;
+    doc_exclusive_scan(P, d, nl, nb, &line0, &byte0);
+    if (l == 0) {
+      w.doc_line_off[d] = line0;
+      w.doc_byte_off[d] = byte0;
+      if (fastdoc) { w.doc_status[d] = 0; w.doc_nlines[d] = nl; w.doc_nbytes[d] = nb; }
+      if (d + 1 == b.n_docs) {
+        w.doc_line_off[b.n_docs] = line0 + nl;
+        w.doc_byte_off[b.n_docs] = byte0 + nb;
+        w.totals[0] = line0 + nl;
+        w.totals[1] = byte0 + nb;
+        w.line_off[min(line0 + nl, (uint64_t)w.desc_cap)] = byte0 + nb;
+      }
+    }
+    if (byte0 + nb > w.out_cap || line0 + nl > w.desc_cap) {
+      if (l == 0) atomicOr(w.counters + CTR_OVERFLOW, (byte0 + nb > w.out_cap ? OVF_OUT : 0u) |
+                                                       (line0 + nl > w.desc_cap ? OVF_DESC : 0u));
+      continue;
+    }
+    if (fastdoc) fast_emit(P, w, S, Sb, ws, ng, nl, line0, byte0);
+    else slow_emit(d, b, f, w, nl, line0, byte0);
+    __syncwarp();
+  }
+}
+
+}  // namespace
+
+int poll_smem_bytes(const FusedParams &P) { return (int)(CONST_PAD + (POLL_THREADS / 32) * P.warp_bytes); }
+
+void launch_poll(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P, int blocks,
+                 cudaStream_t s) {
+  cudaFuncSetAttribute(k_poll, cudaFuncAttributeMaxDynamicSharedMemorySize, poll_smem_bytes(P));
+  k_poll<<<blocks, POLL_THREADS, poll_smem_bytes(P), s>>>(b, f, w, P);
+}
+
+}  // namespace kgm

@@ -699,6 +699,11 @@ __global__ void k_flush(uint4 *buf, uint64_t n16) {
 }
 
 }  // namespace
+}  // namespace kgm
+
+#include "kgm_fused.cuh"
+
+namespace kgm {
 
 void launch_tokenize(const BatchDev &b, const WorkDev &w, int sms, cudaStream_t s) {
   const int warps_per_block = TOK_THREADS / 32;

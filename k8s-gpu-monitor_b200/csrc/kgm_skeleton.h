@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "kgm_common.cuh"
+#include "kgm_fast.cuh"
 
 namespace kgm {
 
@@ -52,5 +53,67 @@ struct SkelPool {
     return fixed;
   }
 };
+
+// ---- template block of one node, for the fused kernel's fast path (kgm_fast.cuh) -------------
+// header | container directory | node pieces | per gated container its 5 variable pieces
+struct TbContIn {
+  bool gated;
+  std::string cid, ns, pod, user;
+  uint32_t vis_begin, nvis;
+  uint32_t fixed;             // SkelPool::pod_pieces() of the same strings
+};
+
+// Appends the block to `out` (16-byte aligned start) and returns true, or leaves `out`
+// untouched and returns false if a length does not fit the block's 16-bit fields.
+inline bool build_template_block(const std::string &host, uint32_t node_fixed,
+                                 const std::vector<TbContIn> &conts, std::vector<uint8_t> &out,
+                                 size_t *start_out, size_t *len_out) {
+  const uint32_t ncn = (uint32_t)conts.size();
+  const std::string n0 = "node_gpu,host=" + host + ",gpu_id=", n5 = ",node=\"" + host + "\",gid=";
+  fast::TbHeader hd{};
+  std::vector<fast::TbCont> dir(ncn);
+  std::vector<uint8_t> pieces;
+  const size_t dir_end = sizeof(fast::TbHeader) + sizeof(fast::TbCont) * (size_t)ncn;
+  bool ok = node_fixed <= 60000 && dir_end + n0.size() + n5.size() <= 60000;
+  hd.nc = ncn;
+  hd.n0_off = (uint16_t)dir_end; hd.n0_len = (uint16_t)n0.size();
+  pieces.insert(pieces.end(), n0.begin(), n0.end());
+  hd.n5_off = (uint16_t)(dir_end + pieces.size()); hd.n5_len = (uint16_t)n5.size();
+  pieces.insert(pieces.end(), n5.begin(), n5.end());
+  hd.fixed = (uint16_t)node_fixed;
+  for (uint32_t c = 0; c < ncn && ok; ++c) {
+    const TbContIn &in = conts[c];
+    fast::TbCont &t = dir[c];
+    t = fast::TbCont{};
+    t.gated = in.gated ? 1 : 0;
+    t.vis_begin = in.vis_begin;
+    t.nvis = in.nvis;
+    t.blk_off = (uint32_t)(dir_end + pieces.size());
+    if (!in.gated) continue;
+    const std::string pc[5] = {"pod_gpu,host=" + host + ",namespace=" + in.ns + ",gpu_id=",
+                               ",containerid=" + in.cid + ",pid_t=",
+                               ",user_name_t=" + in.user + " procressname=\"",
+                               "\",podname=\"" + in.pod + "\",pid=\"",
+                               "\",node=\"" + host + "\",user_name=\"" + in.user + "\",gpu_util="};
+    for (int i = 0; i < 5; ++i) {
+      if (pc[i].size() > 60000) ok = false;
+      t.plen[i] = (uint16_t)pc[i].size();
+      pieces.insert(pieces.end(), pc[i].begin(), pc[i].end());
+    }
+    if (in.fixed > 60000) ok = false;
+    t.fixed = (uint16_t)in.fixed;
+  }
+  const size_t total = dir_end + pieces.size();
+  if (!ok || total > 96 * 1024) return false;
+  while (out.size() & 15) out.push_back(0);
+  *start_out = out.size();
+  *len_out = total;
+  const uint8_t *hp = reinterpret_cast<const uint8_t *>(&hd);
+  out.insert(out.end(), hp, hp + sizeof(hd));
+  const uint8_t *dp = reinterpret_cast<const uint8_t *>(dir.data());
+  out.insert(out.end(), dp, dp + sizeof(fast::TbCont) * (size_t)ncn);
+  out.insert(out.end(), pieces.begin(), pieces.end());
+  return true;
+}
 
 }  // namespace kgm

@@ -78,7 +78,8 @@ class KgmTiming(C.Structure):
     _fields_ = [
         ("h2d_ms", C.c_float), ("tokenize_ms", C.c_float), ("join_ms", C.c_float),
         ("scan_ms", C.c_float), ("encode_ms", C.c_float), ("d2h_ms", C.c_float),
-        ("total_ms", C.c_float), ("launches", C.c_uint32),
+        ("total_ms", C.c_float), ("launches", C.c_uint32), ("fused", C.c_uint32),
+        ("slow_docs", C.c_uint32),
     ]
 
 
@@ -95,6 +96,7 @@ SIGNATURES = {
     "kgm_encode_resident": (C.c_int, [C.c_void_p, C.POINTER(KgmResult)]),
     "kgm_fetch_result": (C.c_int, [C.c_void_p, C.POINTER(KgmResult)]),
     "kgm_get_timing": (C.c_int, [C.c_void_p, C.POINTER(KgmTiming)]),
+    "kgm_set_pipeline": (C.c_int, [C.c_void_p, C.c_int]),
     "kgm_flush_l2": (C.c_int, [C.c_void_p, C.c_uint64]),
     "kgm_host_alloc": (C.c_void_p, [C.c_uint64]),
     "kgm_host_free": (None, [C.c_void_p]),
@@ -103,6 +105,8 @@ SIGNATURES = {
                                            C.c_void_p, C.c_void_p]),
 }
 NOALLOC_MAX_ROWS = 16384
+ABI_VERSION = 2
+PIPELINE_AUTO, PIPELINE_STAGED, PIPELINE_FUSED_GENERIC = 0, 1, 2
 
 _lib = None
 

@@ -123,7 +123,7 @@ class HostResult:
 class Monitor:
     def __init__(self, device=0):
         self._lib = _ffi.load()
-        if self._lib.kgm_abi_version() != 1:
+        if self._lib.kgm_abi_version() != _ffi.ABI_VERSION:
             raise RuntimeError("libkgm.so ABI mismatch")
         self._ctx = C.c_void_p()
         _check(self._lib.kgm_create(C.byref(self._ctx), device), "kgm_create", None, self._lib)
@@ -197,6 +197,10 @@ class Monitor:
         t = _ffi.KgmTiming()
         _check(self._lib.kgm_get_timing(self._ctx, C.byref(t)), "kgm_get_timing", self._ctx, self._lib)
         return {k: getattr(t, k) for k, _ in _ffi.KgmTiming._fields_}
+
+    def set_pipeline(self, mode):
+        """PIPELINE_AUTO (fused kernel when the batch fits), PIPELINE_STAGED, PIPELINE_FUSED_GENERIC."""
+        _check(self._lib.kgm_set_pipeline(self._ctx, int(mode)), "kgm_set_pipeline", self._ctx, self._lib)
 
     def flush_l2(self, nbytes=256 << 20):
         _check(self._lib.kgm_flush_l2(self._ctx, nbytes), "kgm_flush_l2", self._ctx, self._lib)

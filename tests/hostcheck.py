@@ -17,6 +17,7 @@ def lib():
     if _lib is None:
         _lib = C.CDLL(build.build_hostcheck())
         _lib.hc_hash_bytes.restype = C.c_uint64
+        _lib.hc_key_hash_bytes.restype = C.c_uint64
     return _lib
 
 
@@ -85,3 +86,64 @@ def idle_line(host, ns, cid, user, pod, sid):
 
 def hash_bytes(b: bytes) -> int:
     return lib().hc_hash_bytes(b, len(b))
+
+
+# ---- fast path of the fused kernel -----------------------------------------------------------
+def _line_or_none(n, out):
+    """(line bytes, guards intact) from a buffer with 8 guard bytes either side."""
+    if n < 0:
+        return None, True
+    raw = bytes(out[:n + 16])
+    return raw[8:8 + n], raw[:8] == b"\x5a" * 8 and raw[8 + n:] == b"\x5a" * 8
+
+
+def fast_node_line(host, row: bytes, sid, shift=0, align=0):
+    out = (C.c_ubyte * 20000)()
+    planned = C.c_uint32()
+    n = lib().hc_fast_node_line(host.encode(), row + b"\0" * 16, len(row), sid, shift, align, out,
+                                C.byref(planned))
+    line, guards = _line_or_none(n, out)
+    return line, planned.value, guards
+
+
+def fast_busy_line(host, ns, cid, user, pod, prow: bytes, grow: bytes, sid, shift=0, align=0):
+    out = (C.c_ubyte * 20000)()
+    planned = C.c_uint32()
+    n = lib().hc_fast_busy_line(host.encode(), ns.encode(), cid.encode(), user.encode(), pod.encode(),
+                                prow + b"\0" * 16, len(prow), grow + b"\0" * 16, len(grow), sid, shift,
+                                align, out, C.byref(planned))
+    line, guards = _line_or_none(n, out)
+    return line, planned.value, guards
+
+
+def fast_idle_line(host, ns, cid, user, pod, sid, align=0):
+    out = (C.c_ubyte * 20000)()
+    planned = C.c_uint32()
+    n = lib().hc_fast_idle_line(host.encode(), ns.encode(), cid.encode(), user.encode(), pod.encode(),
+                                0xFFFFFFFF if sid is None else sid, align, out, C.byref(planned))
+    line, guards = _line_or_none(n, out)
+    return line, planned.value, guards
+
+
+def fast_gpu_row(row: bytes, shift=0):
+    out = (C.c_uint32 * 16)()
+    h = C.c_uint64()
+    if not lib().hc_fast_gpu_row(row + b"\0" * 16, len(row), shift, out, C.byref(h)):
+        return None
+    f = lambda i: row[out[2 * i]:out[2 * i] + out[2 * i + 1]]
+    return dict(key=f(0), util=f(1), mt=f(2), mu=f(3), mf=f(4), hash=h.value)
+
+
+def fast_proc_row(row: bytes, shift=0):
+    out = (C.c_uint32 * 16)()
+    key = (C.c_ubyte * 48)()
+    u64 = (C.c_uint64 * 2)()
+    if not lib().hc_fast_proc_row(row + b"\0" * 16, len(row), shift, out, key, u64):
+        return None
+    f = lambda i: row[out[2 * i]:out[2 * i] + out[2 * i + 1]]
+    return dict(pid=f(0), name=b"".join(f(1 + i) for i in range(4)), mem=f(5), key=bytes(key[:out[12]]),
+                hash=u64[0], pidkey=u64[1])
+
+
+def key_hash_bytes(b: bytes) -> int:
+    return lib().hc_key_hash_bytes(b, len(b))

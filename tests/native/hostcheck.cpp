@@ -110,6 +110,140 @@ int hc_idle_line(const char *host, const char *ns, const char *cid, const char *
   return (int)(s.p - out);
 }
 
+// ---- fast path of the fused kernel (kgm_fast.cuh), laid out like a warp's shared-memory slice:
+//      const area | gpu text window | apps text window | template block | records | stage
+struct FastSlice {
+  std::vector<uint32_t> words;
+  uint32_t tg, ta, tb, rec, stage;
+  uint8_t *bytes() { return reinterpret_cast<uint8_t *>(words.data()); }
+};
+
+static FastSlice make_slice(const uint8_t *gtext, uint32_t glen, uint32_t gshift, const uint8_t *atext,
+                            uint32_t alen, uint32_t ashift, const std::vector<uint8_t> &tb) {
+  FastSlice sl;
+  auto r16 = [](uint32_t v) { return (v + 15u) & ~15u; };
+  const uint32_t cpad = r16(fast::ConstArea::BYTES);
+  sl.tg = cpad;
+  sl.ta = sl.tg + r16(gshift + glen) + 48;
+  sl.tb = sl.ta + r16(ashift + alen) + 48;
+  sl.rec = sl.tb + r16((uint32_t)tb.size()) + 32;
+  sl.stage = sl.rec + 4096;
+  sl.words.assign((sl.stage + 3 * MAX_LINE_BYTES) / 4, 0x5a5a5a5au);
+  fast::fill_const_area(sl.bytes());
+  memcpy(sl.bytes() + sl.tg + gshift, gtext, glen);
+  memcpy(sl.bytes() + sl.ta + ashift, atext, alen);
+  memcpy(sl.bytes() + sl.tb, tb.data(), tb.size());
+  return sl;
+}
+
+static bool one_container_block(const char *host, const char *ns, const char *cid, const char *user,
+                                const char *pod, std::vector<uint8_t> &tb, uint32_t *node_fixed) {
+  SkelPool pool;
+  Piece pc[POD_PIECES], npc[NODE_PIECES];
+  *node_fixed = pool.node_pieces(host, npc);
+  std::vector<TbContIn> conts(1);
+  conts[0].gated = true;
+  conts[0].cid = cid; conts[0].ns = ns; conts[0].pod = pod; conts[0].user = user;
+  conts[0].vis_begin = 0; conts[0].nvis = 0;
+  conts[0].fixed = pool.pod_pieces(host, ns, cid, user, pod, pc);
+  size_t start = 0, len = 0;
+  return build_template_block(host, *node_fixed, conts, tb, &start, &len);
+}
+
+// node_gpu line through the fast path.  Returns -1 if the row is irregular (generic path),
+// else the bytes written at stage offset `align`; *planned = the length the fast path plans.
+int hc_fast_node_line(const char *host, const uint8_t *row, uint32_t row_len, uint32_t sid, uint32_t shift,
+                      uint32_t align, uint8_t *out, uint32_t *planned) {
+  std::vector<uint8_t> tb;
+  uint32_t node_fixed;
+  if (!one_container_block(host, "ns", "cid", "user", "pod", tb, &node_fixed)) return -2;
+  FastSlice sl = make_slice(row, row_len, shift, row, 0, 0, tb);
+  fast::GRec g;
+  if (!fast::parse_gpu_row(sl.words.data() + sl.tg / 4, shift, shift + row_len, node_fixed, sid, g)) return -1;
+  fast::GRec *gr = reinterpret_cast<fast::GRec *>(sl.bytes() + sl.rec);
+  *gr = g;
+  *planned = g.line_len;
+  const fast::TbHeader &hd = *reinterpret_cast<const fast::TbHeader *>(sl.bytes() + sl.tb);
+  fast::Seg segs[fast::MAX_SEGS];
+  fast::node_segs(segs, 0u, sl.tb, hd, sl.tg, *gr, sl.rec + (uint32_t)offsetof(fast::GRec, fstr), sid);
+  const uint32_t n = fast::write_line(sl.words.data(), sl.stage + 64 + align, segs);
+  memcpy(out, sl.bytes() + sl.stage + 64 + align - 8, n + 16);      // 8 guard bytes either side
+  return (int)n;
+}
+
+int hc_fast_busy_line(const char *host, const char *ns, const char *cid, const char *user, const char *pod,
+                      const uint8_t *prow, uint32_t prow_len, const uint8_t *grow, uint32_t grow_len,
+                      uint32_t sid, uint32_t shift, uint32_t align, uint8_t *out, uint32_t *planned) {
+  std::vector<uint8_t> tb;
+  uint32_t node_fixed;
+  if (!one_container_block(host, ns, cid, user, pod, tb, &node_fixed)) return -2;
+  FastSlice sl = make_slice(grow, grow_len, shift, prow, prow_len, (shift * 7 + 3) & 15, tb);
+  const uint32_t ashift = (shift * 7 + 3) & 15;
+  fast::GRec g;
+  if (!fast::parse_gpu_row(sl.words.data() + sl.tg / 4, shift, shift + grow_len, node_fixed, sid, g)) return -1;
+  fast::PRec p;
+  uint32_t kw[fast::KEY_WORDS], klen;
+  uint64_t kh;
+  if (!fast::parse_proc_row(sl.words.data() + sl.ta / 4, ashift, ashift + prow_len, p, kw, &klen, &kh)) return -1;
+  const fast::TbCont *tc = reinterpret_cast<const fast::TbCont *>(sl.bytes() + sl.tb + sizeof(fast::TbHeader));
+  p.sid = (uint16_t)sid; p.crank = 0;
+  *planned = fast::busy_len(tc[0], p, g, sid);
+  fast::Seg segs[fast::MAX_SEGS];
+  fast::busy_segs(segs, 0u, sl.tb, tc[0], sl.tg, sl.ta, p, g, sid);
+  const uint32_t n = fast::write_line(sl.words.data(), sl.stage + 64 + align, segs);
+  memcpy(out, sl.bytes() + sl.stage + 64 + align - 8, n + 16);
+  return (int)n;
+}
+
+int hc_fast_idle_line(const char *host, const char *ns, const char *cid, const char *user, const char *pod,
+                      uint32_t sid, uint32_t align, uint8_t *out, uint32_t *planned) {
+  std::vector<uint8_t> tb;
+  uint32_t node_fixed;
+  if (!one_container_block(host, ns, cid, user, pod, tb, &node_fixed)) return -2;
+  const uint8_t dummy[4] = {0, 0, 0, 0};
+  FastSlice sl = make_slice(dummy, 0, 0, dummy, 0, 0, tb);
+  const fast::TbCont *tc = reinterpret_cast<const fast::TbCont *>(sl.bytes() + sl.tb + sizeof(fast::TbHeader));
+  *planned = fast::idle_len(tc[0], sid);
+  fast::Seg segs[fast::MAX_SEGS];
+  fast::idle_segs(segs, 0u, sl.tb, tc[0], sid);
+  const uint32_t n = fast::write_line(sl.words.data(), sl.stage + 64 + align, segs);
+  memcpy(out, sl.bytes() + sl.stage + 64 + align - 8, n + 16);
+  return (int)n;
+}
+
+// Fields the fast gpu-row parser extracts: out = key off/len, util off/len, mt, mu, mf off/len
+int hc_fast_gpu_row(const uint8_t *row, uint32_t row_len, uint32_t shift, uint32_t *out, uint64_t *hash) {
+  std::vector<uint8_t> tb(16, 0);
+  FastSlice sl = make_slice(row, row_len, shift, row, 0, 0, tb);
+  fast::GRec g;
+  if (!fast::parse_gpu_row(sl.words.data() + sl.tg / 4, shift, shift + row_len, 100, 0, g)) return 0;
+  const fast::Run runs[5] = {g.key, g.util, g.mt, g.mu, g.mf};
+  for (int i = 0; i < 5; ++i) { out[2 * i] = runs[i].off - shift; out[2 * i + 1] = runs[i].len; }
+  *hash = g.hash;
+  return 1;
+}
+
+// out = pid off/len, 4 name runs off/len, mem off/len, key len; key bytes -> key[48]
+int hc_fast_proc_row(const uint8_t *row, uint32_t row_len, uint32_t shift, uint32_t *out, uint8_t *key,
+                     uint64_t *u64out) {
+  std::vector<uint8_t> tb(16, 0);
+  FastSlice sl = make_slice(row, 0, 0, row, row_len, shift, tb);
+  fast::PRec p;
+  uint32_t kw[fast::KEY_WORDS], klen;
+  uint64_t kh;
+  if (!fast::parse_proc_row(sl.words.data() + sl.ta / 4, shift, shift + row_len, p, kw, &klen, &kh)) return 0;
+  int k = 0;
+  out[k++] = p.pid.off - shift; out[k++] = p.pid.len;
+  for (int i = 0; i < fast::NAME_RUNS; ++i) { out[k++] = p.name[i].off - shift; out[k++] = p.name[i].len; }
+  out[k++] = p.mem.off - shift; out[k++] = p.mem.len;
+  out[k++] = klen;
+  memcpy(key, kw, 4 * fast::KEY_WORDS);
+  u64out[0] = kh; u64out[1] = p.pidkey;
+  return 1;
+}
+
+uint64_t hc_key_hash_bytes(const uint8_t *p, uint32_t n) { return fast::key_hash_bytes(p, n); }
+
 uint64_t hc_hash_bytes(const uint8_t *p, uint32_t n) {
   uint64_t h = hash_init();
   for (uint32_t i = 0; i < n; ++i) h = hash_step(h, p[i]);

@@ -186,3 +186,104 @@ def test_pod_lines_match_the_oracle_template():
         want = poll_oracle.pod_line("h", "-", sid, "cid", "-", 0, "-", "-", "-", 0)
         got, planned = hc.idle_line("h", "-", "cid", "-", "-", sid)
         assert got == (want + "\n").encode() and planned == len(got)
+
+
+# ---- fast path of the fused kernel (kgm_fast.cuh) ---------------------------------------------
+# The fast path may decline a row ("irregular": the kernel then re-does the document with the
+# generic code tested above); whenever it accepts one, its bytes must be the reference's.
+def _digits(s):
+    return re.sub(r"\D", "", s)
+
+
+def test_fast_gpu_row_parser_agrees_with_csv_and_re_or_declines():
+    rng = random.Random(17)
+    base = [r for r in ROW_POOL if r.startswith("GPU")][:200]
+    rows = base + [_mutate(rng, rng.choice(base)) for _ in range(4000)]
+    accepted = 0
+    for row in rows:
+        if not row.isascii():
+            continue
+        for shift in (0, rng.randrange(16)):
+            got = hc.fast_gpu_row(row.encode(), shift)
+            cells = _py_cells(row) if "\r" not in row and '"' not in row else None
+            if got is None:
+                continue
+            accepted += 1
+            assert cells is not None and len(cells) >= 6, row
+            assert got["key"].decode() == cells[0].lstrip(), row
+            assert got["util"].decode() == _digits(cells[1]), row
+            assert got["mt"].decode() == _digits(cells[3]) and got["mu"].decode() == _digits(cells[4]), row
+            assert got["mf"].decode() == _digits(cells[5]), row
+            assert int(_digits(cells[3])) != 0
+            assert got["hash"] == hc.key_hash_bytes(cells[0].lstrip().encode())
+    assert accepted > 1500                                   # the clean rows do take the fast path
+    typical = re.compile(r"^GPU-[0-9a-f-]+, \d+ %, \d+ %, [1-9]\d{0,8} MiB, \d{1,9} MiB, \d{1,9} MiB$")
+    assert sum(1 for row in base if typical.match(row)) > 20
+    for row in base:
+        if typical.match(row):
+            assert hc.fast_gpu_row(row.encode()) is not None, row
+
+
+def test_fast_proc_row_parser_agrees_with_csv_and_re_or_declines():
+    rng = random.Random(19)
+    base = [r for r in ROW_POOL if not r.startswith("GPU") and r.count(",") == 3][:200]
+    rows = base + [_mutate(rng, rng.choice(base)) for _ in range(4000)]
+    accepted = 0
+    for row in rows:
+        if not row.isascii():
+            continue
+        shift = rng.randrange(16)
+        got = hc.fast_proc_row(row.encode(), shift)
+        if got is None:
+            continue
+        accepted += 1
+        assert "\r" not in row and '"' not in row, row
+        cells = _py_cells(row)
+        assert len(cells) >= 4, row
+        assert got["pid"].decode() == cells[0], row
+        assert got["name"].decode() == cells[1].replace(" ", ""), row
+        assert got["key"].decode() == cells[2].lstrip(), row
+        assert got["mem"].decode() == _digits(cells[3]), row
+        assert got["hash"] == hc.key_hash_bytes(cells[2].lstrip().encode())
+        if len(cells[0]) <= 7:
+            assert got["pidkey"] == int.from_bytes(cells[0].encode(), "little") | (len(cells[0]) << 56)
+    assert accepted > 1500
+
+
+def test_fast_lines_are_the_generic_lines_at_every_alignment():
+    """node / busy / idle lines composed by the word-wise writer == the byte-wise composer
+    (itself pinned to the oracle above), at every stage alignment and text shift, without
+    touching a byte outside the line."""
+    rng = random.Random(23)
+    grows = [r for r in ROW_POOL if r.startswith("GPU")][:60]
+    prows = [r for r in ROW_POOL if not r.startswith("GPU") and r.count(",") == 3][:60]
+    prows += ["34443, python3 train.py --lr 1, %s, 419 MiB" % "GPU-aaaa", "7, a  b, GPU-x, 1 MiB"]
+    hosts = ["node-a", "k8s-node-gpu-00012", "n", "None"]
+    checked = 0
+    for _ in range(400):
+        host = rng.choice(hosts)
+        grow, prow = rng.choice(grows), rng.choice(prows)
+        sid = rng.choice([0, 1, 7, 9, 10, 15, 99, 100, 255])
+        shift, align = rng.randrange(16), rng.randrange(16)
+        want, planned_w, n_w = hc.node_line(host, grow.encode(), sid)
+        got, planned, guards = hc.fast_node_line(host, grow.encode(), sid, shift, align)
+        if got is not None:
+            assert want is not None and got == want and planned == len(want) == planned_w and guards, grow
+            checked += 1
+        else:
+            assert want is None or len(want) > 8192 or not hc.fast_gpu_row(grow.encode())
+        ns, cid, user, pod = rng.choice([("ns2", "76a082ecc41d", "q", "jupyter-q-0"),
+                                         ("10007089-name", "16ee8a182726", "alice-bob",
+                                          "turing-gpu-notebook-alice-bob-5d9f-xk2p"), ("-", "c", "-", "-")])
+        want, planned_w, n_w = hc.busy_line(host, ns, cid, user, pod, prow.encode(), grow.encode(), sid)
+        got, planned, guards = hc.fast_busy_line(host, ns, cid, user, pod, prow.encode(), grow.encode(), sid,
+                                                 shift, align)
+        if got is not None:
+            assert want is not None and got == want and planned == len(want) and guards, (prow, grow)
+            checked += 1
+        for s in (sid, None):
+            want, planned_w = hc.idle_line(host, ns, cid, user, pod, s)
+            got, planned, guards = hc.fast_idle_line(host, ns, cid, user, pod, s, align)
+            assert got == want and planned == len(want) and guards
+            checked += 1
+    assert checked > 1200

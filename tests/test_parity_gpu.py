@@ -22,9 +22,18 @@ GOLD = golden_io.load()
 UNSUPPORTED_OK = {"err_quoted_first_cell": _ffi.DOC_UNSUPPORTED_QUOTE}
 
 
-@pytest.fixture(scope="module")
-def mon():
+PIPELINES = {"fused": _ffi.PIPELINE_AUTO, "staged": _ffi.PIPELINE_STAGED,
+             "fused-generic": _ffi.PIPELINE_FUSED_GENERIC}
+
+
+@pytest.fixture(scope="module", params=list(PIPELINES))
+def mon(request):
+    """Every test runs three times: through the fused single-pass kernel (fast path, with its
+    in-kernel generic path for irregular documents), through the four staged kernels, and
+    through the fused kernel with the fast path switched off."""
     m = monitor.Monitor(0)
+    m.set_pipeline(PIPELINES[request.param])
+    m.pipeline_name = request.param
     yield m
     m.close()
 
@@ -190,7 +199,13 @@ def test_full_config2_properties_and_sampled_parity(mon):
     mon.encode_resident()
     assert mon.fetch().body == res.body
     t = mon.timing()
-    assert t["launches"] == 4 and t["total_ms"] > 0
+    assert t["total_ms"] > 0
+    if mon.pipeline_name == "staged":
+        assert t["launches"] == 4 and t["fused"] == 0
+    else:
+        # the clean fleet batch goes through the fast path entirely (or not at all when it is off)
+        assert t["launches"] == 1 and t["fused"] == 1
+        assert t["slow_docs"] == (0 if mon.pipeline_name == "fused" else rp.n_docs)
 
 
 def test_mem_util_floats_parse_back_within_tolerance(mon):
