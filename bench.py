@@ -3,8 +3,9 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl kgm|reference] [--config config2]
 
-A *step* is one pass of the whole hot path (tokenize -> join -> scan -> encode) over one
-batch of synthetic replayed nvidia-smi text.  At N=1 the workload is BASELINE.json
+A *step* is one pass of the whole hot path (tokenize -> join -> scan -> encode; by default
+all of it inside the one fused kernel k_poll, `--pipeline staged` runs the four staged
+kernels) over one batch of synthetic replayed nvidia-smi text.  At N=1 the workload is BASELINE.json
 `configs[1]`: 64 nodes x 8 GPUs x 60 ticks = 3840 documents, 30720 samples, 2048 pods.
 At N>1 (torchrun, one rank per GPU) every rank holds its own 64-node shard ("weak"
 scaling; hosts are the partition unit) and the step additionally all-gathers
@@ -15,7 +16,8 @@ Printed JSON (one line, rank 0):
           CUDA events on the library's stream, max over ranks; L2 flushed before each step
   e2e     the same through kgm_encode_batch with pinned HOST buffers: H2D of the texts and
           D2H of lines/offsets/statuses inside the timed region (wall clock around the call)
-  roofline  the encode kernel (dominant): algorithmic bytes per launch / its CUDA-event time
+  roofline  the dominant kernel (k_poll: the whole fused pass; k_encode when staged):
+          algorithmic bytes per launch / its CUDA-event time
   cpu_baseline  the oracle port of gpu.py timed on this box's host cores (N=1, rank 0)
 
 `--impl reference` times the reference's CPU implementation of the path (the oracle port of
@@ -220,6 +222,7 @@ def run_kgm_arm(args):
 
     rp, entries = build_workload(args.config, rank)
     mon = monitor.Monitor(local_rank)
+    mon.set_pipeline({"fused": 0, "staged": 1, "fused-generic": 2}[args.pipeline])
     mon.load_fleet(entries)
     batch = mon.make_batch(rp.gpu_texts, rp.apps_texts, rp.doc_node, rp.doc_tick, pinned=True)
     samples_rank = rp.n_samples()
@@ -272,6 +275,9 @@ def run_kgm_arm(args):
         sync_all()
     wall_ms = 1e3 * (time.perf_counter() - wall0) / args.steps
     mean = {k: sum(v) / len(v) for k, v in acc.items()}
+    last_t = mon.timing()
+    fused = bool(last_t["fused"])
+    launches_per_step = int(last_t["launches"])
     step_ms = mean["total_ms"] + (sum(coll_ms) / len(coll_ms) if coll_ms else 0.0)
 
     # ---- end to end through the C ABI with host buffers ----
@@ -306,7 +312,7 @@ def run_kgm_arm(args):
         algo_bytes = batch.gpu_bytes + batch.apps_bytes + n_bytes       # per launch, this rank
         achieved = algo_bytes / (enc_ms * 1e-3) / 1e9
         traffic = None
-        tpath = os.path.join(ROOT, "profiles", "encode_traffic.json")
+        tpath = os.path.join(ROOT, "profiles", "poll_traffic.json" if fused else "encode_traffic.json")
         if os.path.isfile(tpath):
             try:
                 traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
@@ -329,13 +335,15 @@ def run_kgm_arm(args):
             "collective_ms": (sum(coll_ms) / len(coll_ms)) if coll_ms else 0.0,
             "wall_ms_per_step_incl_flush": wall_ms,
             "pipeline_frac_of_peak": algo_bytes / (mean["total_ms"] * 1e-3) / 1e9 / peak,
-            "roofline": {"bound": "hbm", "kernel": "k_encode", "achieved": achieved, "peak": peak,
+            "pipeline": "fused (k_poll)" if fused else "staged (k_tokenize, k_join, k_scan, k_encode)",
+            "slow_docs_per_step": int(last_t["slow_docs"]),
+            "roofline": {"bound": "hbm", "kernel": "k_poll" if fused else "k_encode", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                          "algorithmic_bytes_per_launch": algo_bytes, "peak_source": peak_src,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
             "e2e": {"value": samples_total / (e2e_ms * 1e-3), "unit": "samples/s",
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms},
-            "gpu_launches": 4 * args.steps,
+            "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks.summary(),
         }
         if world == 1 and not args.no_cpu:
@@ -356,6 +364,7 @@ def main():
     ap.add_argument("--impl", default="kgm", choices=["kgm", "reference"])
     ap.add_argument("--config", default="config2", choices=["config1", "config2", "config3"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--pipeline", default="fused", choices=["fused", "staged", "fused-generic"])
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

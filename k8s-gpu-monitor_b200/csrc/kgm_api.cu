@@ -53,6 +53,7 @@ struct HostBuf {
 };
 
 enum { EV_START = 0, EV_H2D, EV_TOK, EV_JOIN, EV_SCAN, EV_ENC, EV_D2H, EV_COUNT };
+constexpr int MAX_CHUNKS = 8;
 
 }  // namespace
 
@@ -97,6 +98,11 @@ struct kgm_ctx {
   uint32_t fast_max_nc = 1, fast_max_tb = 0, fast_max_idle = 0, any_fast = 0;
   uint32_t slow_docs = 0;
   bool last_fused = false;
+  // chunked end-to-end path: copies and kernels of consecutive chunks overlap
+  cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+  cudaEvent_t ev_in[MAX_CHUNKS] = {}, ev_k[MAX_CHUNKS] = {};
+  HostBuf h_chunk;                         // per chunk: totals {lines, bytes} + counters
+  uint32_t last_chunks = 1;
 
   // results
   bool have_result = false;
@@ -176,7 +182,7 @@ int ensure_workspace(kgm_ctx *ctx) {
   CU(ctx->w_status.ensure((size_t)std::max(n, 1u) * sizeof(int32_t)));
   CU(ctx->w_doc_line_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
   CU(ctx->w_doc_byte_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
-  CU(ctx->w_totals.ensure(2 * sizeof(uint64_t)));
+  CU(ctx->w_totals.ensure(2 * (MAX_CHUNKS + 1) * sizeof(uint64_t)));
   CU(ctx->w_out.ensure((size_t)ctx->out_cap + 16));
   w.grow = ctx->w_grow.as<GpuRow>(); w.grow_cap = ctx->grow_cap;
   w.prow = ctx->w_prow.as<ProcRow>(); w.prow_cap = ctx->prow_cap;
@@ -395,7 +401,9 @@ void plan_fused(kgm_ctx *ctx, uint32_t n_docs, uint64_t max_g, uint64_t max_a) {
   }
 }
 
-int upload_batch(kgm_ctx *ctx, const kgm_batch *b) {
+// Validates a batch, sizes the device buffers and the workspace guesses for it and points
+// ctx->batch at them.  Nothing is copied.
+int prepare_batch(kgm_ctx *ctx, const kgm_batch *b, uint64_t *gb_out, uint64_t *ab_out) {
   if (!ctx->fleet_loaded) return KGM_E_STATE;
   if (!b || (b->n_docs && (!b->gpu_off || !b->apps_off || !b->doc_node))) return KGM_E_INVALID;
   const uint32_t n = b->n_docs;
@@ -416,14 +424,12 @@ int upload_batch(kgm_ctx *ctx, const kgm_batch *b) {
   if ((gb && !b->gpu_csv) || (ab && !b->apps_csv)) return KGM_E_INVALID;
   ctx->batch_resident = false;
   ctx->have_result = false;
-  CU(cudaEventRecord(ctx->ev[EV_START], ctx->stream));
-  int rc;
-  if ((rc = upload(ctx, ctx->b_gpu, b->gpu_csv, gb))) return rc;
-  if ((rc = upload(ctx, ctx->b_apps, b->apps_csv, ab))) return rc;
-  if ((rc = upload(ctx, ctx->b_gpu_off, goff, (size_t)n + 1))) return rc;
-  if ((rc = upload(ctx, ctx->b_apps_off, aoff, (size_t)n + 1))) return rc;
-  if ((rc = upload(ctx, ctx->b_node, b->doc_node, n))) return rc;
-  if (b->doc_tick && (rc = upload(ctx, ctx->b_tick, b->doc_tick, n))) return rc;
+  CU(ctx->b_gpu.ensure(std::max<uint64_t>(gb, 1)));
+  CU(ctx->b_apps.ensure(std::max<uint64_t>(ab, 1)));
+  CU(ctx->b_gpu_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
+  CU(ctx->b_apps_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
+  CU(ctx->b_node.ensure(std::max<size_t>(n, 1) * sizeof(uint32_t)));
+  if (b->doc_tick) CU(ctx->b_tick.ensure(std::max<size_t>(n, 1) * sizeof(uint32_t)));
   ctx->batch.n_docs = n;
   ctx->batch.gpu_csv = ctx->b_gpu.as<uint8_t>();
   ctx->batch.gpu_off = ctx->b_gpu_off.as<uint64_t>();
@@ -437,7 +443,145 @@ int upload_batch(kgm_ctx *ctx, const kgm_batch *b) {
   ctx->prow_cap = std::max<uint64_t>(ctx->prow_cap, ab / 40 + n + 64);
   ctx->desc_cap = std::max<uint64_t>(ctx->desc_cap, gb / 48 + ab / 40 + idle_cap + n + 64);
   ctx->out_cap = std::max<uint64_t>(ctx->out_cap, 4 * (gb + ab) + 400 * idle_cap + (1u << 20));
+  *gb_out = gb; *ab_out = ab;
+  return KGM_OK;
+}
+
+// Copies the small per-document arrays of a prepared batch (offsets, node ids, ticks).
+int upload_doc_arrays(kgm_ctx *ctx, const kgm_batch *b) {
+  const uint32_t n = b->n_docs;
+  static const uint64_t zero_off[1] = {0};
+  int rc;
+  if ((rc = upload(ctx, ctx->b_gpu_off, n ? b->gpu_off : zero_off, (size_t)n + 1))) return rc;
+  if ((rc = upload(ctx, ctx->b_apps_off, n ? b->apps_off : zero_off, (size_t)n + 1))) return rc;
+  if ((rc = upload(ctx, ctx->b_node, b->doc_node, n))) return rc;
+  if (b->doc_tick && (rc = upload(ctx, ctx->b_tick, b->doc_tick, n))) return rc;
+  return KGM_OK;
+}
+
+int upload_batch(kgm_ctx *ctx, const kgm_batch *b) {
+  uint64_t gb = 0, ab = 0;
+  int rc = prepare_batch(ctx, b, &gb, &ab);
+  if (rc) return rc;
+  CU(cudaEventRecord(ctx->ev[EV_START], ctx->stream));
+  if ((rc = upload(ctx, ctx->b_gpu, b->gpu_csv, gb))) return rc;
+  if ((rc = upload(ctx, ctx->b_apps, b->apps_csv, ab))) return rc;
+  if ((rc = upload_doc_arrays(ctx, b))) return rc;
   ctx->batch_resident = true;
+  return KGM_OK;
+}
+
+// End-to-end path for a large batch in host memory: the batch is cut into up to
+// MAX_CHUNKS runs of documents; the text copy of chunk c+1, the fused kernel of chunk c and
+// the result copy of chunk c-1 run at the same time on three streams.  Every kernel takes
+// the running {lines, bytes} of its predecessors from device memory, so the chunks write
+// one contiguous result, identical to the one-launch result.  Returns 1 if a workspace
+// guess was too small (the caller then runs the plain path on the resident batch).
+int encode_pipelined(kgm_ctx *ctx, const kgm_batch *b, uint32_t chunks, kgm_result *out) {
+  uint64_t gb = 0, ab = 0;
+  int rc = prepare_batch(ctx, b, &gb, &ab);
+  if (rc) return rc;
+  if (!use_fused(ctx) || b->n_docs < chunks) { rc = upload_batch(ctx, b); return rc ? rc : 1; }
+  const uint32_t n = b->n_docs;
+  if ((rc = ensure_workspace(ctx))) return rc;
+  CU(ctx->h_chunk.ensure(MAX_CHUNKS * (2 * sizeof(uint64_t) + CTR_COUNT * sizeof(uint32_t))));
+  CU(ctx->h_lines.ensure(ctx->out_cap + 16));
+  CU(ctx->h_line_off.ensure(((size_t)ctx->desc_cap + 1) * sizeof(uint64_t)));
+  CU(ctx->h_doc_line_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
+  CU(ctx->h_status.ensure(std::max<size_t>(n, 1) * sizeof(int32_t)));
+  uint64_t *h_tot = ctx->h_chunk.as<uint64_t>();
+  uint32_t *h_cnt = reinterpret_cast<uint32_t *>(h_tot + 2 * MAX_CHUNKS);
+
+  CU(cudaEventRecord(ctx->ev[EV_START], ctx->stream));
+  if ((rc = upload_doc_arrays(ctx, b))) return rc;
+  uint64_t *d_tot = ctx->w_totals.as<uint64_t>();
+  uint32_t c0[MAX_CHUNKS + 1];
+  for (uint32_t c = 0; c <= chunks; ++c) c0[c] = (uint32_t)((uint64_t)n * c / chunks);
+  for (uint32_t c = 0; c < chunks; ++c) {
+    const uint64_t g0 = b->gpu_off[c0[c]], g1 = b->gpu_off[c0[c + 1]];
+    const uint64_t a0 = b->apps_off[c0[c]], a1 = b->apps_off[c0[c + 1]];
+    if (g1 > g0) CU(cudaMemcpyAsync(ctx->b_gpu.as<uint8_t>() + g0, b->gpu_csv + g0, g1 - g0, cudaMemcpyHostToDevice, ctx->s_h2d));
+    if (a1 > a0) CU(cudaMemcpyAsync(ctx->b_apps.as<uint8_t>() + a0, b->apps_csv + a0, a1 - a0, cudaMemcpyHostToDevice, ctx->s_h2d));
+    CU(cudaEventRecord(ctx->ev_in[c], ctx->s_h2d));
+  }
+  const BatchDev whole = ctx->batch;
+  const WorkDev wfull = ctx->work;
+  for (uint32_t c = 0; c < chunks; ++c) {
+    const uint32_t lo = c0[c], cn = c0[c + 1] - c0[c];
+    BatchDev &bd = ctx->batch;
+    bd = whole;
+    bd.n_docs = cn; bd.gpu_off = whole.gpu_off + lo; bd.apps_off = whole.apps_off + lo;
+    bd.doc_node = whole.doc_node + lo; bd.doc_tick = whole.doc_tick ? whole.doc_tick + lo : nullptr;
+    WorkDev &wd = ctx->work;
+    wd = wfull;
+    wd.doc_g0 += lo; wd.doc_ng += lo; wd.doc_p0 += lo; wd.doc_np += lo; wd.doc_perr += lo;
+    wd.doc_desc0 += lo; wd.doc_nlines += lo; wd.doc_nbytes += lo; wd.doc_status += lo;
+    wd.doc_line_off += lo; wd.doc_byte_off += lo;
+    wd.totals = d_tot + 2 * (c + 1);
+    ctx->fused.carry = c ? reinterpret_cast<const unsigned long long *>(d_tot + 2 * c) : nullptr;
+    CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_in[c], 0));
+    if (c == 0) CU(cudaEventRecord(ctx->ev[EV_H2D], ctx->stream));
+    rc = launch_pipeline(ctx);                     // cn > 0; sets wd.counters to this launch's set
+    if (rc) { ctx->batch = whole; ctx->work = wfull; ctx->fused.carry = nullptr; return rc; }
+    CU(cudaMemcpyAsync(h_tot + 2 * c, wd.totals, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(h_cnt + CTR_COUNT * c, wd.counters, CTR_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaEventRecord(ctx->ev_k[c], ctx->stream));
+  }
+  ctx->batch = whole;
+  ctx->work = wfull;
+  ctx->fused.carry = nullptr;
+  CU(cudaEventRecord(ctx->ev[EV_ENC], ctx->stream));
+
+  uint64_t lines_done = 0, bytes_done = 0;
+  uint32_t slow = 0;
+  bool overflow = false;
+  for (uint32_t c = 0; c < chunks; ++c) {
+    CU(cudaEventSynchronize(ctx->ev_k[c]));
+    const uint32_t *cnt = h_cnt + CTR_COUNT * c;
+    if (cnt[CTR_OVERFLOW]) {
+      overflow = true;
+      if (cnt[CTR_OVERFLOW] & OVF_GROW) ctx->grow_cap = std::max(ctx->grow_cap * 2, cnt[CTR_GROW] + 64);
+      if (cnt[CTR_OVERFLOW] & OVF_PROW) ctx->prow_cap = std::max(ctx->prow_cap * 2, cnt[CTR_PROW] + 64);
+      if (cnt[CTR_OVERFLOW] & OVF_DESC) ctx->desc_cap = std::max<uint64_t>(ctx->desc_cap * 2, cnt[CTR_DESC] + 64);
+      if (cnt[CTR_OVERFLOW] & OVF_OUT) ctx->out_cap = ctx->out_cap * 2;
+      break;
+    }
+    slow += cnt[CTR_SLOW];
+    const uint64_t nl = h_tot[2 * c], nb = h_tot[2 * c + 1];
+    if (nb > bytes_done)
+      CU(cudaMemcpyAsync(ctx->h_lines.as<uint8_t>() + bytes_done, ctx->work.out + bytes_done, nb - bytes_done,
+                         cudaMemcpyDeviceToHost, ctx->s_d2h));
+    if (nl > lines_done)
+      CU(cudaMemcpyAsync(ctx->h_line_off.as<uint64_t>() + lines_done, ctx->work.line_off + lines_done,
+                         (nl - lines_done) * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->s_d2h));
+    lines_done = nl; bytes_done = nb;
+  }
+  if (overflow) {
+    CU(cudaStreamSynchronize(ctx->s_h2d));
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaStreamSynchronize(ctx->s_d2h));
+    ctx->batch_resident = true;                    // every text byte has been copied
+    return 1;
+  }
+  CU(cudaMemcpyAsync(ctx->h_doc_line_off.p, ctx->work.doc_line_off, ((size_t)n + 1) * sizeof(uint64_t),
+                     cudaMemcpyDeviceToHost, ctx->s_d2h));
+  CU(cudaMemcpyAsync(ctx->h_status.p, ctx->work.doc_status, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                     ctx->s_d2h));
+  CU(cudaEventRecord(ctx->ev[EV_D2H], ctx->s_d2h));
+  CU(cudaStreamSynchronize(ctx->s_d2h));
+  ctx->h_line_off.as<uint64_t>()[lines_done] = bytes_done;
+  ctx->n_lines = lines_done; ctx->n_bytes = bytes_done;
+  ctx->slow_docs = slow;
+  ctx->batch_resident = true;
+  ctx->have_result = true;
+  ctx->last_chunks = chunks;
+  out->lines = ctx->h_lines.as<uint8_t>();
+  out->n_bytes = bytes_done;
+  out->line_off = ctx->h_line_off.as<uint64_t>();
+  out->n_lines = lines_done;
+  out->doc_line_off = ctx->h_doc_line_off.as<uint64_t>();
+  out->doc_status = ctx->h_status.as<int32_t>();
+  out->n_docs = n;
   return KGM_OK;
 }
 
@@ -485,6 +629,12 @@ int kgm_create(kgm_ctx **out, int device) {
   cudaError_t e = cudaSetDevice(device);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   for (int i = 0; i < EV_COUNT && e == cudaSuccess; ++i) e = cudaEventCreate(&ctx->ev[i]);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->s_h2d, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->s_d2h, cudaStreamNonBlocking);
+  for (int i = 0; i < MAX_CHUNKS && e == cudaSuccess; ++i) {
+    e = cudaEventCreateWithFlags(&ctx->ev_in[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_k[i], cudaEventDisableTiming);
+  }
   cudaDeviceProp prop;
   if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
   if (e != cudaSuccess) { kgm_destroy(ctx); cudaGetLastError(); return KGM_E_CUDA; }
@@ -513,9 +663,16 @@ void kgm_destroy(kgm_ctx *ctx) {
                    &ctx->f_node_fast, &ctx->f_tb_off, &ctx->f_tb_len, &ctx->f_tb_pool, &ctx->f_pid16,
                    &ctx->f_vis_hash2};
   for (DevBuf *b : dev) b->release();
-  HostBuf *host[] = {&ctx->h_small, &ctx->h_lines, &ctx->h_line_off, &ctx->h_doc_line_off, &ctx->h_status};
+  HostBuf *host[] = {&ctx->h_small, &ctx->h_lines, &ctx->h_line_off, &ctx->h_doc_line_off, &ctx->h_status,
+                     &ctx->h_chunk};
   for (HostBuf *b : host) b->release();
   for (int i = 0; i < EV_COUNT; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+  for (int i = 0; i < MAX_CHUNKS; ++i) {
+    if (ctx->ev_in[i]) cudaEventDestroy(ctx->ev_in[i]);
+    if (ctx->ev_k[i]) cudaEventDestroy(ctx->ev_k[i]);
+  }
+  if (ctx->s_h2d) cudaStreamDestroy(ctx->s_h2d);
+  if (ctx->s_d2h) cudaStreamDestroy(ctx->s_d2h);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   cudaGetLastError();
   delete ctx;
@@ -750,6 +907,34 @@ int kgm_fetch_result(kgm_ctx *ctx, kgm_result *out) {
 int kgm_encode_batch(kgm_ctx *ctx, const kgm_batch *b, int want_host_copy, kgm_result *out) {
   if (!ctx || !out) return KGM_E_INVALID;
   CU(cudaSetDevice(ctx->device));
+  ctx->last_chunks = 1;
+  // large host batches: chunked, copies overlapped with the fused kernel
+  if (want_host_copy && b && ctx->fleet_loaded && ctx->pipeline != KGM_PIPELINE_STAGED && b->n_docs >= 1024 &&
+      b->gpu_off && b->apps_off && b->doc_node &&
+      b->gpu_off[b->n_docs] + b->apps_off[b->n_docs] >= (4u << 20)) {
+    const uint64_t total = b->gpu_off[b->n_docs] + b->apps_off[b->n_docs];
+    const uint32_t chunks = (uint32_t)std::min<uint64_t>(MAX_CHUNKS, std::max<uint64_t>(2, total / (2u << 20)));
+    int rc = encode_pipelined(ctx, b, chunks, out);
+    if (rc <= 0) {
+      if (rc == KGM_OK) {
+        ctx->timing = kgm_timing{};
+        cudaEventElapsedTime(&ctx->timing.total_ms, ctx->ev[EV_START], ctx->ev[EV_D2H]);   // copies and kernels overlap
+        ctx->timing.launches = chunks;
+        ctx->timing.fused = 1;
+        ctx->timing.slow_docs = ctx->slow_docs;
+        cudaGetLastError();
+      }
+      return rc;
+    }
+    // a workspace guess was too small (or the batch does not fit the fused kernel): the
+    // batch is resident now, run it the plain way
+    rc = run_resident(ctx, false);
+    if (rc) return rc;
+    rc = fetch(ctx, out);
+    if (rc) return rc;
+    fill_timing(ctx, false, true);
+    return KGM_OK;
+  }
   int rc = upload_batch(ctx, b);          // records EV_START, copies are asynchronous
   if (rc) return rc;
   rc = run_resident(ctx, true);

@@ -140,10 +140,35 @@ KGM_HD void shortest_decimal(uint64_t bits, uint64_t *digits, int *exp10) {
   *exp10 = e10 + removed;
 }
 
-KGM_HD int decimal_length17(uint64_t v) {
-  int n = 1;
-  while (v >= 10) { v /= 10; ++n; }
-  return n;
+KGM_HD int decimal_length17(uint64_t v) {            // v < 10^17
+  if (v >= 10000000000000000ull) return 17;
+  if (v >= 1000000000000000ull) return 16;
+  if (v >= 100000000000000ull) return 15;
+  if (v >= 10000000000000ull) return 14;
+  if (v >= 1000000000000ull) return 13;
+  if (v >= 100000000000ull) return 12;
+  if (v >= 10000000000ull) return 11;
+  if (v >= 1000000000ull) return 10;
+  const uint32_t w = (uint32_t)v;
+  if (w >= 100000000u) return 9;
+  if (w >= 10000000u) return 8;
+  if (w >= 1000000u) return 7;
+  if (w >= 100000u) return 6;
+  if (w >= 10000u) return 5;
+  if (w >= 1000u) return 4;
+  if (w >= 100u) return 3;
+  if (w >= 10u) return 2;
+  return 1;
+}
+
+// The nd decimal digits of dg (< 10^17), most significant first, using 32-bit arithmetic
+// for all but one division.
+KGM_HD void decimal_digits17(uint64_t dg, int nd, unsigned char *d) {
+  uint32_t hi = (uint32_t)(dg / 100000000ull);       // < 10^9
+  uint32_t lo = (uint32_t)(dg - (uint64_t)hi * 100000000ull);
+  int i = nd - 1;
+  for (int k = 0; k < 8 && i >= 0; ++k, --i) { const uint32_t q = lo / 10u; d[i] = (unsigned char)('0' + (lo - q * 10u)); lo = q; }
+  for (; i >= 0; --i) { const uint32_t q = hi / 10u; d[i] = (unsigned char)('0' + (hi - q * 10u)); hi = q; }
 }
 
 // repr(float) for a finite double >= 0.  Writes at most 24 bytes, returns the length.
@@ -157,7 +182,7 @@ KGM_HD int float_repr(double x, unsigned char *out) {
   shortest_decimal(bits, &dg, &e10);
   const int nd = decimal_length17(dg);
   unsigned char d[17];
-  for (int i = nd - 1; i >= 0; --i) { d[i] = (unsigned char)('0' + dg % 10); dg /= 10; }
+  decimal_digits17(dg, nd, d);
   const int decpt = nd + e10;          // value = 0.d1..dn * 10^decpt
   int n = 0;
   if (decpt > 16 || decpt < -3) {      // exponent form: d[.ddd]e+XX

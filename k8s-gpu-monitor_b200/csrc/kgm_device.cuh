@@ -84,6 +84,8 @@ struct FusedParams {
   unsigned long long *ticket;    // monotonic document ticket counter
   unsigned long long *scan_state;   // 2 words per document
   uint32_t *next_counters;       // the counter set of the next launch (zeroed by this one)
+  const unsigned long long *carry;  // {lines, bytes} emitted by earlier launches of the same batch
+                                    // (chunked end-to-end path), or null
 };
 
 void launch_poll(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P, int blocks,

@@ -28,7 +28,11 @@ KGM_HD uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t s) {       // ((hi:l
 #endif
 }
 KGM_HD uint32_t low_mask(uint32_t nbytes) {                            // nbytes in 0..4
+#if defined(__CUDA_ARCH__)
+  return __funnelshift_rc(0xffffffffu, 0u, 32u - 8u * nbytes);        // clamps the shift at 32
+#else
   return nbytes >= 4 ? 0xffffffffu : ((1u << (8 * nbytes)) - 1u);
+#endif
 }
 // 4 bytes starting at byte offset `o` of the word array W (reads W[o/4] and W[o/4+1])
 KGM_HD uint32_t load4(const uint32_t *W, uint32_t o) {
@@ -63,15 +67,23 @@ KGM_HD uint64_t key_hash_words(const uint32_t *k, uint32_t len) {
   }
   return hash_mix(((uint64_t)a << 32) | b);
 }
-// key bytes [o, o+len) of W -> k[KEY_WORDS], zero padded
+// key bytes [o, o+len) of W -> k[KEY_WORDS], zero padded (len <= 4*KEY_WORDS)
 KGM_HD void load_key(const uint32_t *W, uint32_t o, uint32_t len, uint32_t *k) {
+  const uint32_t *p = W + (o >> 2);
+  const uint32_t s = 8u * (o & 3u);
+  uint32_t prev = p[0];
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
   for (int i = 0; i < KEY_WORDS; ++i) {
     const uint32_t b = 4u * i;
-    uint32_t w = b < len ? load4(W, o + b) : 0u;
-    if (b + 4 > len) w &= low_mask(len > b ? len - b : 0u);
+    uint32_t w = 0;
+    if (b < len) {
+      const uint32_t cur = p[i + 1];
+      w = funnel_r(prev, cur, s);
+      prev = cur;
+      if (b + 4 > len) w &= low_mask(len - b);
+    }
     k[i] = w;
   }
 }
@@ -100,6 +112,7 @@ struct alignas(8) GRec {                            // one --query-gpu row (gpu.
   uint8_t flen;
   uint8_t pad[3];
   uint32_t line_len;                                // node_gpu line incl. '\n'
+  uint32_t keyw[KEY_WORDS];                         // the key, word aligned and zero padded
 };
 
 constexpr int NAME_RUNS = 4;
@@ -125,7 +138,7 @@ struct RowShape {
   bool irregular;
 };
 
-// cells of a row [s, e): `want` commas are recorded (more are counted, not stored)
+// cells of a row [s, e): the first WANT commas are recorded (more are counted, not stored)
 template <int WANT>
 KGM_HD void scan_commas(const uint32_t *W, uint32_t s, uint32_t e, RowShape &r) {
   r.ncommas = 0;
@@ -134,19 +147,14 @@ KGM_HD void scan_commas(const uint32_t *W, uint32_t s, uint32_t e, RowShape &r) 
 #pragma unroll
 #endif
   for (int i = 0; i < 6; ++i) r.comma[i] = 0;
-  uint32_t bad = 0;
-  for (uint32_t wi = s >> 2; wi <= (e - 1) >> 2 && s < e; ++wi) {
-    uint32_t w = W[wi];
-    const uint32_t base = wi << 2;
-    // bytes outside [s, e) are replaced by 'a'
-    uint32_t keep = 0xffffffffu;
-    if (base < s) keep &= ~low_mask(s - base);
-    if (base + 4 > e) keep &= low_mask(e - base);
-    w = (w & keep) | (0x61616161u & ~keep);
-    bad |= w & 0x80808080u;
-    const uint32_t w7 = w & 0x7f7f7f7fu;
-    bad |= lt_mask(w7, 0x20202020u) | eq_mask(w7, 0x22222222u) | eq_mask(w7, 0x7f7f7f7fu);
-    uint32_t cm = eq_mask(w7, 0x2c2c2c2cu);
+  if (s >= e) return;
+  uint32_t bad = 0, n = 0;
+  auto word = [&](uint32_t wi, uint32_t w) {
+    // any byte >= 0x80, < 0x20 or == '"' makes the row irregular ("any" tests, not positions)
+    const uint32_t q = w ^ 0x22222222u;
+    bad |= w | ((w - 0x20202020u) & ~w) | ((q - 0x01010101u) & ~q);
+    const uint32_t c = (w & 0x7f7f7f7fu) ^ 0x2c2c2c2cu;              // exact ',' positions
+    uint32_t cm = ~((c + 0x7f7f7f7fu) | w) & 0x80808080u;
     while (cm) {
 #if defined(__CUDA_ARCH__)
       const uint32_t bit = __ffs(cm) - 1;
@@ -154,16 +162,24 @@ KGM_HD void scan_commas(const uint32_t *W, uint32_t s, uint32_t e, RowShape &r) 
       const uint32_t bit = __builtin_ctz(cm);
 #endif
       cm &= cm - 1;
-      const uint32_t pos = base + (bit >> 3);
-      if (r.ncommas < (uint32_t)WANT) {
+      const uint32_t pos = (wi << 2) + (bit >> 3);
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-        for (int i = 0; i < WANT; ++i) if (r.ncommas == (uint32_t)i) r.comma[i] = (uint16_t)pos;
-      }
-      ++r.ncommas;
+      for (int i = 0; i < WANT; ++i) if (n == (uint32_t)i) r.comma[i] = (uint16_t)pos;
+      ++n;
     }
-  }
+  };
+  // bytes outside [s, e) in the first and last word are replaced by 'a'
+  const uint32_t a = s >> 2, z = (e - 1) >> 2;
+  uint32_t keep_a = ~low_mask(s - (a << 2));
+  const uint32_t keep_z = low_mask(e - (z << 2));
+  if (a == z) keep_a &= keep_z;
+  word(a, (W[a] & keep_a) | (0x61616161u & ~keep_a));
+  for (uint32_t wi = a + 1; wi < z; ++wi) word(wi, W[wi]);
+  if (z > a) word(z, (W[z] & keep_z) | (0x61616161u & ~keep_z));
+  bad &= 0x80808080u;
+  r.ncommas = n;
   r.irregular = bad != 0;
 }
 
@@ -220,9 +236,8 @@ KGM_HD bool parse_gpu_row(const uint32_t *W, uint32_t s, uint32_t e, uint32_t no
   while (k < c0 && load1(W, k) == 32u) ++k;
   if (c0 - k > 4u * KEY_WORDS) return false;
   g.key.off = (uint16_t)k; g.key.len = (uint16_t)(c0 - k);
-  uint32_t kw[KEY_WORDS];
-  load_key(W, k, c0 - k, kw);
-  g.hash = key_hash_words(kw, c0 - k);
+  load_key(W, k, c0 - k, g.keyw);
+  g.hash = key_hash_words(g.keyw, c0 - k);
   if (!digit_run(W, c0 + 1, c1, g.util)) return false;
   if (!digit_run(W, c2 + 1, c3, g.mt)) return false;
   if (!digit_run(W, c3 + 1, c4, g.mu)) return false;
@@ -322,71 +337,56 @@ KGM_HD uint32_t name_len(const PRec &p) {
 }
 
 // ---- line writer ---------------------------------------------------------------------------
-// Appends byte runs to an output stream in shared memory with aligned 32-bit stores.  A
-// line's first bytes up to the next word boundary and its last partial word are written
-// byte-wise by the caller, because those words are shared with the neighbouring lines
-// (which other lanes write at the same time).
-struct LineWriter {
-  uint32_t *dst;      // next full word
-  uint32_t acc;       // pending bytes: low `fill` bytes valid, the rest zero
-  uint32_t fill;      // 0..3
-
-  // bytes [so, so+n) of the word array B.  Reads up to 2 words past and 1 word before the run.
-  KGM_HDM void append(const uint32_t *B, uint32_t so, uint32_t n) {
-    if (n == 0) return;
-    const uint32_t sh = so & 3u;
-    const uint32_t *p = B + (so >> 2);
-    uint32_t s;
-    if (sh >= fill) { s = 8u * (sh - fill); } else { s = 8u * (sh + 4u - fill); --p; }
-    const uint32_t total = fill + n, full = total >> 2, rem = total & 3u;
-    uint32_t prev = p[0];
-    if (full) {
-      uint32_t cur = p[1];
-      dst[0] = (funnel_r(prev, cur, s) & ~low_mask(fill)) | acc;
-      prev = cur;
-      for (uint32_t j = 1; j < full; ++j) {
-        cur = p[j + 1];
-        dst[j] = funnel_r(prev, cur, s);
-        prev = cur;
-      }
-      dst += full;
-      acc = rem ? (funnel_r(prev, p[full + 1], s) & low_mask(rem)) : 0u;
-    } else {
-      acc = ((funnel_r(prev, p[1], s) & ~low_mask(fill)) | acc) & low_mask(rem);
-    }
-    fill = rem;
+// Copies the byte run [so, so+n) of the word array B to byte offset `o` of the same array:
+// byte stores up to the next word boundary of the destination, aligned 32-bit stores
+// (source realigned with a funnel shift) for the body, byte stores for the tail.  Lines of
+// neighbouring lanes meet inside a word, so only byte stores ever touch a shared word.
+// Reads up to 2 words past the run.
+KGM_HD void copy_run(uint32_t *B, uint32_t o, uint32_t so, uint32_t n) {
+  uint8_t *Bb = reinterpret_cast<uint8_t *>(B);
+  uint32_t h = (4u - (o & 3u)) & 3u;
+  if (h > n) h = n;
+  if (h > 0) Bb[o] = Bb[so];
+  if (h > 1) Bb[o + 1] = Bb[so + 1];
+  if (h > 2) Bb[o + 2] = Bb[so + 2];
+  o += h; so += h; n -= h;
+  const uint32_t full = n >> 2, t = n & 3u;
+  const uint32_t *p = B + (so >> 2);
+  const uint32_t s = 8u * (so & 3u);
+  uint32_t *d = B + (o >> 2);
+  uint32_t prev = p[0];
+  for (uint32_t j = 0; j < full; ++j) {
+    const uint32_t cur = p[j + 1];
+    d[j] = funnel_r(prev, cur, s);
+    prev = cur;
   }
-  KGM_HDM void put_byte(uint32_t c) {
-    acc |= c << (8u * fill);
-    if (++fill == 4u) { *dst++ = acc; acc = 0; fill = 0; }
+  if (t) {
+    const uint32_t w = funnel_r(prev, p[full + 1], s);
+    uint8_t *tail = reinterpret_cast<uint8_t *>(d + full);
+    tail[0] = (uint8_t)w;
+    if (t > 1) tail[1] = (uint8_t)(w >> 8);
+    if (t > 2) tail[2] = (uint8_t)(w >> 16);
   }
-};
+}
 
 struct Seg { uint32_t off; uint32_t len; };          // byte offset into the warp's word array
 
 constexpr int MAX_SEGS = 19;
 
 // Writes the line made of segs[0..MAX_SEGS) + '\n' at byte offset `o` of the word array
-// `B` (sources and destination live in the same array: the warp's shared memory).
+// `B` (sources and destination live in the same array: the CTA's shared memory).
 // Returns the number of bytes written.
-KGM_HD uint32_t write_line(uint32_t *B, uint32_t o, Seg *segs) {
-  uint8_t *bytes = reinterpret_cast<uint8_t *>(B);
-  const uint32_t k = (4u - (o & 3u)) & 3u;          // bytes up to the next word boundary
-  // head bytes come from the first segment (>= 13 bytes for every line kind)
-  for (uint32_t i = 0; i < k; ++i) bytes[o + i] = (uint8_t)load1(B, segs[0].off + i);
-  segs[0].off += k; segs[0].len -= k;
-  const uint32_t written = k;
-  LineWriter w{B + ((o + k) >> 2), 0u, 0u};
-  uint32_t body = 0;
+KGM_HD uint32_t write_line(uint32_t *B, uint32_t o, const Seg *segs) {
+  uint32_t at = o;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-  for (int i = 0; i < MAX_SEGS; ++i) { w.append(B, segs[i].off, segs[i].len); body += segs[i].len; }
-  w.put_byte(10u);
-  ++body;
-  uint8_t *tail = reinterpret_cast<uint8_t *>(w.dst);
-  for (uint32_t i = 0; i < w.fill; ++i) tail[i] = (uint8_t)(w.acc >> (8u * i));
-  return written + body;
+  for (int i = 0; i < MAX_SEGS; ++i) {
+    if (segs[i].len) copy_run(B, at, segs[i].off, segs[i].len);
+    at += segs[i].len;
+  }
+  reinterpret_cast<uint8_t *>(B)[at++] = 10u;
+  return at - o;
 }
 
 // ---- segment lists of the three line kinds ----------------------------------------------------

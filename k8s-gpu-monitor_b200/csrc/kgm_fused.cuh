@@ -59,21 +59,27 @@ __device__ __forceinline__ uint64_t warp_sum64(uint64_t v) {
   return v;
 }
 
-// Publishes the document's (lines, bytes) and returns its exclusive prefix over all
-// earlier documents.  Every lane of the warp calls it.
-__device__ void doc_exclusive_scan(const FusedParams &P, uint32_t d, uint64_t nl, uint64_t nb,
-                                   uint64_t *line0, uint64_t *byte0) {
+// Device-wide exclusive scan over documents, decoupled look-back.  scan_publish makes the
+// document's (lines, bytes) visible as an aggregate; scan_resolve, called later, sums the
+// predecessors' aggregates back to the nearest inclusive prefix and publishes the
+// document's own inclusive prefix.  Between the two calls the warp composes its lines, so
+// that the predecessors it has to wait for have normally published by then.
+__device__ __forceinline__ void scan_publish(const FusedParams &P, uint32_t d, uint64_t nl, uint64_t nb) {
+  if (lane_id() != 0) return;
+  unsigned long long *st = P.scan_state + 2ull * d;
+  const uint64_t tag = st_tag(P.epoch, d == 0 ? ST_INC : ST_AGG);
+  st_relaxed(st + 1, tag | nb);
+  st_release(st, tag | nl);
+}
+
+__device__ void scan_resolve(const FusedParams &P, uint32_t d, uint64_t nl, uint64_t nb, uint64_t *line0,
+                             uint64_t *byte0) {
   const uint32_t l = lane_id();
   unsigned long long *st = P.scan_state;
   const uint64_t agg = st_tag(P.epoch, ST_AGG), inc = st_tag(P.epoch, ST_INC);
   const uint64_t VAL = (1ull << 46) - 1ull;
   uint64_t ex_l = 0, ex_b = 0;
-  if (d == 0) {
-    if (l == 0) { st_relaxed(st + 1, inc | nb); st_release(st, inc | nl); }
-    *line0 = 0; *byte0 = 0;
-    return;
-  }
-  if (l == 0) { st_relaxed(st + 2ull * d + 1, agg | nb); st_release(st + 2ull * d, agg | nl); }
+  if (d == 0) { *line0 = 0; *byte0 = 0; return; }
   long long j = (long long)d - 1;
   for (;;) {
     const long long idx = j - (long long)l;
@@ -87,7 +93,7 @@ __device__ void doc_exclusive_scan(const FusedParams &P, uint32_t d, uint64_t nl
           const uint64_t w1 = ld_relaxed(st + 2ull * idx + 1);
           if ((w1 & ~VAL) == t0) { vl = w0 & VAL; vb = w1 & VAL; is_inc = t0 == inc; break; }
         }
-        __nanosleep(40);
+        __nanosleep(100);
       }
     }
     const uint32_t incs = __ballot_sync(FULL, is_inc);
@@ -120,6 +126,12 @@ __device__ __forceinline__ void load_window(const uint8_t *text, uint64_t lo, ui
     *reinterpret_cast<uint4 *>(dst + i) = __ldg(reinterpret_cast<const uint4 *>(text + w0 + i));
   *s = (uint32_t)(lo - w0);
   *e = *s + (uint32_t)(hi - lo);
+  __syncwarp();
+  // bytes of the neighbouring documents (before s, after e) and the slack that word-wise
+  // readers may touch are zeroed: no line feed, comma or digit outside the text
+  if (lane_id() < *s) dst[lane_id()] = 0;
+  dst[*e + lane_id()] = 0;
+  if (lane_id() < 16) dst[*e + 32u + lane_id()] = 0;
 }
 
 // Line feeds of the window bytes [s, e) -> row_start[0..nrows]; row r = [row_start[r],
@@ -129,34 +141,29 @@ __device__ bool find_rows(const uint32_t *T, uint32_t s, uint32_t e, uint16_t *r
                           uint32_t *nrows) {
   const uint32_t l = lane_id();
   uint32_t running = 0;
-  for (uint32_t it = s & ~15u; it < e; it += 512u) {
-    const uint32_t pos = it + 16u * l;
-    uint32_t m[4] = {0, 0, 0, 0};
-    if (pos < e) {
-      const uint4 v = *reinterpret_cast<const uint4 *>(T + (pos >> 2));
-      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  for (uint32_t it = s & ~31u; it < e; it += 1024u) {
+    const uint32_t pos = it + 32u * l;              // this lane's 32 bytes = 8 words
+    uint32_t m[8];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < 8; ++k) m[k] = 0;
+    if (pos < e) {
+      const uint4 v0 = *reinterpret_cast<const uint4 *>(T + (pos >> 2));
+      const uint4 v1 = *reinterpret_cast<const uint4 *>(T + (pos >> 2) + 4);
+      const uint32_t w[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
         const uint32_t z = w[k] ^ 0x0a0a0a0au;                         // exact zero-byte test
         m[k] = ~(((z & 0x7f7f7f7fu) + 0x7f7f7f7fu) | z) & 0x80808080u;
       }
-      if (pos < s || pos + 16u > e) {                                  // boundary chunk: drop outside bytes
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const uint32_t b = pos + 4u * k;
-          uint32_t keep = 0xffffffffu;
-          if (b < s) keep &= ~low_mask(min(s - b, 4u));
-          if (b + 4u > e) keep &= low_mask(e > b ? e - b : 0u);
-          m[k] &= keep;
-        }
-      }
     }
-    const uint32_t c = __popc(m[0]) + __popc(m[1]) + __popc(m[2]) + __popc(m[3]);
+    uint32_t c = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) c += __popc(m[k]);
     const uint32_t incl = warp_incl_scan(c);
     uint32_t idx = running + incl - c;
     if (c) {
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
+      for (int k = 0; k < 8; ++k) {
         uint32_t mk = m[k];
         while (mk) {
           const uint32_t bit = __ffs(mk) - 1;
@@ -252,11 +259,9 @@ __device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, cons
         uint32_t sid = NONE32;
         for (uint32_t j = 0; j < ng && sid == NONE32; ++j) {
           if (grec[j].hash == kh && grec[j].key.len == klen) {
-            uint32_t gk[KEY_WORDS];
-            load_key(TG, grec[j].key.off, klen, gk);
             bool eq = true;
 #pragma unroll
-            for (int i = 0; i < KEY_WORDS; ++i) eq &= gk[i] == kw[i];
+            for (int i = 0; i < KEY_WORDS; ++i) eq &= grec[j].keyw[i] == kw[i];
             if (eq) sid = j;
           }
         }
@@ -376,57 +381,105 @@ __device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, cons
   return true;
 }
 
-// Writes the planned lines of a regular document: stage in shared memory, 16-byte stores out.
-__device__ void fast_emit(const FusedParams &P, const WorkDev &w, uint32_t *S, uint8_t *Sb,
-                          const WarpSlice &ws, uint32_t ng, uint32_t nl, uint64_t line0, uint64_t byte0) {
+// Writes the planned lines of a regular document.  Lines are composed into the stage from
+// its start (whatever the global alignment will be); the copy to global memory realigns
+// them: byte stores up to the first 16-byte boundary of the destination, then 16-byte
+// stores assembled from five shared-memory words each, byte stores for the tail.  The
+// document's position in the output is only needed for that copy, so the look-back that
+// yields it (scan_resolve) runs after the first round of lines has been composed.
+__device__ void fast_emit(const FusedParams &P, const WorkDev &w, uint32_t *S, uint8_t *Sb, const WarpSlice &ws,
+                          uint32_t d, uint32_t n_docs, uint32_t nl, uint32_t nb) {
   const uint32_t l = lane_id();
   const TbHeader &hd = *reinterpret_cast<const TbHeader *>(Sb + ws.tb);
   const TbCont *tc = reinterpret_cast<const TbCont *>(Sb + ws.tb + sizeof(TbHeader));
   const GRec *grec = reinterpret_cast<const GRec *>(Sb + ws.grec);
   const PRec *prec = reinterpret_cast<const PRec *>(Sb + ws.prec);
   const uint32_t *plan = S + (ws.plan >> 2), *loff = S + (ws.loff >> 2);
-  (void)ng;
+  // rounds of equal size: as few as the stage allows, at most 32 lines each
+  uint32_t rounds = max((nl + 31u) / 32u, (nb + P.stage_bytes - 64u - 1u) / (P.stage_bytes - 64u));
+  uint32_t per = rounds ? (nl + rounds - 1u) / rounds : 0u;
+  uint64_t line0 = 0, byte0 = 0;
+  bool resolved = false, fits_out = true;
   uint32_t i0 = 0;
-  while (i0 < nl) {
-    const uint32_t r_lo = loff[i0];
-    const uint32_t pad = (uint32_t)((byte0 + r_lo) & 15ull);
-    // as many of the next 32 lines as the stage holds
-    const uint32_t cand = i0 + l + 1;
-    const bool fits = cand <= nl && pad + (loff[min(cand, nl)] - r_lo) + 16u <= P.stage_bytes;
-    const uint32_t take = __popc(__ballot_sync(FULL, fits));
-    if (take == 0) return;                          // cannot happen: the stage holds any single line
-    const uint32_t i1 = i0 + take, i = i0 + l;
-    if (i < i1) {
-      const uint32_t pl = plan[i], kind = pl >> 30;
-      Seg segs[MAX_SEGS];
-      if (kind == KIND_NODE) {
-        const uint32_t r = pl & 0xffffu;
-        node_segs(segs, 0u, ws.tb, hd, ws.tg, grec[r], ws.grec + r * (uint32_t)sizeof(GRec) + (uint32_t)offsetof(GRec, fstr), r);
-      } else if (kind == KIND_BUSY) {
-        const PRec &p = prec[pl & 0x3fffffffu];
-        busy_segs(segs, 0u, ws.tb, tc[p.crank], ws.tg, ws.ta, p, grec[p.sid], p.sid);
-      } else {
-        const uint32_t sid = pl & 0xfffu;
-        idle_segs(segs, 0u, ws.tb, tc[(pl >> 12) & 0x3ffffu], sid == IDLE_NONE ? NONE32 : sid);
+  do {
+    // the next `per` lines, fewer if their bytes exceed the stage
+    uint32_t i1 = min(nl, i0 + per);
+    uint32_t r_lo = 0;
+    if (nl) {
+      r_lo = loff[i0];
+      const uint32_t cand = i0 + l + 1;
+      const bool fits = cand <= i1 && loff[cand] - r_lo + 64u <= P.stage_bytes;
+      i1 = i0 + __popc(__ballot_sync(FULL, fits));
+      if (i1 == i0) {                               // cannot happen: the stage holds any single line
+        if (!resolved) scan_resolve(P, d, nl, nb, &line0, &byte0);
+        return;
       }
-      write_line(S, ws.stage + pad + (loff[i] - r_lo), segs);
-      w.line_off[line0 + i] = byte0 + loff[i];
+      const uint32_t i = i0 + l;
+      if (i < i1) {
+        const uint32_t pl = plan[i], kind = pl >> 30;
+        Seg segs[MAX_SEGS];
+        if (kind == KIND_NODE) {
+          const uint32_t r = pl & 0xffffu;
+          node_segs(segs, 0u, ws.tb, hd, ws.tg, grec[r],
+                    ws.grec + r * (uint32_t)sizeof(GRec) + (uint32_t)offsetof(GRec, fstr), r);
+        } else if (kind == KIND_BUSY) {
+          const PRec &p = prec[pl & 0x3fffffffu];
+          busy_segs(segs, 0u, ws.tb, tc[p.crank], ws.tg, ws.ta, p, grec[p.sid], p.sid);
+        } else {
+          const uint32_t sid = pl & 0xfffu;
+          idle_segs(segs, 0u, ws.tb, tc[(pl >> 12) & 0x3ffffu], sid == IDLE_NONE ? NONE32 : sid);
+        }
+        write_line(S, ws.stage + (loff[i] - r_lo), segs);
+      }
+    }
+    if (!resolved) {
+      scan_resolve(P, d, nl, nb, &line0, &byte0);
+      if (P.carry) { line0 += P.carry[0]; byte0 += P.carry[1]; }
+      resolved = true;
+      fits_out = byte0 + nb <= w.out_cap && line0 + nl <= w.desc_cap;
+      if (l == 0) {
+        w.doc_line_off[d] = line0;
+        w.doc_byte_off[d] = byte0;
+        w.doc_status[d] = 0; w.doc_nlines[d] = nl; w.doc_nbytes[d] = nb;
+        if (d + 1 == n_docs) {
+          w.doc_line_off[n_docs] = line0 + nl;
+          w.doc_byte_off[n_docs] = byte0 + nb;
+          w.totals[0] = line0 + nl;
+          w.totals[1] = byte0 + nb;
+          w.line_off[min(line0 + nl, (uint64_t)w.desc_cap)] = byte0 + nb;
+        }
+        if (!fits_out)
+          atomicOr(w.counters + CTR_OVERFLOW, (byte0 + nb > w.out_cap ? OVF_OUT : 0u) |
+                                                  (line0 + nl > w.desc_cap ? OVF_DESC : 0u));
+      }
     }
     __syncwarp();
-    // stage -> global: byte stores up to the first 16-byte boundary and after the last one
+    if (!fits_out || nl == 0) return;
+    if (i0 + l < i1) w.line_off[line0 + i0 + l] = byte0 + loff[i0 + l];
+    // stage -> global
     const uint32_t nbytes = loff[i1] - r_lo;
     uint8_t *g = w.out + byte0 + r_lo;
-    const uint8_t *st = Sb + ws.stage + pad;
-    const uint32_t head = min(nbytes, (16u - pad) & 15u);
+    const uint8_t *st = Sb + ws.stage;
+    const uint32_t head = min(nbytes, (uint32_t)((16u - ((byte0 + r_lo) & 15ull)) & 15u));
     if (l < head) g[l] = st[l];
     const uint32_t nvec = (nbytes - head) >> 4;
-    for (uint32_t v = l; v < nvec; v += 32)
-      *reinterpret_cast<uint4 *>(g + head + 16u * v) = *reinterpret_cast<const uint4 *>(st + head + 16u * v);
+    {
+      const uint32_t *sw = S + ((ws.stage + head) >> 2);     // stage word holding byte `head`
+      const uint32_t sh = 8u * (head & 3u);
+      for (uint32_t v = l; v < nvec; v += 32) {
+        const uint32_t *q = sw + 4u * v;
+        const uint32_t a0 = q[0], a1 = q[1], a2 = q[2], a3 = q[3], a4 = q[4];
+        uint4 o;
+        o.x = __funnelshift_r(a0, a1, sh); o.y = __funnelshift_r(a1, a2, sh);
+        o.z = __funnelshift_r(a2, a3, sh); o.w = __funnelshift_r(a3, a4, sh);
+        *reinterpret_cast<uint4 *>(g + head + 16u * v) = o;
+      }
+    }
     const uint32_t done = head + 16u * nvec;
     if (l < nbytes - done) g[done + l] = st[done + l];
     __syncwarp();
     i0 = i1;
-  }
+  } while (i0 < nl);
 }
 
 // ---- generic path for one document (device functions of the staged kernels) -------------------
@@ -505,16 +558,21 @@ __global__ void __launch_bounds__(POLL_THREADS, 2) k_poll(BatchDev b, FleetDev f
     uint32_t ng = 0, nl = 0, nb = 0;
     const bool fastdoc = P.allow_fast && fast_plan(d, b, f, P, S, Sb, ws, &ng, &nl, &nb);
     __syncwarp();
-    if (!fastdoc) {
-      slow_plan(d, b, f, w, S + (ws.stage >> 2), &nl, &nb);
-      if (l == 0) atomicAdd(w.counters + CTR_SLOW, 1u);
+    if (fastdoc) {
+      scan_publish(P, d, nl, nb);
+      fast_emit(P, w, S, Sb, ws, d, b.n_docs, nl, nb);
+      __syncwarp();
+      continue;
     }
+    slow_plan(d, b, f, w, S + (ws.stage >> 2), &nl, &nb);
+    if (l == 0) atomicAdd(w.counters + CTR_SLOW, 1u);
+    scan_publish(P, d, nl, nb);
     uint64_t line0, byte0;
-    doc_exclusive_scan(P, d, nl, nb, &line0, &byte0);
+    scan_resolve(P, d, nl, nb, &line0, &byte0);
+    if (P.carry) { line0 += P.carry[0]; byte0 += P.carry[1]; }
     if (l == 0) {
       w.doc_line_off[d] = line0;
       w.doc_byte_off[d] = byte0;
-      if (fastdoc) { w.doc_status[d] = 0; w.doc_nlines[d] = nl; w.doc_nbytes[d] = nb; }
       if (d + 1 == b.n_docs) {
         w.doc_line_off[b.n_docs] = line0 + nl;
         w.doc_byte_off[b.n_docs] = byte0 + nb;
@@ -528,8 +586,7 @@ __global__ void __launch_bounds__(POLL_THREADS, 2) k_poll(BatchDev b, FleetDev f
                                                        (line0 + nl > w.desc_cap ? OVF_DESC : 0u));
       continue;
     }
-    if (fastdoc) fast_emit(P, w, S, Sb, ws, ng, nl, line0, byte0);
-    else slow_emit(d, b, f, w, nl, line0, byte0);
+    slow_emit(d, b, f, w, nl, line0, byte0);
     __syncwarp();
   }
 }
