@@ -162,6 +162,40 @@ int  kgm_fetch_result(kgm_ctx *ctx, kgm_result *out_host);
 
 int  kgm_get_timing(kgm_ctx *ctx, kgm_timing *out);
 
+/* ---- stage 3: time-window reductions -------------------------------------------------
+ * No counterpart in the reference: gpu.py:136-143,206-216 emit raw per-poll lines with no
+ * timestamp and leave aggregation to InfluxQL / Grafana.  This is an ADDITIVE output; it
+ * never changes a byte of the node_gpu / pod_gpu lines.  Every emitted line of the resident
+ * batch is one sample of a series
+ *     kind 0  node_gpu line: (host, gpu_id)              -- its tag set, gpu.py:137
+ *     kind 1  pod_gpu line:  (host, container, gpu_id)   -- "per (node, pod, gpu)"
+ * in window doc_tick / window_ticks.  Values are the integers behind the line's fields
+ * (digit strip as in gpu.py:133-134,138-143,204-205, saturating at 2^32-2): metric 0 =
+ * gpu_util, 1 = mem_used (node line) / used_memory (pod line), 2 = the digits of a 7th
+ * --query-gpu column (power.draw of an extended query; absent in the reference's query).  A
+ * line whose field has no digits contributes no sample to that metric (m_count).  Groups
+ * are returned in ascending (kind, node|container, gpu_id, window) order; gpu_id 0xffff is
+ * the idle branch's "None" (gpu.py:226).  last = the value of the line with the greatest
+ * (tick, position in the batch).  mean = sum / m_count in IEEE double.
+ * The batch must have been uploaded with doc_tick.  Pointers belong to the context and
+ * stay valid until the next call on it (host pointers iff want_host_copy != 0).          */
+typedef struct kgm_windows {
+  uint64_t        n;
+  const uint8_t  *kind;
+  const uint32_t *node;          /* node index of the series                                */
+  const uint32_t *container;     /* global container index (kind 1), 0xffffffff (kind 0)     */
+  const uint32_t *gpu_id;
+  const uint32_t *window;
+  const uint32_t *count;         /* lines in the group                                       */
+  const uint32_t *m_count[3];
+  const uint32_t *m_min[3];
+  const uint32_t *m_max[3];
+  const uint32_t *m_last[3];
+  const uint64_t *m_sum[3];
+  const double   *m_mean[3];
+} kgm_windows;
+int  kgm_window_reduce(kgm_ctx *ctx, uint32_t window_ticks, int want_host_copy, kgm_windows *out);
+
 /* Which kernels run a batch (no counterpart in the reference; results are identical):
  *   AUTO           one fused single-pass kernel when the batch fits its shared-memory slices,
  *                  the staged kernels otherwise (default)

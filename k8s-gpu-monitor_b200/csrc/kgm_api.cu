@@ -15,6 +15,7 @@
 #include "../../include/kgm.h"
 #include "kgm_device.cuh"
 #include "kgm_skeleton.h"
+#include "kgm_window.cuh"
 
 using namespace kgm;
 
@@ -103,6 +104,11 @@ struct kgm_ctx {
   cudaEvent_t ev_in[MAX_CHUNKS] = {}, ev_k[MAX_CHUNKS] = {};
   HostBuf h_chunk;                         // per chunk: totals {lines, bytes} + counters
   uint32_t last_chunks = 1;
+  // window reductions
+  uint32_t max_tick = 0;
+  bool have_ticks = false;
+  DevBuf w_win_samples, w_win_groups, w_win_temp;
+  HostBuf h_win_groups;
 
   // results
   bool have_result = false;
@@ -419,6 +425,9 @@ int prepare_batch(kgm_ctx *ctx, const kgm_batch *b, uint64_t *gb_out, uint64_t *
     max_a = std::max(max_a, aoff[d + 1] - aoff[d]);
   }
   plan_fused(ctx, n, max_g, max_a);
+  ctx->have_ticks = b->doc_tick != nullptr;
+  ctx->max_tick = 0;
+  if (b->doc_tick) for (uint32_t d = 0; d < n; ++d) ctx->max_tick = std::max(ctx->max_tick, b->doc_tick[d]);
   const uint64_t gb = goff[n], ab = aoff[n];
   if (gb >= 0xfff00000ull || ab >= 0xfff00000ull) return KGM_E_LIMIT;
   if ((gb && !b->gpu_csv) || (ab && !b->apps_csv)) return KGM_E_INVALID;
@@ -661,10 +670,10 @@ void kgm_destroy(kgm_ctx *ctx) {
                    &ctx->w_status, &ctx->w_doc_line_off, &ctx->w_doc_byte_off, &ctx->w_totals,
                    &ctx->w_line_off, &ctx->w_out, &ctx->w_flush, &ctx->w_ticket, &ctx->w_scan,
                    &ctx->f_node_fast, &ctx->f_tb_off, &ctx->f_tb_len, &ctx->f_tb_pool, &ctx->f_pid16,
-                   &ctx->f_vis_hash2};
+                   &ctx->f_vis_hash2, &ctx->w_win_samples, &ctx->w_win_groups, &ctx->w_win_temp};
   for (DevBuf *b : dev) b->release();
   HostBuf *host[] = {&ctx->h_small, &ctx->h_lines, &ctx->h_line_off, &ctx->h_doc_line_off, &ctx->h_status,
-                     &ctx->h_chunk};
+                     &ctx->h_chunk, &ctx->h_win_groups};
   for (HostBuf *b : host) b->release();
   for (int i = 0; i < EV_COUNT; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
   for (int i = 0; i < MAX_CHUNKS; ++i) {
@@ -946,6 +955,120 @@ int kgm_encode_batch(kgm_ctx *ctx, const kgm_batch *b, int want_host_copy, kgm_r
     fill_result_dev(ctx, out);
   }
   fill_timing(ctx, true, want_host_copy != 0);
+  return KGM_OK;
+}
+
+extern "C++" {
+namespace {
+
+// Runs the staged tokenizer and join only (token tables + line plan stay in the workspace).
+int run_plan_only(kgm_ctx *ctx, uint32_t *n_desc) {
+  if (!ctx->fleet_loaded || !ctx->batch_resident) return KGM_E_STATE;
+  CU(ctx->h_small.ensure(64));
+  for (int attempt = 0; attempt < 6; ++attempt) {
+    int rc = ensure_workspace(ctx);
+    if (rc) return rc;
+    ctx->work.counters = ctx->w_counters.as<uint32_t>();
+    ctx->counters_clean = false;
+    CU(cudaMemsetAsync(ctx->work.counters, 0, CTR_COUNT * sizeof(uint32_t), ctx->stream));
+    launch_tokenize(ctx->batch, ctx->work, ctx->sms, ctx->stream);
+    launch_join(ctx->batch, ctx->fleet, ctx->work, ctx->sms, ctx->stream);
+    CU(cudaGetLastError());
+    uint32_t *hc = ctx->h_small.as<uint32_t>();
+    CU(cudaMemcpyAsync(hc, ctx->work.counters, CTR_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    const uint32_t ovf = hc[CTR_OVERFLOW];
+    if (!ovf) { *n_desc = hc[CTR_DESC]; return KGM_OK; }
+    if (ovf & OVF_GROW) ctx->grow_cap = std::max(ctx->grow_cap * 2, hc[CTR_GROW] + 64);
+    if (ovf & OVF_PROW) ctx->prow_cap = std::max(ctx->prow_cap * 2, hc[CTR_PROW] + 64);
+    if (ovf & OVF_DESC) ctx->desc_cap = std::max(ctx->desc_cap * 2, hc[CTR_DESC] + 64);
+  }
+  return KGM_E_LIMIT;
+}
+
+// Carves 256-byte aligned arrays out of one allocation.
+struct Carver {
+  uint8_t *base;
+  size_t off = 0;
+  template <class T> T *take(size_t n) {
+    T *p = reinterpret_cast<T *>(base + off);
+    off += (n * sizeof(T) + 255) & ~(size_t)255;
+    return p;
+  }
+};
+
+WinGroups carve_groups(uint8_t *base, size_t n, size_t *bytes) {
+  Carver c{base};
+  WinGroups g{};
+  g.kind = c.take<uint8_t>(n);
+  g.node = c.take<uint32_t>(n); g.container = c.take<uint32_t>(n); g.gpu_id = c.take<uint32_t>(n);
+  g.window = c.take<uint32_t>(n); g.count = c.take<uint32_t>(n);
+  for (int m = 0; m < 3; ++m) {
+    g.m_count[m] = c.take<uint32_t>(n); g.m_min[m] = c.take<uint32_t>(n); g.m_max[m] = c.take<uint32_t>(n);
+    g.m_last[m] = c.take<uint32_t>(n); g.m_sum[m] = c.take<uint64_t>(n); g.m_mean[m] = c.take<double>(n);
+  }
+  g.key = c.take<uint64_t>(n);
+  for (int m = 0; m < 3; ++m) g.m_order[m] = c.take<uint64_t>(n);
+  *bytes = c.off;
+  return g;
+}
+
+}  // namespace
+}  // extern "C++"
+
+int kgm_window_reduce(kgm_ctx *ctx, uint32_t window_ticks, int want_host_copy, kgm_windows *out) {
+  if (!ctx || !out || window_ticks == 0) return KGM_E_INVALID;
+  CU(cudaSetDevice(ctx->device));
+  if (!ctx->fleet_loaded || !ctx->batch_resident) return KGM_E_STATE;
+  if (!ctx->have_ticks) return KGM_E_INVALID;                  // the batch was uploaded without doc_tick
+  if (ctx->max_tick / window_ticks > 0xffffu || ctx->max_tick >= (1u << 20) || ctx->batch.n_docs >= (1u << 26) ||
+      ctx->fleet.n_containers >= 0x7fffffffu)
+    return KGM_E_LIMIT;
+  uint32_t n_desc = 0;
+  int rc = run_plan_only(ctx, &n_desc);
+  if (rc) return rc;
+  *out = kgm_windows{};
+  if (n_desc == 0) return KGM_OK;
+  // samples
+  const size_t n = n_desc;
+  const size_t sample_bytes = 12 * ((n * 8 + 255) & ~(size_t)255) + 4096;
+  CU(ctx->w_win_samples.ensure(sample_bytes));
+  Carver c{ctx->w_win_samples.as<uint8_t>()};
+  WinSamples s{};
+  s.key = c.take<uint64_t>(n); s.key_sorted = c.take<uint64_t>(n); s.order = c.take<uint64_t>(n);
+  s.idx = c.take<uint32_t>(n); s.idx_sorted = c.take<uint32_t>(n);
+  for (int m = 0; m < 3; ++m) s.val[m] = c.take<uint32_t>(n);
+  s.node = c.take<uint32_t>(n);
+  uint32_t *head = c.take<uint32_t>(n), *seg_incl = c.take<uint32_t>(n);
+  const size_t temp_bytes = window_sort_temp_bytes(n_desc);
+  CU(ctx->w_win_temp.ensure(temp_bytes));
+  CU(launch_window_samples(ctx->batch, ctx->work, n_desc, window_ticks, s, ctx->w_win_temp.p, temp_bytes, head,
+                           seg_incl, ctx->stream));
+  CU(cudaGetLastError());
+  uint32_t *h32 = ctx->h_small.as<uint32_t>();
+  CU(cudaMemcpyAsync(h32, seg_incl + (n - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  const uint32_t n_groups = h32[0];
+  if (n_groups == 0) return KGM_OK;
+  size_t group_bytes = 0;
+  (void)carve_groups(nullptr, n_groups, &group_bytes);
+  CU(ctx->w_win_groups.ensure(group_bytes));
+  const WinGroups g = carve_groups(ctx->w_win_groups.as<uint8_t>(), n_groups, &group_bytes);
+  CU(launch_window_reduce(s, seg_incl, n_desc, g, n_groups, ctx->stream));
+  WinGroups r = g;
+  if (want_host_copy) {
+    CU(ctx->h_win_groups.ensure(group_bytes));
+    CU(cudaMemcpyAsync(ctx->h_win_groups.p, ctx->w_win_groups.p, group_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    r = carve_groups(ctx->h_win_groups.as<uint8_t>(), n_groups, &group_bytes);
+  }
+  CU(cudaStreamSynchronize(ctx->stream));
+  out->n = n_groups;
+  out->kind = r.kind; out->node = r.node; out->container = r.container; out->gpu_id = r.gpu_id;
+  out->window = r.window; out->count = r.count;
+  for (int m = 0; m < 3; ++m) {
+    out->m_count[m] = r.m_count[m]; out->m_min[m] = r.m_min[m]; out->m_max[m] = r.m_max[m];
+    out->m_last[m] = r.m_last[m]; out->m_sum[m] = r.m_sum[m]; out->m_mean[m] = r.m_mean[m];
+  }
   return KGM_OK;
 }
 

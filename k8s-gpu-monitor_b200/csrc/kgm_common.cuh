@@ -69,7 +69,8 @@ struct GpuRow {
   uint32_t first;         // local index of the first row with the same key
   uint32_t last;          // (on first rows) local index of the last row with that key
   uint32_t sid;           // (on first rows) short id = rank in first-seen order (gpu.py:119)
-  uint32_t pad;
+  uint32_t power;         // int(digits(cell 6)) of an extended query (power.draw), saturating;
+                          // NONE32 if the row has no 7th cell or it holds no digit (stage 3 only)
 };
 
 // One row of the --query-compute-apps text (gpu.py:111-116), tokenised.
@@ -156,6 +157,7 @@ struct GpuRowScan {
   uint32_t len;           // row length without trailing CRs
   uint32_t pending_cr;
   uint32_t ndig;          // digits in the current cell
+  uint32_t sig;           // of them, from the first non-zero one on
   uint64_t val;
   bool cell_first, lead, over;
 
@@ -163,19 +165,22 @@ struct GpuRowScan {
     r = GpuRow();
     r.row_off = row_off; r.row_end = row_end;
     r.key_hash = hash_init();
-    base = row_off; ci = 0; len = 0; pending_cr = 0; ndig = 0; val = 0;
+    r.power = NONE32;
+    base = row_off; ci = 0; len = 0; pending_cr = 0; ndig = 0; sig = 0; val = 0;
     cell_first = true; lead = true; over = false;
   }
+  KGM_HDM uint32_t sat32() const { return (over || sig > 10 || val > 0xffffffffull) ? 0xffffffffu : (uint32_t)val; }
   KGM_HDM void close_cell(uint32_t p) {
     if (p > 65535u) r.flags |= RF_LONG;
     if (ci < 6) r.cell_end[ci] = (uint16_t)p;
     if (ci == 0 && lead) r.key_lo = (uint16_t)p;
     const uint8_t nd8 = (uint8_t)(ndig > 255u ? 255u : ndig);
-    if (ci == 1) { r.nd[0] = nd8; r.util = (over || val > 0xffffffffull) ? 0xffffffffu : (uint32_t)val; }
-    else if (ci == 3) { r.nd[1] = nd8; r.mem_total = val; if (ndig > 19) r.flags |= RF_RANGE; }
-    else if (ci == 4) { r.nd[2] = nd8; r.mem_used = val; if (ndig > 19) r.flags |= RF_RANGE; }
+    if (ci == 1) { r.nd[0] = nd8; r.util = sat32(); }
+    else if (ci == 3) { r.nd[1] = nd8; r.mem_total = val; if (over) r.flags |= RF_RANGE; }
+    else if (ci == 4) { r.nd[2] = nd8; r.mem_used = val; if (over) r.flags |= RF_RANGE; }
     else if (ci == 5) { r.nd[3] = nd8; }
-    ndig = 0; val = 0; over = false;
+    else if (ci == 6) { r.power = ndig ? sat32() : NONE32; }
+    ndig = 0; sig = 0; val = 0; over = false;
   }
   KGM_HDM void step(uint32_t c, uint32_t pos) {
     const uint32_t p = pos - base;
@@ -191,7 +196,8 @@ struct GpuRowScan {
       r.key_hash = hash_step(r.key_hash, c);
     } else if (is_digit(c)) {
       ++ndig;
-      if (ndig > 19) over = true; else val = val * 10 + (c - 48u);
+      if (sig || c != 48u) ++sig;
+      if (sig > 19) over = true; else val = val * 10 + (c - 48u);
     }
   }
   KGM_HDM void finish() {
@@ -203,7 +209,7 @@ struct GpuRowScan {
 
 struct ProcRowScan {
   ProcRow r;
-  uint32_t base, ci, len, pending_cr, ndig, name_len, pid_len;
+  uint32_t base, ci, len, pending_cr, ndig, sig, name_len, pid_len;
   uint64_t val;
   bool cell_first, lead;
 
@@ -212,7 +218,7 @@ struct ProcRowScan {
     r.row_off = row_off; r.row_end = row_end;
     r.uuid_hash = hash_init();
     r.sid = NONE32; r.crank = NONE32;
-    base = row_off; ci = 0; len = 0; pending_cr = 0; ndig = 0; name_len = 0; pid_len = 0; val = 0;
+    base = row_off; ci = 0; len = 0; pending_cr = 0; ndig = 0; sig = 0; name_len = 0; pid_len = 0; val = 0;
     cell_first = true; lead = true;
   }
   KGM_HDM void close_cell(uint32_t p) {
@@ -229,9 +235,9 @@ struct ProcRowScan {
       if (lead) r.key_lo = (uint16_t)p;
     } else if (ci == 3) {
       r.nd_mem = (uint8_t)(ndig > 255u ? 255u : ndig);
-      r.used_mem = (ndig > 9 || val > 0xffffffffull) ? 0xffffffffu : (uint32_t)val;
+      r.used_mem = (sig > 10 || val > 0xffffffffull) ? 0xffffffffu : (uint32_t)val;
     }
-    ndig = 0; val = 0;
+    ndig = 0; sig = 0; val = 0;
   }
   KGM_HDM void step(uint32_t c, uint32_t pos) {
     const uint32_t p = pos - base;
@@ -253,7 +259,8 @@ struct ProcRowScan {
       r.uuid_hash = hash_step(r.uuid_hash, c);
     } else if (ci == 3 && is_digit(c)) {
       ++ndig;
-      if (ndig <= 10) val = val * 10 + (c - 48u);
+      if (sig || c != 48u) ++sig;
+      if (sig <= 10) val = val * 10 + (c - 48u);
     }
   }
   KGM_HDM void finish() {

@@ -222,13 +222,12 @@ __device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, cons
   // ---- gpu rows: one lane per row (gpu.py:104-109,119-143) ----
   GRec *grec = reinterpret_cast<GRec *>(Sb + ws.grec);
   uint64_t my_hash = 0;
-  uint32_t node_bytes = 0;
   {
     bool ok = true;
     if (l < ng) {
       GRec g;
       ok = parse_gpu_row(TG, gstart[l], gstart[l + 1] - 1u, hd.fixed, l, g);
-      if (ok) { grec[l] = g; my_hash = g.hash; node_bytes = g.line_len; }
+      if (ok) { grec[l] = g; my_hash = g.hash; }
     }
     if (!__all_sync(FULL, ok)) return false;
     bool dup = false;                               // equal keys: last row wins (gpu.py:54) -> generic path

@@ -74,6 +74,13 @@ class KgmResult(C.Structure):
     ]
 
 
+class KgmWindows(C.Structure):
+    _fields_ = [("n", C.c_uint64), ("kind", C.c_void_p), ("node", C.c_void_p), ("container", C.c_void_p),
+                ("gpu_id", C.c_void_p), ("window", C.c_void_p), ("count", C.c_void_p),
+                ("m_count", C.c_void_p * 3), ("m_min", C.c_void_p * 3), ("m_max", C.c_void_p * 3),
+                ("m_last", C.c_void_p * 3), ("m_sum", C.c_void_p * 3), ("m_mean", C.c_void_p * 3)]
+
+
 class KgmTiming(C.Structure):
     _fields_ = [
         ("h2d_ms", C.c_float), ("tokenize_ms", C.c_float), ("join_ms", C.c_float),
@@ -97,6 +104,7 @@ SIGNATURES = {
     "kgm_fetch_result": (C.c_int, [C.c_void_p, C.POINTER(KgmResult)]),
     "kgm_get_timing": (C.c_int, [C.c_void_p, C.POINTER(KgmTiming)]),
     "kgm_set_pipeline": (C.c_int, [C.c_void_p, C.c_int]),
+    "kgm_window_reduce": (C.c_int, [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]),
     "kgm_flush_l2": (C.c_int, [C.c_void_p, C.c_uint64]),
     "kgm_host_alloc": (C.c_void_p, [C.c_uint64]),
     "kgm_host_free": (None, [C.c_void_p]),

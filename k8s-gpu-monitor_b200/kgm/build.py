@@ -21,9 +21,9 @@ HOSTCHECK = os.path.join(ROOT, "tests", "native", "_hostcheck.so")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
-SOURCES = ["kgm_kernels.cu", "kgm_api.cu"]
+SOURCES = ["kgm_kernels.cu", "kgm_api.cu", "kgm_window.cu"]
 HEADERS = ["kgm_common.cuh", "kgm_d2s.cuh", "kgm_d2s_tables.h", "kgm_device.cuh", "kgm_skeleton.h",
-           "kgm_fast.cuh", "kgm_fused.cuh"]
+           "kgm_fast.cuh", "kgm_fused.cuh", "kgm_window.cuh"]
 
 
 def _stale(target, deps):

@@ -193,6 +193,25 @@ class Monitor:
         _check(self._lib.kgm_fetch_result(self._ctx, C.byref(res)), "kgm_fetch_result", self._ctx, self._lib)
         return HostResult(res)
 
+    def window_reduce(self, window_ticks) -> dict:
+        """Stage 3 (kgm_window_reduce) on the resident batch, which must carry ``doc_tick``:
+        per (series, window) count / min / max / sum / mean / last of gpu_util, mem and
+        power, as numpy arrays (copies), ascending (kind, node|container, gpu_id, window)."""
+        w = _ffi.KgmWindows()
+        _check(self._lib.kgm_window_reduce(self._ctx, int(window_ticks), 1, C.byref(w)), "kgm_window_reduce",
+               self._ctx, self._lib)
+        n = int(w.n)
+        view = lambda ptr, ctype: (np.ctypeslib.as_array((ctype * n).from_address(ptr)).copy()
+                                   if n else np.zeros(0, ctype))
+        out = {"n": n, "kind": view(w.kind, C.c_uint8)}
+        for name in ("node", "container", "gpu_id", "window", "count"):
+            out[name] = view(getattr(w, name), C.c_uint32)
+        for m, metric in enumerate(("gpu_util", "mem", "power")):
+            for stat, ctype in (("count", C.c_uint32), ("min", C.c_uint32), ("max", C.c_uint32),
+                                ("last", C.c_uint32), ("sum", C.c_uint64), ("mean", C.c_double)):
+                out["%s_%s" % (metric, stat)] = view(getattr(w, "m_" + stat)[m], ctype)
+        return out
+
     def timing(self) -> dict:
         t = _ffi.KgmTiming()
         _check(self._lib.kgm_get_timing(self._ctx, C.byref(t)), "kgm_get_timing", self._ctx, self._lib)

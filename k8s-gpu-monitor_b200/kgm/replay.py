@@ -174,8 +174,10 @@ def make_node(seed, node, *, gpus=8, containers=8, procs_per_container=4,
     return NodeSnap(name=name_fmt % node, uuids=uuids, containers=snaps)
 
 
-def make_texts(seed, node_idx, snap: NodeSnap, tick):
-    """The two nvidia-smi texts of one poll of ``snap`` at ``tick`` (gpu.py:104-116)."""
+def make_texts(seed, node_idx, snap: NodeSnap, tick, power=False):
+    """The two nvidia-smi texts of one poll of ``snap`` at ``tick`` (gpu.py:104-116).
+    ``power`` appends a 7th ``power.draw`` column (an extended query; the reference's
+    ``zip`` ignores extra cells, gpu.py:49, so its lines do not change)."""
     ng = len(snap.uuids)
     g = np.arange(ng, dtype=np.uint64)
     base = np.uint64(h(seed, 10, node_idx, tick))
@@ -183,11 +185,14 @@ def make_texts(seed, node_idx, snap: NodeSnap, tick):
     umem = (mix64(base ^ (g * np.uint64(4) + np.uint64(2))) % np.uint64(101)).astype(np.int64)
     used = (mix64(base ^ (g * np.uint64(4) + np.uint64(3))) %
             np.uint64(MEM_TOTAL_MIB + 1)).astype(np.int64)
-    rows = [GPU_HEADER]
+    rows = [GPU_HEADER[:-1] + ", power.draw [W]\n" if power else GPU_HEADER]
+    watts = (mix64(base ^ (g * np.uint64(4))) % np.uint64(100001)).astype(np.int64)   # 0.00 .. 1000.00 W
     for i in range(ng):
-        rows.append("%s, %d %%, %d %%, %d MiB, %d MiB, %d MiB\n" %
-                    (snap.uuids[i], util[i], umem[i], MEM_TOTAL_MIB, used[i],
-                     MEM_TOTAL_MIB - used[i]))
+        row = "%s, %d %%, %d %%, %d MiB, %d MiB, %d MiB" % (snap.uuids[i], util[i], umem[i], MEM_TOTAL_MIB,
+                                                            used[i], MEM_TOTAL_MIB - used[i])
+        if power:
+            row += ", %d.%02d W" % (watts[i] // 100, watts[i] % 100)
+        rows.append(row + "\n")
     gpu_csv = "".join(rows)
     rows = [APPS_HEADER]
     # nvidia-smi lists compute apps GPU-major
@@ -219,12 +224,12 @@ class Replay:
         return sum(t.count("\n") - 1 for t in self.gpu_texts)
 
 
-def make_replay(seed=0, *, nodes=1, ticks=1, node_base=0, **node_kw) -> Replay:
+def make_replay(seed=0, *, nodes=1, ticks=1, node_base=0, power=False, **node_kw) -> Replay:
     snaps = [make_node(seed, node_base + n, **node_kw) for n in range(nodes)]
     doc_node, doc_tick, gt, at = [], [], [], []
     for n, snap in enumerate(snaps):
         for t in range(ticks):
-            a, b = make_texts(seed, node_base + n, snap, t)
+            a, b = make_texts(seed, node_base + n, snap, t, power=power)
             doc_node.append(n)
             doc_tick.append(t)
             gt.append(a)
