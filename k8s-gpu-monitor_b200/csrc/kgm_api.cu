@@ -97,6 +97,8 @@ struct kgm_ctx {
   DevBuf w_ticket, w_scan;
   DevBuf f_node_fast, f_tb_off, f_tb_len, f_tb_pool, f_pid16, f_vis_hash2;
   uint32_t fast_max_nc = 1, fast_max_tb = 0, fast_max_idle = 0, any_fast = 0;
+  std::vector<uint8_t> h_node_fast;        // host copies of FleetDev::node_fast / tb_len
+  std::vector<uint32_t> h_tb_len;
   uint32_t slow_docs = 0;
   bool last_fused = false;
   // chunked end-to-end path: copies and kernels of consecutive chunks overlap
@@ -358,32 +360,43 @@ int fetch(kgm_ctx *ctx, kgm_result *out) {
 }
 
 // Lays out a warp's shared-memory slice for this batch (FusedParams) and decides whether the
-// fused kernel can run it: two CTAs of four warps per SM if the slices fit, else one.
-// Documents larger than the slice still work (they take the generic path inside the kernel);
-// the sizes are therefore clamped, not rejected.
-void plan_fused(kgm_ctx *ctx, uint32_t n_docs, uint64_t max_g, uint64_t max_a) {
+// fused kernel can run it.  Slices are sized for two CTAs of four warps per SM; the text
+// windows, the template block and the per-document tables are clamped to that budget, and a
+// document (or a node) that does not fit takes the generic path inside the kernel.  If
+// fewer than 90 % of the documents fit that way, one CTA per SM with slices twice as large
+// is used when that covers more of them.
+struct FusedFit { FusedParams P; uint64_t fits; bool ok; };
+
+FusedFit fused_layout(kgm_ctx *ctx, const kgm_batch *b, int ctas, uint64_t max_g, uint64_t max_a) {
   auto r16 = [](uint64_t v) { return (uint32_t)((v + 15) & ~15ull); };
-  ctx->fused_ok = false;
-  if (n_docs == 0) return;
+  FusedFit f{};
   const uint32_t const_pad = (fast::ConstArea::BYTES + 15u) & ~15u;
-  for (int ctas = 2; ctas >= 1; --ctas) {
-    const uint32_t dyn_max = ctas == 2 ? 115712u : 232448u;
-    const uint32_t warp_bytes = ((dyn_max - const_pad) / 4) & ~15u;
-    // at most ~45% of a slice for the two text windows; larger documents take the generic path
-    const uint32_t text_budget = warp_bytes * 45 / 100;
-    uint64_t g = std::min<uint64_t>(max_g, 8192), a = std::min<uint64_t>(max_a, 32768);
-    if (r16(g + 15) + r16(a + 15) + 96 > text_budget) {
-      a = text_budget > r16(g + 15) + 96 + 1024 ? text_budget - r16(g + 15) - 96 - 16 : 1024;
-    }
-    FusedParams P{};
+  const uint32_t dyn_max = ctas == 2 ? 115712u : 232448u;
+  const uint32_t warp_bytes = ((dyn_max - const_pad) / 4) & ~15u;
+  const uint64_t need_stage = std::max<uint64_t>(MAX_LINE_BYTES + 64, 12ull * ctx->fleet.max_nc + 16);
+  if (need_stage + 4096 > warp_bytes) return f;
+  const uint64_t budget = warp_bytes - need_stage;            // texts + template block + tables
+  // the template block gets what it needs up to 40 % of the budget, the texts up to 45 %;
+  // the per-row tables follow the text size, so the two are shrunk until everything fits
+  uint64_t tb = std::min<uint64_t>(r16(ctx->fast_max_tb) + 32, (budget * 40 / 100) & ~15ull);
+  uint64_t g = std::min<uint64_t>(max_g, 8192), a = std::min<uint64_t>(max_a, 60000);
+  const uint64_t text_budget = budget * 45 / 100;
+  if (r16(g + 15) + r16(a + 15) + 96 > text_budget) {
+    g = std::min<uint64_t>(g, text_budget / 4);
+    a = text_budget > r16(g + 15) + 96 + 1024 ? text_budget - r16(g + 15) - 96 - 16 : 1024;
+  }
+  FusedParams &P = f.P;
+  uint32_t o = 0;
+  for (int round = 0; round < 12; ++round) {
+    P = FusedParams{};
     P.cap_g = r16(g + 15) + 48;
     P.cap_a = r16(a + 15) + 48;
     P.cap_ng = (uint32_t)std::min<uint64_t>(32, std::max<uint64_t>(8, g / 64 + 2));
     P.cap_np = (uint32_t)std::min<uint64_t>(2048, std::max<uint64_t>(8, a / 64 + 2));
-    P.cap_c = std::max(1u, ctx->fast_max_nc);
-    P.cap_t = r16(ctx->fast_max_tb) + 32;
-    P.cap_lines = P.cap_ng + P.cap_np + ctx->fast_max_idle;
-    uint32_t o = 0;
+    P.cap_c = std::min(512u, std::max(1u, ctx->fast_max_nc));
+    P.cap_t = r16(tb);
+    P.cap_lines = P.cap_ng + P.cap_np + std::min(ctx->fast_max_idle, 512u);
+    o = 0;
     P.off_tg = o; o += P.cap_g;
     P.off_ta = o; o += P.cap_a;
     P.off_gstart = o; o += r16(2ull * (P.cap_ng + 2));
@@ -396,15 +409,44 @@ void plan_fused(kgm_ctx *ctx, uint32_t n_docs, uint64_t max_g, uint64_t max_a) {
     P.off_loff = o; o += r16(4ull * (P.cap_lines + 1));
     P.off_tb = o; o += P.cap_t;
     P.off_stage = o;
-    const uint64_t need_stage = std::max<uint64_t>(MAX_LINE_BYTES + 64, 12ull * ctx->fleet.max_nc + 16);
-    if ((uint64_t)o + need_stage > warp_bytes) continue;
-    P.warp_bytes = warp_bytes;
-    P.stage_bytes = warp_bytes - o;
-    ctx->fused = P;
-    ctx->fused_ctas_per_sm = ctas;
-    ctx->fused_ok = true;
-    return;
+    if ((uint64_t)o + need_stage <= warp_bytes) break;
+    const uint64_t over = (uint64_t)o + need_stage - warp_bytes;
+    const uint64_t cut_a = std::min<uint64_t>(a > 1024 ? a - 1024 : 0, over * 2 / 5 + 64);
+    const uint64_t cut_t = std::min<uint64_t>(tb > 1024 ? tb - 1024 : 0, over * 2 / 5 + 64);
+    if (!cut_a && !cut_t) break;
+    a -= cut_a; tb -= cut_t;
   }
+  if ((uint64_t)o + need_stage > warp_bytes) return f;
+  P.warp_bytes = warp_bytes;
+  P.stage_bytes = warp_bytes - o;
+  // how many documents can take the fast path with these caps (same tests as fast_plan)
+  for (uint32_t d = 0; d < b->n_docs; ++d) {
+    const uint32_t nd = b->doc_node[d];
+    const uint64_t g_lo = b->gpu_off[d], g_hi = b->gpu_off[d + 1], a_lo = b->apps_off[d], a_hi = b->apps_off[d + 1];
+    if (!ctx->h_node_fast[nd]) continue;
+    if (((g_hi + 15) & ~15ull) - (g_lo & ~15ull) + 32 > P.cap_g) continue;
+    if (((a_hi + 15) & ~15ull) - (a_lo & ~15ull) + 32 > P.cap_a) continue;
+    if (ctx->h_tb_len[nd] + 16 > P.cap_t) continue;
+    ++f.fits;
+  }
+  f.ok = true;
+  return f;
+}
+
+void plan_fused(kgm_ctx *ctx, const kgm_batch *b, uint64_t max_g, uint64_t max_a) {
+  ctx->fused_ok = false;
+  if (b->n_docs == 0) return;
+  const FusedFit two = fused_layout(ctx, b, 2, max_g, max_a);
+  FusedFit pick = two;
+  int ctas = 2;
+  if (!two.ok || two.fits * 10 < (uint64_t)b->n_docs * 9) {
+    const FusedFit one = fused_layout(ctx, b, 1, max_g, max_a);
+    if (one.ok && (!two.ok || one.fits > two.fits + b->n_docs / 20)) { pick = one; ctas = 1; }
+  }
+  if (!pick.ok) return;
+  ctx->fused = pick.P;
+  ctx->fused_ctas_per_sm = ctas;
+  ctx->fused_ok = true;
 }
 
 // Validates a batch, sizes the device buffers and the workspace guesses for it and points
@@ -424,7 +466,7 @@ int prepare_batch(kgm_ctx *ctx, const kgm_batch *b, uint64_t *gb_out, uint64_t *
     max_g = std::max(max_g, goff[d + 1] - goff[d]);
     max_a = std::max(max_a, aoff[d + 1] - aoff[d]);
   }
-  plan_fused(ctx, n, max_g, max_a);
+  plan_fused(ctx, b, max_g, max_a);
   ctx->have_ticks = b->doc_tick != nullptr;
   ctx->max_tick = 0;
   if (b->doc_tick) for (uint32_t d = 0; d < n; ++d) ctx->max_tick = std::max(ctx->max_tick, b->doc_tick[d]);
@@ -882,6 +924,8 @@ int kgm_load_fleet(kgm_ctx *ctx, const kgm_fleet *fl) {
   f.vis_hash2 = ctx->f_vis_hash2.as<uint64_t>();
   ctx->fast_max_nc = fast_max_nc; ctx->fast_max_tb = fast_max_tb; ctx->fast_max_idle = fast_max_idle;
   ctx->any_fast = any_fast;
+  ctx->h_node_fast = node_fast;
+  ctx->h_tb_len = tb_len;
   ctx->fused_ok = false;
   ctx->fleet_loaded = true;
   return KGM_OK;

@@ -100,6 +100,9 @@ class NodeSnap:
     name: str
     uuids: list
     containers: list                # ContainerSnap, in `docker stats` order
+    mig: int = 0                    # 0 = plain GPUs; 1 = MIG parents: utilization prints "[N/A]" and idle
+                                    # containers see MIG instance uuids; 2 = additionally the process
+                                    # rows name MIG instance uuids (the reference dies: gpu.py:151)
 
     @property
     def ps_text(self):              # gpu.py:92-97; argv is not shell-parsed -> literal quotes
@@ -188,8 +191,12 @@ def make_texts(seed, node_idx, snap: NodeSnap, tick, power=False):
     rows = [GPU_HEADER[:-1] + ", power.draw [W]\n" if power else GPU_HEADER]
     watts = (mix64(base ^ (g * np.uint64(4))) % np.uint64(100001)).astype(np.int64)   # 0.00 .. 1000.00 W
     for i in range(ng):
-        row = "%s, %d %%, %d %%, %d MiB, %d MiB, %d MiB" % (snap.uuids[i], util[i], umem[i], MEM_TOTAL_MIB,
-                                                            used[i], MEM_TOTAL_MIB - used[i])
+        if snap.mig:                # a MIG parent reports no utilization
+            row = "%s, [N/A], [N/A], %d MiB, %d MiB, %d MiB" % (snap.uuids[i], MEM_TOTAL_MIB, used[i],
+                                                                MEM_TOTAL_MIB - used[i])
+        else:
+            row = "%s, %d %%, %d %%, %d MiB, %d MiB, %d MiB" % (snap.uuids[i], util[i], umem[i], MEM_TOTAL_MIB,
+                                                                used[i], MEM_TOTAL_MIB - used[i])
         if power:
             row += ", %d.%02d W" % (watts[i] // 100, watts[i] % 100)
         rows.append(row + "\n")
@@ -201,7 +208,10 @@ def make_texts(seed, node_idx, snap: NodeSnap, tick, power=False):
                    for j, (pid, gpu, name) in enumerate(c.gpu_procs))
     for gpu, ci, j, pid, name in procs:
         mem = 100 + h(seed, 11, node_idx, tick, ci, j) % 39901
-        rows.append("%d, %s, %s, %d MiB\n" % (pid, _PROC_NAMES[name], snap.uuids[gpu], mem))
+        uuid = snap.uuids[gpu]
+        if snap.mig == 2:
+            uuid = "MIG-" + uuid[4:]
+        rows.append("%d, %s, %s, %d MiB\n" % (pid, _PROC_NAMES[name], uuid, mem))
     return gpu_csv, "".join(rows)
 
 
@@ -236,6 +246,42 @@ def make_replay(seed=0, *, nodes=1, ticks=1, node_base=0, power=False, **node_kw
             at.append(b)
     return Replay(seed, snaps, np.asarray(doc_node, np.int32), np.asarray(doc_tick, np.int32),
                   gt, at)
+
+
+def make_skewed_replay(seed=0, *, hosts=40, epochs=3, ticks_per_epoch=4, gpus=8, max_containers=160,
+                       zipf=1.2, scale=6, mig_every=3, node_base=0) -> Replay:
+    """BASELINE configs[4] in miniature: short-lived pods and skewed series keys.  Every host
+    has ``epochs`` docker snapshots (its pods are replaced from one epoch to the next), the
+    number of containers per host follows a Zipf law (a few hosts carry most pods), every
+    ``mig_every``-th host is a MIG host (utilization "[N/A]", idle pods see MIG uuids ->
+    ``gpu_id=None``) and every other one of those also reports MIG uuids in its process rows,
+    on which the reference raises after the node lines.  Documents are tick-major inside an
+    epoch, i.e. consecutive documents belong to different hosts."""
+    snaps, doc_node, doc_tick, gt, at = [], [], [], [], []
+    for e in range(epochs):
+        first = len(snaps)
+        for hst in range(hosts):
+            u = (h(seed, 20, hst) % 100000 + 1) / 100001.0
+            nc = max(1, min(max_containers, int(scale / (u ** (1.0 / zipf)))))
+            mig = 0
+            if mig_every and hst % mig_every == mig_every - 1:
+                mig = 2 if (hst // mig_every) % 2 else 1
+            snap = make_node(seed + 1000 * e, node_base + hst, gpus=gpus, containers=nc,
+                             procs_per_container=1 + h(seed, 21, hst, e) % 3, idle_every=3, ungated_every=5)
+            snap.mig = mig
+            if mig:
+                for c in snap.containers:
+                    c.visible = ["MIG-" + v[4:] for v in c.visible]
+            snaps.append(snap)
+        for t in range(ticks_per_epoch):
+            tick = e * ticks_per_epoch + t
+            for hst in range(hosts):
+                a, b = make_texts(seed, node_base + hst, snaps[first + hst], tick)
+                doc_node.append(first + hst)
+                doc_tick.append(tick)
+                gt.append(a)
+                at.append(b)
+    return Replay(seed, snaps, np.asarray(doc_node, np.int32), np.asarray(doc_tick, np.int32), gt, at)
 
 
 # BASELINE.json `configs`, as generator parameters (SURVEY.md section 8d)

@@ -73,6 +73,130 @@ def concat_encoded(local: torch.Tensor, counts: torch.Tensor, out: torch.Tensor 
     return out[:total], off
 
 
+class ShardGather:
+    """Concatenation of every rank's encoded buffer on rank 0, rank-major, without padding.
+
+    Per step: the ranks all-gather their {bytes, lines} (a communicator of its own, so the
+    16 bytes never queue behind bulk traffic); every rank copies its bytes into one of two
+    exchange buffers (the library may then overwrite its output with the next batch) and
+    sends them to their final offset in rank 0's buffer as NCCL (gloo in the CPU tests)
+    send/recv.  ``use_ipc=True`` (experimental) instead maps rank 0's buffer into every
+    process through a CUDA IPC handle and writes the shard with a peer ``cudaMemcpyAsync``,
+    which needs no SM; on the test pool that path measured slower than NCCL, so it is off.
+    ``start`` returns once the local copy is done; ``finish`` waits for every transfer."""
+
+    def __init__(self, cap_bytes: int, device, group=None, use_ipc=False):
+        self.group, self.device = group, device
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.cap = int(cap_bytes)
+        self.xbuf = [torch.empty(self.cap, dtype=torch.uint8, device=device) for _ in range(2)]
+        self.final = (torch.empty(self.cap * self.world, dtype=torch.uint8, device=device)
+                      if self.rank == 0 else None)
+        # the tiny count exchange gets its own communicator, so that it never queues behind the
+        # bulk shard transfers of the previous step
+        self.ctl_group = dist.new_group(backend=dist.get_backend(group)) if self.world > 1 else None
+        self.pending = [[], []]
+        self.k = 0
+        self.last_offsets = None
+        self.cuda = device.type == "cuda"
+        self.stream = torch.cuda.Stream(device) if self.cuda else None
+        self.copied = [torch.cuda.Event(), torch.cuda.Event()] if self.cuda else None
+        self.peer_final = None
+        self.mode = "p2p"
+        if self.cuda and use_ipc and self.world > 1:
+            self._open_ipc()
+
+    def _open_ipc(self):
+        """Rank 0 exports its buffer; the others map it (same node, NVLink peers)."""
+        ok = torch.ones(1, dtype=torch.int32, device=self.device)
+        try:
+            box = [self.final.untyped_storage()._share_cuda_() if self.rank == 0 else None]
+            dist.broadcast_object_list(box, src=0, group=self.group)
+            if self.rank != 0:
+                storage = torch.UntypedStorage._new_shared_cuda(*box[0])
+                self.peer_final = torch.empty(0, dtype=torch.uint8, device=storage.device).set_(storage)
+                if self.peer_final.numel() < self.cap * self.world:
+                    raise RuntimeError("mapped buffer is smaller than expected")
+                probe = torch.zeros(16, dtype=torch.uint8, device=self.device)
+                self.peer_final[:16].copy_(probe)                 # peer access works?
+                torch.cuda.synchronize(self.device)
+        except Exception:
+            ok.zero_()
+            self.peer_final = None
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+        self.mode = "ipc" if int(ok.item()) == 1 else "p2p"
+
+    def start(self, local: torch.Tensor, n_bytes: int, n_lines: int):
+        slot = self.k & 1
+        self.k += 1
+        for w in self.pending[slot]:                 # the exchange buffer of step k-2 is free again
+            w.wait()
+        self.pending[slot] = []
+        counts = gather_counts(n_bytes, n_lines, self.device, self.ctl_group)
+        off = slice_offsets(counts)                  # host copy: one sync per step
+        sizes = [int(x) for x in off[1:, 0] - off[:-1, 0]]
+        if max(sizes) > self.cap:
+            raise ValueError("a shard exceeds the exchange buffer")
+        xb = self.xbuf[slot]
+        mine = int(off[self.rank, 0])
+        if self.cuda:
+            ev = self.copied[slot]
+            with torch.cuda.stream(self.stream):
+                if self.mode == "ipc" and self.rank != 0:
+                    ev.synchronize()                 # the peer write of step k-2 has left xb
+                if self.rank == 0:
+                    self.final[mine:mine + n_bytes].copy_(local[:n_bytes], non_blocking=True)
+                else:
+                    xb[:n_bytes].copy_(local[:n_bytes], non_blocking=True)
+                done = torch.cuda.Event()
+                done.record(self.stream)
+                if self.mode == "ipc" and self.rank != 0 and n_bytes:
+                    self.peer_final[mine:mine + n_bytes].copy_(xb[:n_bytes], non_blocking=True)
+                    ev.record(self.stream)
+            if self.mode == "p2p":
+                ops = []
+                if self.rank == 0:
+                    for r in range(1, self.world):
+                        if sizes[r]:
+                            o = int(off[r, 0])
+                            ops.append(dist.P2POp(dist.irecv, self.final[o:o + sizes[r]], r, self.group))
+                elif n_bytes:
+                    torch.cuda.current_stream(self.device).wait_event(done)
+                    ops.append(dist.P2POp(dist.isend, xb[:n_bytes], 0, self.group))
+                self.pending[slot] = dist.batch_isend_irecv(ops) if ops else []
+            done.synchronize()                       # the library may now reuse its output buffer
+        else:
+            ops = []
+            if self.rank == 0:
+                self.final[mine:mine + n_bytes].copy_(local[:n_bytes])
+                for r in range(1, self.world):
+                    if sizes[r]:
+                        o = int(off[r, 0])
+                        ops.append(dist.P2POp(dist.irecv, self.final[o:o + sizes[r]], r, self.group))
+            elif n_bytes:
+                xb[:n_bytes].copy_(local[:n_bytes])
+                ops.append(dist.P2POp(dist.isend, xb[:n_bytes], 0, self.group))
+            self.pending[slot] = dist.batch_isend_irecv(ops) if ops else []
+        self.last_offsets = off
+        return off
+
+    def finish(self):
+        for slot in (0, 1):
+            for w in self.pending[slot]:
+                w.wait()
+            self.pending[slot] = []
+        if self.cuda:
+            self.stream.synchronize()
+            torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            dist.barrier(group=self.ctl_group)       # every shard has landed on rank 0
+
+    def body(self):
+        """Rank 0: the concatenated bytes of the last finished step."""
+        total = int(self.last_offsets[-1, 0])
+        return self.final[:total]
+
+
 class DevicePointer:
     """Zero-copy torch view of a raw device buffer owned by libkgm (CUDA array interface)."""
 

@@ -66,6 +66,13 @@ def _worker(rank, world, port, q):
         out = torch.zeros(len(b"".join(bodies)) + 64, dtype=torch.uint8)
         whole2, _ = shard.concat_encoded(local, counts, out=out)
         assert bytes(whole2.numpy().tobytes()) == b"".join(bodies)
+        # asynchronous gather of the shards to rank 0 (what bench.py runs every step), twice
+        sg = shard.ShardGather(max(len(b) for b in bodies) + 16, torch.device("cpu"))
+        for _ in range(3):
+            sg.start(local, len(bodies[rank]), lines[rank])
+        sg.finish()
+        if rank == 0:
+            assert bytes(sg.body().numpy().tobytes()) == b"".join(bodies)
         q.put((rank, "ok"))
     except Exception as exc:  # pragma: no cover - reported to the parent
         q.put((rank, "%s: %s" % (type(exc).__name__, exc)))
