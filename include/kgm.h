@@ -132,6 +132,7 @@ typedef struct kgm_timing {
   uint32_t fused;      /* 1: the batch went through the fused single-pass kernel; its time is
                           reported as encode_ms and tokenize/join/scan are 0                  */
   uint32_t slow_docs;  /* fused kernel: documents that took the generic per-byte path inside it */
+  uint32_t fused_ctas_per_sm;  /* fused kernel: resident CTAs per SM its shared-memory slices allowed */
 } kgm_timing;
 
 int  kgm_abi_version(void);

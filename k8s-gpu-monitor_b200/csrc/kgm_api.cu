@@ -106,6 +106,7 @@ struct kgm_ctx {
   cudaEvent_t ev_in[MAX_CHUNKS] = {}, ev_k[MAX_CHUNKS] = {};
   HostBuf h_chunk;                         // per chunk: totals {lines, bytes} + counters
   uint32_t last_chunks = 1;
+  uint32_t force_teams = 0;                // KGM_FUSED_TEAMS=3|4 (experiments)
   // window reductions
   uint32_t max_tick = 0;
   bool have_ticks = false;
@@ -242,7 +243,7 @@ int launch_pipeline(kgm_ctx *ctx) {
     P.scan_state = ctx->w_scan.as<unsigned long long>();
     P.next_counters = cbase + (1u - cur) * CTR_COUNT;
     const uint32_t n = ctx->batch.n_docs;
-    const int wpb = 4;
+    const int wpb = (int)P.teams;                   // teams (documents in flight) per CTA
     int blocks = (int)((n + wpb - 1) / wpb);
     blocks = std::max(1, std::min(blocks, ctx->sms * ctx->fused_ctas_per_sm));
     ctx->ticket_next += (unsigned long long)n + (unsigned long long)blocks * wpb;
@@ -318,6 +319,7 @@ void fill_timing(kgm_ctx *ctx, bool h2d, bool d2h) {
   t.launches = ctx->last_fused ? 1 : 4;
   t.fused = ctx->last_fused ? 1 : 0;
   t.slow_docs = ctx->slow_docs;
+  t.fused_ctas_per_sm = ctx->last_fused ? (uint32_t)ctx->fused_ctas_per_sm : 0u;
   cudaGetLastError();
 }
 
@@ -367,24 +369,19 @@ int fetch(kgm_ctx *ctx, kgm_result *out) {
 // is used when that covers more of them.
 struct FusedFit { FusedParams P; uint64_t fits; bool ok; };
 
-FusedFit fused_layout(kgm_ctx *ctx, const kgm_batch *b, int ctas, uint64_t max_g, uint64_t max_a) {
+FusedFit fused_layout(kgm_ctx *ctx, const kgm_batch *b, int ctas, uint32_t teams, uint64_t max_g, uint64_t max_a) {
   auto r16 = [](uint64_t v) { return (uint32_t)((v + 15) & ~15ull); };
   FusedFit f{};
   const uint32_t const_pad = (fast::ConstArea::BYTES + 15u) & ~15u;
   const uint32_t dyn_max = ctas == 2 ? 115712u : 232448u;
-  const uint32_t warp_bytes = ((dyn_max - const_pad) / 4) & ~15u;
+  const uint32_t warp_bytes = ((dyn_max - const_pad) / teams) & ~15u;
   const uint64_t need_stage = std::max<uint64_t>(MAX_LINE_BYTES + 64, 12ull * ctx->fleet.max_nc + 16);
   if (need_stage + 4096 > warp_bytes) return f;
   const uint64_t budget = warp_bytes - need_stage;            // texts + template block + tables
-  // the template block gets what it needs up to 40 % of the budget, the texts up to 45 %;
-  // the per-row tables follow the text size, so the two are shrunk until everything fits
-  uint64_t tb = std::min<uint64_t>(r16(ctx->fast_max_tb) + 32, (budget * 40 / 100) & ~15ull);
-  uint64_t g = std::min<uint64_t>(max_g, 8192), a = std::min<uint64_t>(max_a, 60000);
-  const uint64_t text_budget = budget * 45 / 100;
-  if (r16(g + 15) + r16(a + 15) + 96 > text_budget) {
-    g = std::min<uint64_t>(g, text_budget / 4);
-    a = text_budget > r16(g + 15) + 96 + 1024 ? text_budget - r16(g + 15) - 96 - 16 : 1024;
-  }
+  // start from what the batch needs (bounded by what a slice could ever hold); the per-row
+  // tables follow the text size; texts and template block are shrunk until everything fits
+  uint64_t tb = std::min<uint64_t>(r16(ctx->fast_max_tb) + 32, budget * 60 / 100);
+  uint64_t g = std::min<uint64_t>(max_g, 8192), a = std::min<uint64_t>(max_a, budget * 60 / 100);
   FusedParams &P = f.P;
   uint32_t o = 0;
   for (int round = 0; round < 12; ++round) {
@@ -397,6 +394,7 @@ FusedFit fused_layout(kgm_ctx *ctx, const kgm_batch *b, int ctas, uint64_t max_g
     P.cap_t = r16(tb);
     P.cap_lines = P.cap_ng + P.cap_np + std::min(ctx->fast_max_idle, 512u);
     o = 0;
+    P.off_mbox = o; o += 64;
     P.off_tg = o; o += P.cap_g;
     P.off_ta = o; o += P.cap_a;
     P.off_gstart = o; o += r16(2ull * (P.cap_ng + 2));
@@ -419,6 +417,7 @@ FusedFit fused_layout(kgm_ctx *ctx, const kgm_batch *b, int ctas, uint64_t max_g
   if ((uint64_t)o + need_stage > warp_bytes) return f;
   P.warp_bytes = warp_bytes;
   P.stage_bytes = warp_bytes - o;
+  P.teams = teams;
   // how many documents can take the fast path with these caps (same tests as fast_plan)
   for (uint32_t d = 0; d < b->n_docs; ++d) {
     const uint32_t nd = b->doc_node[d];
@@ -436,11 +435,19 @@ FusedFit fused_layout(kgm_ctx *ctx, const kgm_batch *b, int ctas, uint64_t max_g
 void plan_fused(kgm_ctx *ctx, const kgm_batch *b, uint64_t max_g, uint64_t max_a) {
   ctx->fused_ok = false;
   if (b->n_docs == 0) return;
-  const FusedFit two = fused_layout(ctx, b, 2, max_g, max_a);
+  // Four teams per CTA unless the stage of such a slice cannot hold a whole document of this
+  // batch (lines are ~3.4x the text): then the two warps of a team would each compose
+  // half-empty rounds, and three teams with larger slices do better.
+  const uint64_t est_out = (max_g + max_a) * 17 / 5 + 256;
+  FusedFit two = fused_layout(ctx, b, 2, ctx->force_teams ? ctx->force_teams : 4, max_g, max_a);
+  if (!ctx->force_teams && two.ok && two.P.stage_bytes < est_out) {
+    const FusedFit three = fused_layout(ctx, b, 2, 3, max_g, max_a);
+    if (three.ok && three.P.stage_bytes >= est_out && three.fits >= two.fits) two = three;
+  }
   FusedFit pick = two;
   int ctas = 2;
   if (!two.ok || two.fits * 10 < (uint64_t)b->n_docs * 9) {
-    const FusedFit one = fused_layout(ctx, b, 1, max_g, max_a);
+    const FusedFit one = fused_layout(ctx, b, 1, 4, max_g, max_a);
     if (one.ok && (!two.ok || one.fits > two.fits + b->n_docs / 20)) { pick = one; ctas = 1; }
   }
   if (!pick.ok) return;
@@ -690,6 +697,10 @@ int kgm_create(kgm_ctx **out, int device) {
   if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
   if (e != cudaSuccess) { kgm_destroy(ctx); cudaGetLastError(); return KGM_E_CUDA; }
   ctx->sms = prop.multiProcessorCount;
+  if (const char *env = getenv("KGM_FUSED_TEAMS")) {
+    if (!strcmp(env, "3")) ctx->force_teams = 3;
+    else if (!strcmp(env, "4")) ctx->force_teams = 4;
+  }
   if (const char *env = getenv("KGM_PIPELINE")) {
     if (!strcmp(env, "staged")) ctx->pipeline = KGM_PIPELINE_STAGED;
     else if (!strcmp(env, "fused-generic")) ctx->pipeline = KGM_PIPELINE_FUSED_GENERIC;
@@ -975,6 +986,7 @@ int kgm_encode_batch(kgm_ctx *ctx, const kgm_batch *b, int want_host_copy, kgm_r
         ctx->timing.launches = chunks;
         ctx->timing.fused = 1;
         ctx->timing.slow_docs = ctx->slow_docs;
+        ctx->timing.fused_ctas_per_sm = (uint32_t)ctx->fused_ctas_per_sm;
         cudaGetLastError();
       }
       return rc;

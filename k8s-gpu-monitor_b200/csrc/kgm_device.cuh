@@ -75,9 +75,10 @@ struct FusedParams {
   uint32_t cap_c;                // containers per node
   uint32_t cap_t;                // template block
   uint32_t cap_lines;            // lines per document
-  uint32_t warp_bytes, stage_bytes;
+  uint32_t warp_bytes, stage_bytes;   // bytes of a team's slice / of its stage
+  uint32_t teams;                // teams (documents in flight) per CTA: 3 or 4
   uint32_t off_tg, off_ta, off_gstart, off_pstart, off_grec, off_prec, off_cnt, off_cstart, off_plan,
-      off_loff, off_tb, off_stage;
+      off_loff, off_tb, off_stage, off_mbox;
   uint32_t epoch;                // tags the look-back state of this launch
   uint32_t allow_fast;           // 0 = every document takes the generic path (testing)
   unsigned long long ticket_base;

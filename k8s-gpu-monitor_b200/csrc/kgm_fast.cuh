@@ -344,6 +344,12 @@ KGM_HD uint32_t name_len(const PRec &p) {
 // Reads up to 2 words past the run.
 KGM_HD void copy_run(uint32_t *B, uint32_t o, uint32_t so, uint32_t n) {
   uint8_t *Bb = reinterpret_cast<uint8_t *>(B);
+  if (n <= 3u) {                                     // short ids, utilization digits, "-", "0"
+    Bb[o] = Bb[so];
+    if (n > 1) Bb[o + 1] = Bb[so + 1];
+    if (n > 2) Bb[o + 2] = Bb[so + 2];
+    return;
+  }
   uint32_t h = (4u - (o & 3u)) & 3u;
   if (h > n) h = n;
   if (h > 0) Bb[o] = Bb[so];

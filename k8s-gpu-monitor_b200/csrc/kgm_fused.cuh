@@ -25,7 +25,7 @@ namespace {
 
 using namespace fast;
 
-constexpr int POLL_THREADS = 128;                   // 4 independent warps per CTA
+constexpr int POLL_THREADS = 256;                   // at most 4 teams of 2 warps per CTA; a team owns a document
 constexpr uint32_t CONST_PAD = (ConstArea::BYTES + 15u) & ~15u;
 constexpr uint32_t KIND_NODE = 0, KIND_BUSY = 1, KIND_IDLE = 2;
 constexpr uint32_t IDLE_NONE = 0xfffu;
@@ -114,7 +114,7 @@ __device__ void scan_resolve(const FusedParams &P, uint32_t d, uint64_t nl, uint
 
 // ---- fast path -------------------------------------------------------------------------------
 struct WarpSlice {                                   // byte offsets from the CTA's shared memory base
-  uint32_t tg, ta, gstart, pstart, grec, prec, cnt, cstart, plan, loff, tb, stage;
+  uint32_t tg, ta, gstart, pstart, grec, prec, cnt, cstart, plan, loff, tb, stage, mbox;
 };
 
 // Coalesced copy of the 16-byte aligned window that covers text[lo, hi) into shared memory.
@@ -156,22 +156,17 @@ __device__ bool find_rows(const uint32_t *T, uint32_t s, uint32_t e, uint16_t *r
         m[k] = ~(((z & 0x7f7f7f7fu) + 0x7f7f7f7fu) | z) & 0x80808080u;
       }
     }
-    uint32_t c = 0;
+    uint32_t bits = 0;                              // bit i = byte pos+i is a line feed
 #pragma unroll
-    for (int k = 0; k < 8; ++k) c += __popc(m[k]);
+    for (int k = 0; k < 8; ++k) bits |= pack4(m[k]) << (4 * k);
+    const uint32_t c = __popc(bits);
     const uint32_t incl = warp_incl_scan(c);
     uint32_t idx = running + incl - c;
-    if (c) {
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        uint32_t mk = m[k];
-        while (mk) {
-          const uint32_t bit = __ffs(mk) - 1;
-          mk &= mk - 1;
-          if (idx <= cap) row_start[idx] = (uint16_t)(pos + 4u * k + (bit >> 3) + 1u);
-          ++idx;
-        }
-      }
+    while (bits) {
+      const uint32_t bit = __ffs(bits) - 1;
+      bits &= bits - 1;
+      if (idx <= cap) row_start[idx] = (uint16_t)(pos + bit + 1u);
+      ++idx;
     }
     running += __shfl_sync(FULL, incl, 31);
   }
@@ -182,181 +177,248 @@ __device__ bool find_rows(const uint32_t *T, uint32_t s, uint32_t e, uint16_t *r
   return true;
 }
 
-// Plans a regular document.  On success the warp's slice holds the row records, the line
-// plan and the in-document offsets, and (*nl, *nb) are its line and byte counts.
-__device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, const FusedParams &P,
-                          uint32_t *S, uint8_t *Sb, const WarpSlice &ws, uint32_t *o_ng, uint32_t *o_nl,
-                          uint32_t *o_nb) {
+// ---- a document is worked on by a TEAM of two warps -----------------------------------------
+// half 0 owns the --query-gpu side (window, rows, float formatting, template block, container
+// scan, look-back), half 1 the --query-compute-apps side (window, rows, uuid / pid lookups);
+// both compose half of the lines and copy half of the stage out.  The halves meet at named
+// barriers; what they tell each other goes through a small mailbox in the team's slice.
+// Every decision that ends the fast path is taken by both halves from the same mailbox
+// words after a barrier, so the two warps always leave together.
+struct Mailbox {
+  uint32_t ok0, ok1;            // the half's verdict of the current stage (1 = regular so far)
+  uint32_t ng, np;
+  uint32_t nl, nb;
+  uint32_t total0;              // bytes of the lines half 0 measured
+  uint32_t pad;
+  unsigned long long line0, byte0;
+  unsigned long long ticket;
+};
+
+__device__ __forceinline__ void team_sync(uint32_t team) {
+  asm volatile("bar.sync %0, 64;" ::"r"(team + 1u) : "memory");
+}
+
+// pid -> container: how many containers of node n list this pid string, and the first one
+__device__ __forceinline__ void pid_probe(const FleetDev &f, uint32_t n, uint64_t pidkey, uint32_t *nm,
+                                          uint32_t *c_first) {
+  uint32_t h = pid16_hash(pidkey, n) & f.pid16_mask;
+  for (;;) {
+    const uint4 raw = __ldg(reinterpret_cast<const uint4 *>(f.pid16 + h));
+    if (raw.z == NONE32) break;
+    const uint64_t key = ((uint64_t)raw.y << 32) | raw.x;
+    if (raw.z == n && key == pidkey) { if (!*nm) *c_first = raw.w; ++*nm; }
+    h = (h + 1) & f.pid16_mask;
+  }
+}
+
+// Plans a regular document.  On success the team's slice holds the row records, the line
+// plan and the in-document offsets, and the mailbox its line and byte counts.
+__device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, const FusedParams &P, uint32_t *S,
+                          uint8_t *Sb, const WarpSlice &ws, uint32_t team, uint32_t half) {
   const uint32_t l = lane_id();
+  volatile Mailbox *mb = reinterpret_cast<volatile Mailbox *>(Sb + ws.mbox);
   const uint32_t n = b.doc_node[d];
-  if (!f.node_fast[n]) return false;
+  if (!f.node_fast[n]) return false;                 // (both halves read the same words: same verdict)
   const uint64_t g_lo = b.gpu_off[d], g_hi = b.gpu_off[d + 1], a_lo = b.apps_off[d], a_hi = b.apps_off[d + 1];
   const uint32_t tb_len = f.tb_len[n];
   if (((g_hi + 15ull) & ~15ull) - (g_lo & ~15ull) + 32ull > P.cap_g) return false;
   if (((a_hi + 15ull) & ~15ull) - (a_lo & ~15ull) + 32ull > P.cap_a) return false;
   if (tb_len + 16u > P.cap_t || g_hi == g_lo || a_hi == a_lo) return false;
 
-  // ---- texts and the node's template block -> shared memory ----
-  uint32_t gs, ge, as, ae;
-  load_window(b.gpu_csv, g_lo, g_hi, Sb + ws.tg, &gs, &ge);
-  load_window(b.apps_csv, a_lo, a_hi, Sb + ws.ta, &as, &ae);
-  {
-    const uint8_t *src = f.tb_pool + f.tb_off[n];
-    for (uint32_t i = l * 16u; i < tb_len; i += 512u)
-      *reinterpret_cast<uint4 *>(Sb + ws.tb + i) = __ldg(reinterpret_cast<const uint4 *>(src + i));
-  }
-  __syncwarp();
   const uint32_t *TG = S + (ws.tg >> 2), *TA = S + (ws.ta >> 2);
   const TbHeader &hd = *reinterpret_cast<const TbHeader *>(Sb + ws.tb);
   const TbCont *tc = reinterpret_cast<const TbCont *>(Sb + ws.tb + sizeof(TbHeader));
-  const uint32_t nc = hd.nc;
-  if (nc > P.cap_c) return false;
-
   uint16_t *gstart = reinterpret_cast<uint16_t *>(Sb + ws.gstart);
   uint16_t *pstart = reinterpret_cast<uint16_t *>(Sb + ws.pstart);
-  uint32_t ng, np;
-  if (!find_rows(TG, gs, ge, gstart, P.cap_ng, &ng)) return false;
-  if (!find_rows(TA, as, ae, pstart, P.cap_np, &np)) return false;
-  if (ng > 32u) return false;
-
-  // ---- gpu rows: one lane per row (gpu.py:104-109,119-143) ----
   GRec *grec = reinterpret_cast<GRec *>(Sb + ws.grec);
-  uint64_t my_hash = 0;
-  {
-    bool ok = true;
-    if (l < ng) {
-      GRec g;
-      ok = parse_gpu_row(TG, gstart[l], gstart[l + 1] - 1u, hd.fixed, l, g);
-      if (ok) { grec[l] = g; my_hash = g.hash; }
-    }
-    if (!__all_sync(FULL, ok)) return false;
-    bool dup = false;                               // equal keys: last row wins (gpu.py:54) -> generic path
-    for (uint32_t j = 0; j + 1 < ng; ++j) {
-      const uint64_t hj = __shfl_sync(FULL, my_hash, j);
-      dup |= l < ng && j < l && hj == my_hash;
-    }
-    if (__any_sync(FULL, dup)) return false;
-  }
-  __syncwarp();
-
-  // ---- process rows: parse, uuid -> short id (gpu.py:151), pid -> container (gpu.py:177-178) ----
   PRec *prec = reinterpret_cast<PRec *>(Sb + ws.prec);
   uint32_t *cnt = S + (ws.cnt >> 2), *cstart = S + (ws.cstart >> 2);
-  for (uint32_t c = l; c < nc; c += 32) cnt[c] = 0;
-  __syncwarp();
-  for (uint32_t r0 = 0; r0 < np; r0 += 32) {
-    const uint32_t r = r0 + l;
-    const bool valid = r < np;
-    bool ok = true;
-    PRec p;
-    uint32_t emit_c = NONE32;
-    if (valid) {
-      uint32_t kw[KEY_WORDS], klen;
-      uint64_t kh;
-      ok = parse_proc_row(TA, pstart[r], pstart[r + 1] - 1u, p, kw, &klen, &kh);
-      if (ok) {
-        uint32_t sid = NONE32;
-        for (uint32_t j = 0; j < ng && sid == NONE32; ++j) {
-          if (grec[j].hash == kh && grec[j].key.len == klen) {
-            bool eq = true;
+  uint32_t *plan = S + (ws.plan >> 2), *loff = S + (ws.loff >> 2);
+
+  // ---- stage A: windows -> shared memory, rows; half 0 also parses the gpu rows ----
+  if (half == 0) {
+    uint32_t gs, ge, ng = 0;
+    load_window(b.gpu_csv, g_lo, g_hi, Sb + ws.tg, &gs, &ge);
+    {
+      const uint8_t *src = f.tb_pool + f.tb_off[n];
+      for (uint32_t i = l * 16u; i < tb_len; i += 512u)
+        *reinterpret_cast<uint4 *>(Sb + ws.tb + i) = __ldg(reinterpret_cast<const uint4 *>(src + i));
+    }
+    __syncwarp();
+    bool ok = hd.nc <= P.cap_c && find_rows(TG, gs, ge, gstart, P.cap_ng, &ng) && ng <= 32u;
+    if (ok) {                                        // one lane per gpu row (gpu.py:104-109,119-143)
+      uint64_t my_hash = 0;
+      bool rok = true;
+      if (l < ng) {
+        GRec g;
+        rok = parse_gpu_row(TG, gstart[l], gstart[l + 1] - 1u, hd.fixed, l, g);
+        if (rok) { grec[l] = g; my_hash = g.hash; }
+      }
+      bool dup = false;                              // equal keys: last row wins (gpu.py:54) -> generic path
+      for (uint32_t j = 0; j + 1 < ng; ++j) {
+        const uint64_t hj = __shfl_sync(FULL, my_hash, j);
+        dup |= l < ng && j < l && hj == my_hash;
+      }
+      ok = __all_sync(FULL, rok) && !__any_sync(FULL, dup);
+      for (uint32_t c = l; c < hd.nc && ok; c += 32) cnt[c] = 0;
+    }
+    if (l == 0) { mb->ok0 = ok ? 1u : 0u; mb->ng = ng; }
+  }
+  // half 1: window, rows, and the parse of the first 32 process rows -- none of it needs
+  // the gpu side, so it runs while half 0 is still formatting floats
+  PRec p0;                                           // (half 1) row `l` of the first chunk
+  uint32_t kw0[KEY_WORDS], klen0 = 0, np_local = 0;
+  uint64_t kh0 = 0;
+  uint32_t nm0 = 0, cfirst0 = NONE32;
+  if (half == 1) {
+    uint32_t as, ae;
+    load_window(b.apps_csv, a_lo, a_hi, Sb + ws.ta, &as, &ae);
+    bool ok = find_rows(TA, as, ae, pstart, P.cap_np, &np_local);
+    if (ok) {
+      bool rok = true;
+      if (l < np_local) {
+        rok = parse_proc_row(TA, pstart[l], pstart[l + 1] - 1u, p0, kw0, &klen0, &kh0);
+        if (rok && p0.pidkey != ~0ull) pid_probe(f, n, p0.pidkey, &nm0, &cfirst0);
+      }
+      ok = __all_sync(FULL, rok);
+    }
+    if (l == 0) { mb->ok1 = ok ? 1u : 0u; mb->np = np_local; }
+  }
+  team_sync(team);
+  if (!(mb->ok0 & mb->ok1)) return false;
+  const uint32_t ng = mb->ng, np = mb->np, nc = hd.nc;
+  team_sync(team);                                   // the mailbox may be rewritten now
+
+  // ---- stage B (half 1): uuid -> short id (gpu.py:151), pid -> container (gpu.py:177-178),
+  //      place inside the container; further chunks of 32 rows are parsed here as well ----
+  if (half == 1) {
+    bool all_ok = true;
+    for (uint32_t r0 = 0; r0 < np && all_ok; r0 += 32) {
+      const uint32_t r = r0 + l;
+      const bool valid = r < np;
+      bool ok = true;
+      PRec p;
+      uint32_t kw[KEY_WORDS], klen = 0, nm = 0, c_first = NONE32;
+      uint64_t kh = 0;
+      if (r0 == 0) {
+        p = p0; klen = klen0; kh = kh0; nm = nm0; c_first = cfirst0;
 #pragma unroll
-            for (int i = 0; i < KEY_WORDS; ++i) eq &= grec[j].keyw[i] == kw[i];
-            if (eq) sid = j;
-          }
+        for (int i = 0; i < KEY_WORDS; ++i) kw[i] = kw0[i];
+      } else if (valid) {
+        ok = parse_proc_row(TA, pstart[r], pstart[r + 1] - 1u, p, kw, &klen, &kh);
+        if (ok && p.pidkey != ~0ull) pid_probe(f, n, p.pidkey, &nm, &c_first);
+      }
+      uint32_t emit_c = NONE32;
+      if (valid && ok) {
+        // first gpu row with this hash and length; the bytes are compared once, afterwards
+        uint32_t sid = NONE32;
+        for (uint32_t j = 0; j < ng && sid == NONE32; ++j)
+          if (grec[j].hash == kh && grec[j].key.len == klen) sid = j;
+        bool eq = sid != NONE32;                    // no such uuid: KeyError gpu.py:151
+        if (eq) {
+#pragma unroll
+          for (int i = 0; i < KEY_WORDS; ++i) eq &= grec[sid].keyw[i] == kw[i];
         }
-        if (sid == NONE32) ok = false;              // KeyError gpu.py:151
+        ok = eq;                                    // (a hash collision also goes to the generic path)
         p.sid = (uint16_t)sid;
         if (ok && p.pidkey != ~0ull) {
-          uint32_t nm = 0, c_first = NONE32;
-          uint32_t h = pid16_hash(p.pidkey, n) & f.pid16_mask;
-          for (;;) {
-            const uint4 raw = __ldg(reinterpret_cast<const uint4 *>(f.pid16 + h));
-            if (raw.z == NONE32) break;
-            const uint64_t key = ((uint64_t)raw.y << 32) | raw.x;
-            if (raw.z == n && key == p.pidkey) { if (!nm) c_first = raw.w; ++nm; }
-            h = (h + 1) & f.pid16_mask;
-          }
           if (nm > 1) ok = false;                   // a pid listed by several containers
           if (nm == 1 && c_first < nc && tc[c_first].gated) emit_c = c_first;
           p.digest = pair_digest(p.pidkey, p.pid.len, sid);
         }
       }
+      all_ok = __all_sync(FULL, ok);
+      if (!all_ok) break;
+      // duplicate (pid, gpu) keys keep the first row's place and the last row's values
+      // (gpu.py:54): screened by digest, any hit goes to the generic path
+      const bool screened = valid && p.pidkey != ~0ull;
+      const uint32_t act = __ballot_sync(FULL, screened);
+      bool dup = false;
+      if (screened) {
+        dup = __popc(__match_any_sync(act, p.digest)) > 1;
+        for (uint32_t j = 0; j < r0 && !dup; ++j) dup = prec[j].pidkey != ~0ull && prec[j].digest == p.digest;
+      }
+      if (__any_sync(FULL, dup)) { all_ok = false; break; }
+      // place inside the container: rank among the earlier rows of the same container
+      const uint32_t emitting = __ballot_sync(FULL, emit_c != NONE32);
+      uint32_t pos = 0;
+      if (emit_c != NONE32) {
+        const uint32_t peers = __match_any_sync(emitting, emit_c);
+        const int leader = __ffs(peers) - 1;
+        uint32_t base = 0;
+        if ((int)l == leader) { base = cnt[emit_c]; cnt[emit_c] = base + __popc(peers); }
+        base = __shfl_sync(peers, base, leader);
+        pos = base + __popc(peers & lanemask_lt());
+      }
+      if (valid) {
+        p.crank = (uint16_t)(emit_c == NONE32 ? 0xffffu : emit_c);
+        p.pos = (uint16_t)pos;
+        prec[r] = p;
+      }
+      __syncwarp();
     }
-    if (!__all_sync(FULL, ok)) return false;
-    // duplicate (pid, gpu) keys keep the first row's place and the last row's values
-    // (gpu.py:54): screened by digest, any hit goes to the generic path
-    const bool screened = valid && p.pidkey != ~0ull;
-    const uint32_t act = __ballot_sync(FULL, screened);
-    bool dup = false;
-    if (screened) {
-      dup = __popc(__match_any_sync(act, p.digest)) > 1;
-      for (uint32_t j = 0; j < r0 && !dup; ++j) dup = prec[j].pidkey != ~0ull && prec[j].digest == p.digest;
-    }
-    if (__any_sync(FULL, dup)) return false;
-    // place inside the container: rank among the earlier rows of the same container
-    const uint32_t emitting = __ballot_sync(FULL, emit_c != NONE32);
-    uint32_t pos = 0;
-    if (emit_c != NONE32) {
-      const uint32_t peers = __match_any_sync(emitting, emit_c);
-      const int leader = __ffs(peers) - 1;
-      uint32_t base = 0;
-      if ((int)l == leader) { base = cnt[emit_c]; cnt[emit_c] = base + __popc(peers); }
-      base = __shfl_sync(peers, base, leader);
-      pos = base + __popc(peers & lanemask_lt());
-    }
-    if (valid) {
-      p.crank = (uint16_t)(emit_c == NONE32 ? 0xffffu : emit_c);
-      p.pos = (uint16_t)pos;
-      prec[r] = p;
-    }
-    __syncwarp();
+    if (l == 0) mb->ok1 = all_ok ? 1u : 0u;
   }
+  team_sync(team);
+  if (!mb->ok1) return false;
 
-  // ---- containers in docker stats order: busy lines, or idle lines (gpu.py:174-253) ----
-  uint32_t total_pod = 0;
-  for (uint32_t c0 = 0; c0 < nc; c0 += 32) {
-    const uint32_t c = c0 + l;
-    uint32_t lines = 0;
-    if (c < nc && tc[c].gated) lines = cnt[c] ? cnt[c] : tc[c].nvis;
-    const uint32_t incl = warp_incl_scan(lines);
-    if (c < nc) cstart[c] = total_pod + incl - lines;
-    total_pod += __shfl_sync(FULL, incl, 31);
-  }
-  const uint32_t nl = ng + total_pod;
-  if (nl > P.cap_lines) return false;
-  __syncwarp();
-  uint32_t *plan = S + (ws.plan >> 2), *loff = S + (ws.loff >> 2);
-  if (l < ng) plan[l] = (KIND_NODE << 30) | l;
-  for (uint32_t r = l; r < np; r += 32) {
-    const PRec &p = prec[r];
-    if (p.crank != 0xffffu) plan[ng + cstart[p.crank] + p.pos] = (KIND_BUSY << 30) | r;
-  }
-  for (uint32_t c = l; c < nc; c += 32) {
-    if (!tc[c].gated || cnt[c]) continue;
-    for (uint32_t v = 0; v < tc[c].nvis; ++v) {      // uuids visible inside an idle container (gpu.py:221-226)
-      const uint32_t gv = tc[c].vis_begin + v;
-      const uint64_t vh = f.vis_hash2[gv];
-      const uint32_t vo = f.vis_off[gv], vlen = f.vis_off[gv + 1] - vo;
-      uint32_t sid = IDLE_NONE;
-      for (uint32_t j = 0; j < ng && sid == IDLE_NONE; ++j) {
-        if (grec[j].hash == vh && grec[j].key.len == vlen) {
-          bool eq = true;
-          for (uint32_t i = 0; i < vlen; ++i) eq &= f.vis_bytes[vo + i] == load1(TG, grec[j].key.off + i);
-          if (eq) sid = j;
+  // ---- stage C (half 0): containers in docker stats order: busy lines, or idle lines
+  //      (gpu.py:174-253); node entries and idle entries of the plan ----
+  if (half == 0) {
+    uint32_t total_pod = 0;
+    for (uint32_t c0 = 0; c0 < nc; c0 += 32) {
+      const uint32_t c = c0 + l;
+      uint32_t lines = 0;
+      if (c < nc && tc[c].gated) lines = cnt[c] ? cnt[c] : tc[c].nvis;
+      const uint32_t incl = warp_incl_scan(lines);
+      if (c < nc) cstart[c] = total_pod + incl - lines;
+      total_pod += __shfl_sync(FULL, incl, 31);
+    }
+    const uint32_t nl = ng + total_pod;
+    if (l == 0) { mb->nl = nl; mb->ok0 = nl <= P.cap_lines ? 1u : 0u; }
+    __syncwarp();
+    if (nl <= P.cap_lines) {
+      if (l < ng) plan[l] = (KIND_NODE << 30) | l;
+      for (uint32_t c = l; c < nc; c += 32) {
+        if (!tc[c].gated || cnt[c]) continue;
+        for (uint32_t v = 0; v < tc[c].nvis; ++v) {  // uuids visible inside an idle container (gpu.py:221-226)
+          const uint32_t gv = tc[c].vis_begin + v;
+          const uint64_t vh = f.vis_hash2[gv];
+          const uint32_t vo = f.vis_off[gv], vlen = f.vis_off[gv + 1] - vo;
+          uint32_t sid = IDLE_NONE;
+          for (uint32_t j = 0; j < ng && sid == IDLE_NONE; ++j) {
+            if (grec[j].hash == vh && grec[j].key.len == vlen) {
+              bool eq = true;
+              for (uint32_t i = 0; i < vlen; ++i) eq &= f.vis_bytes[vo + i] == load1(TG, grec[j].key.off + i);
+              if (eq) sid = j;
+            }
+          }
+          plan[ng + cstart[c] + v] = (KIND_IDLE << 30) | (c << 12) | sid;
         }
       }
-      plan[ng + cstart[c] + v] = (KIND_IDLE << 30) | (c << 12) | sid;
     }
   }
-  __syncwarp();
+  team_sync(team);
+  if (!mb->ok0) return false;
+  const uint32_t nl = mb->nl;
+  if (half == 1) {                                   // busy entries (needs cstart)
+    for (uint32_t r = l; r < np; r += 32) {
+      const PRec &p = prec[r];
+      if (p.crank != 0xffffu) plan[ng + cstart[p.crank] + p.pos] = (KIND_BUSY << 30) | r;
+    }
+  }
+  team_sync(team);
 
-  // ---- line lengths -> offsets inside the document ----
+  // ---- stage D: line lengths -> offsets inside the document; each half measures half of
+  //      the lines, half 1 then shifts its offsets by half 0's bytes ----
+  const uint32_t mid = (nl + 1u) >> 1;
+  const uint32_t lo_i = half ? mid : 0u, hi_i = half ? nl : mid;
   uint32_t nb = 0;
   bool too_long = false;
-  for (uint32_t i0 = 0; i0 < nl; i0 += 32) {
+  for (uint32_t i0 = lo_i; i0 < hi_i; i0 += 32) {
     const uint32_t i = i0 + l;
     uint32_t len = 0;
-    if (i < nl) {
+    if (i < hi_i) {
       const uint32_t pl = plan[i], kind = pl >> 30;
       if (kind == KIND_NODE) {
         len = grec[pl & 0xffffu].line_len;
@@ -370,51 +432,59 @@ __device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, cons
       too_long |= len > MAX_LINE_BYTES;
     }
     const uint32_t incl = warp_incl_scan(len);
-    if (i < nl) loff[i] = nb + incl - len;
+    if (i < hi_i) loff[i] = nb + incl - len;
     nb += __shfl_sync(FULL, incl, 31);
   }
-  if (l == 0) loff[nl] = nb;
-  if (__any_sync(FULL, too_long)) return false;
-  __syncwarp();
-  *o_ng = ng; *o_nl = nl; *o_nb = nb;
+  too_long = __any_sync(FULL, too_long);
+  if (l == 0) {
+    if (half == 0) { mb->total0 = nb; mb->ok0 = too_long ? 0u : 1u; }
+    else { mb->nb = nb; mb->ok1 = too_long ? 0u : 1u; }
+  }
+  team_sync(team);
+  if (!(mb->ok0 & mb->ok1)) return false;
+  const uint32_t total0 = mb->total0, total = total0 + mb->nb;
+  if (half == 1) {
+    for (uint32_t i = lo_i + l; i < hi_i; i += 32) loff[i] += total0;
+    if (l == 0) loff[nl] = total;
+  }
+  team_sync(team);
+  if (half == 0 && l == 0) { mb->nb = total; }
+  team_sync(team);
   return true;
 }
 
 // Writes the planned lines of a regular document.  Lines are composed into the stage from
-// its start (whatever the global alignment will be); the copy to global memory realigns
-// them: byte stores up to the first 16-byte boundary of the destination, then 16-byte
-// stores assembled from five shared-memory words each, byte stores for the tail.  The
-// document's position in the output is only needed for that copy, so the look-back that
-// yields it (scan_resolve) runs after the first round of lines has been composed.
+// its start (whatever the global alignment will be), half of a round's lines by each warp
+// of the team; the copy to global memory realigns them: byte stores up to the first 16-byte
+// boundary of the destination, then 16-byte stores assembled from five shared-memory words
+// each, byte stores for the tail.  The document's position in the output is only needed for
+// that copy, so the look-back that yields it (scan_resolve, half 0) runs after the first
+// round of lines has been composed.
 __device__ void fast_emit(const FusedParams &P, const WorkDev &w, uint32_t *S, uint8_t *Sb, const WarpSlice &ws,
-                          uint32_t d, uint32_t n_docs, uint32_t nl, uint32_t nb) {
+                          uint32_t team, uint32_t half, uint32_t d, uint32_t n_docs, uint32_t nl, uint32_t nb) {
   const uint32_t l = lane_id();
+  volatile Mailbox *mb = reinterpret_cast<volatile Mailbox *>(Sb + ws.mbox);
   const TbHeader &hd = *reinterpret_cast<const TbHeader *>(Sb + ws.tb);
   const TbCont *tc = reinterpret_cast<const TbCont *>(Sb + ws.tb + sizeof(TbHeader));
   const GRec *grec = reinterpret_cast<const GRec *>(Sb + ws.grec);
   const PRec *prec = reinterpret_cast<const PRec *>(Sb + ws.prec);
   const uint32_t *plan = S + (ws.plan >> 2), *loff = S + (ws.loff >> 2);
-  // rounds of equal size: as few as the stage allows, at most 32 lines each
-  uint32_t rounds = max((nl + 31u) / 32u, (nb + P.stage_bytes - 64u - 1u) / (P.stage_bytes - 64u));
-  uint32_t per = rounds ? (nl + rounds - 1u) / rounds : 0u;
+  // rounds of equal size: as few as the stage allows, at most 64 lines (32 per warp) each
+  const uint32_t rounds = max((nl + 63u) / 64u, (nb + P.stage_bytes - 64u - 1u) / (P.stage_bytes - 64u));
+  const uint32_t per = rounds ? (nl + rounds - 1u) / rounds : 0u;
   uint64_t line0 = 0, byte0 = 0;
   bool resolved = false, fits_out = true;
   uint32_t i0 = 0;
   do {
-    // the next `per` lines, fewer if their bytes exceed the stage
     uint32_t i1 = min(nl, i0 + per);
     uint32_t r_lo = 0;
     if (nl) {
       r_lo = loff[i0];
-      const uint32_t cand = i0 + l + 1;
-      const bool fits = cand <= i1 && loff[cand] - r_lo + 64u <= P.stage_bytes;
-      i1 = i0 + __popc(__ballot_sync(FULL, fits));
-      if (i1 == i0) {                               // cannot happen: the stage holds any single line
-        if (!resolved) scan_resolve(P, d, nl, nb, &line0, &byte0);
-        return;
-      }
-      const uint32_t i = i0 + l;
-      if (i < i1) {
+      // the next `per` lines, fewer if their bytes exceed the stage (both warps compute the same)
+      while (i1 > i0 + 1 && loff[i1] - r_lo + 64u > P.stage_bytes) i1 = i0 + ((i1 - i0) >> 1);
+      const uint32_t cnt = i1 - i0, first = half ? (cnt + 1u) >> 1 : 0u, last = half ? cnt : (cnt + 1u) >> 1;
+      const uint32_t i = i0 + first + l;
+      if (i < i0 + last) {
         const uint32_t pl = plan[i], kind = pl >> 30;
         Seg segs[MAX_SEGS];
         if (kind == KIND_NODE) {
@@ -432,40 +502,46 @@ __device__ void fast_emit(const FusedParams &P, const WorkDev &w, uint32_t *S, u
       }
     }
     if (!resolved) {
-      scan_resolve(P, d, nl, nb, &line0, &byte0);
-      if (P.carry) { line0 += P.carry[0]; byte0 += P.carry[1]; }
+      if (half == 0) {
+        scan_resolve(P, d, nl, nb, &line0, &byte0);
+        if (P.carry) { line0 += P.carry[0]; byte0 += P.carry[1]; }
+        if (l == 0) {
+          mb->line0 = line0; mb->byte0 = byte0;
+          w.doc_line_off[d] = line0;
+          w.doc_byte_off[d] = byte0;
+          w.doc_status[d] = 0; w.doc_nlines[d] = nl; w.doc_nbytes[d] = nb;
+          if (d + 1 == n_docs) {
+            w.doc_line_off[n_docs] = line0 + nl;
+            w.doc_byte_off[n_docs] = byte0 + nb;
+            w.totals[0] = line0 + nl;
+            w.totals[1] = byte0 + nb;
+            w.line_off[min(line0 + nl, (uint64_t)w.desc_cap)] = byte0 + nb;
+          }
+          if (byte0 + nb > w.out_cap || line0 + nl > w.desc_cap)
+            atomicOr(w.counters + CTR_OVERFLOW, (byte0 + nb > w.out_cap ? OVF_OUT : 0u) |
+                                                    (line0 + nl > w.desc_cap ? OVF_DESC : 0u));
+        }
+      }
+      team_sync(team);                               // lines composed, position known
+      line0 = mb->line0; byte0 = mb->byte0;
       resolved = true;
       fits_out = byte0 + nb <= w.out_cap && line0 + nl <= w.desc_cap;
-      if (l == 0) {
-        w.doc_line_off[d] = line0;
-        w.doc_byte_off[d] = byte0;
-        w.doc_status[d] = 0; w.doc_nlines[d] = nl; w.doc_nbytes[d] = nb;
-        if (d + 1 == n_docs) {
-          w.doc_line_off[n_docs] = line0 + nl;
-          w.doc_byte_off[n_docs] = byte0 + nb;
-          w.totals[0] = line0 + nl;
-          w.totals[1] = byte0 + nb;
-          w.line_off[min(line0 + nl, (uint64_t)w.desc_cap)] = byte0 + nb;
-        }
-        if (!fits_out)
-          atomicOr(w.counters + CTR_OVERFLOW, (byte0 + nb > w.out_cap ? OVF_OUT : 0u) |
-                                                  (line0 + nl > w.desc_cap ? OVF_DESC : 0u));
-      }
+    } else {
+      team_sync(team);                               // lines of this round composed
     }
-    __syncwarp();
     if (!fits_out || nl == 0) return;
-    if (i0 + l < i1) w.line_off[line0 + i0 + l] = byte0 + loff[i0 + l];
-    // stage -> global
+    for (uint32_t i = i0 + 32u * half + l; i < i1; i += 64u) w.line_off[line0 + i] = byte0 + loff[i];
+    // stage -> global, the vectors dealt alternately to the two warps
     const uint32_t nbytes = loff[i1] - r_lo;
     uint8_t *g = w.out + byte0 + r_lo;
     const uint8_t *st = Sb + ws.stage;
     const uint32_t head = min(nbytes, (uint32_t)((16u - ((byte0 + r_lo) & 15ull)) & 15u));
-    if (l < head) g[l] = st[l];
+    if (half == 0 && l < head) g[l] = st[l];
     const uint32_t nvec = (nbytes - head) >> 4;
     {
       const uint32_t *sw = S + ((ws.stage + head) >> 2);     // stage word holding byte `head`
       const uint32_t sh = 8u * (head & 3u);
-      for (uint32_t v = l; v < nvec; v += 32) {
+      for (uint32_t v = 32u * half + l; v < nvec; v += 64u) {
         const uint32_t *q = sw + 4u * v;
         const uint32_t a0 = q[0], a1 = q[1], a2 = q[2], a3 = q[3], a4 = q[4];
         uint4 o;
@@ -475,9 +551,9 @@ __device__ void fast_emit(const FusedParams &P, const WorkDev &w, uint32_t *S, u
       }
     }
     const uint32_t done = head + 16u * nvec;
-    if (l < nbytes - done) g[done + l] = st[done + l];
-    __syncwarp();
+    if (half == 1 && l < nbytes - done) g[done + l] = st[done + l];
     i0 = i1;
+    team_sync(team);                                 // the stage may be overwritten
   } while (i0 < nl);
 }
 
@@ -532,72 +608,79 @@ __global__ void __launch_bounds__(POLL_THREADS, 2) k_poll(BatchDev b, FleetDev f
   extern __shared__ __align__(16) uint32_t S[];
   uint8_t *Sb = reinterpret_cast<uint8_t *>(S);
   // constant strings (same for every CTA)
-  for (uint32_t i = threadIdx.x; i < CONST_PAD / 4; i += POLL_THREADS) S[i] = 0;
+  for (uint32_t i = threadIdx.x; i < CONST_PAD / 4; i += blockDim.x) S[i] = 0;
   __syncthreads();
   if (threadIdx.x == 0) fill_const_strings(Sb);
-  for (uint32_t v = threadIdx.x; v <= MAX_FAST_SID; v += POLL_THREADS) fill_const_decimal(Sb, v);
+  for (uint32_t v = threadIdx.x; v <= MAX_FAST_SID; v += blockDim.x) fill_const_decimal(Sb, v);
   // the counters of the NEXT launch start from zero (this launch uses the other set)
   if (blockIdx.x == 0 && threadIdx.x < CTR_COUNT) P.next_counters[threadIdx.x] = 0;
   __syncthreads();
 
-  const uint32_t wib = threadIdx.x >> 5, l = lane_id();
-  const uint32_t base = CONST_PAD + wib * P.warp_bytes;
+  const uint32_t team = threadIdx.x >> 6, half = (threadIdx.x >> 5) & 1u, l = lane_id();
+  const uint32_t base = CONST_PAD + team * P.warp_bytes;
   WarpSlice ws;
   ws.tg = base + P.off_tg; ws.ta = base + P.off_ta; ws.gstart = base + P.off_gstart;
   ws.pstart = base + P.off_pstart; ws.grec = base + P.off_grec; ws.prec = base + P.off_prec;
   ws.cnt = base + P.off_cnt; ws.cstart = base + P.off_cstart; ws.plan = base + P.off_plan;
   ws.loff = base + P.off_loff; ws.tb = base + P.off_tb; ws.stage = base + P.off_stage;
+  ws.mbox = base + P.off_mbox;
+  volatile Mailbox *mb = reinterpret_cast<volatile Mailbox *>(Sb + ws.mbox);
 
   for (;;) {
-    unsigned long long t = 0;
-    if (l == 0) t = atomicAdd(P.ticket, 1ull) - P.ticket_base;
-    t = __shfl_sync(FULL, t, 0);
+    if (half == 0 && l == 0) mb->ticket = atomicAdd(P.ticket, 1ull) - P.ticket_base;
+    team_sync(team);
+    const unsigned long long t = mb->ticket;
     if (t >= b.n_docs) break;
     const uint32_t d = (uint32_t)t;
-    uint32_t ng = 0, nl = 0, nb = 0;
-    const bool fastdoc = P.allow_fast && fast_plan(d, b, f, P, S, Sb, ws, &ng, &nl, &nb);
-    __syncwarp();
+    const bool fastdoc = P.allow_fast && fast_plan(d, b, f, P, S, Sb, ws, team, half);
     if (fastdoc) {
+      const uint32_t nl = mb->nl, nb = mb->nb;
+      team_sync(team);
+      if (half == 0) scan_publish(P, d, nl, nb);
+      fast_emit(P, w, S, Sb, ws, team, half, d, b.n_docs, nl, nb);
+      team_sync(team);
+      continue;
+    }
+    team_sync(team);                                 // both halves have left the fast path
+    if (half == 0) {                                 // the generic path is one warp's work
+      uint32_t nl = 0, nb = 0;
+      slow_plan(d, b, f, w, S + (ws.stage >> 2), &nl, &nb);
+      if (l == 0) atomicAdd(w.counters + CTR_SLOW, 1u);
       scan_publish(P, d, nl, nb);
-      fast_emit(P, w, S, Sb, ws, d, b.n_docs, nl, nb);
-      __syncwarp();
-      continue;
-    }
-    slow_plan(d, b, f, w, S + (ws.stage >> 2), &nl, &nb);
-    if (l == 0) atomicAdd(w.counters + CTR_SLOW, 1u);
-    scan_publish(P, d, nl, nb);
-    uint64_t line0, byte0;
-    scan_resolve(P, d, nl, nb, &line0, &byte0);
-    if (P.carry) { line0 += P.carry[0]; byte0 += P.carry[1]; }
-    if (l == 0) {
-      w.doc_line_off[d] = line0;
-      w.doc_byte_off[d] = byte0;
-      if (d + 1 == b.n_docs) {
-        w.doc_line_off[b.n_docs] = line0 + nl;
-        w.doc_byte_off[b.n_docs] = byte0 + nb;
-        w.totals[0] = line0 + nl;
-        w.totals[1] = byte0 + nb;
-        w.line_off[min(line0 + nl, (uint64_t)w.desc_cap)] = byte0 + nb;
+      uint64_t line0, byte0;
+      scan_resolve(P, d, nl, nb, &line0, &byte0);
+      if (P.carry) { line0 += P.carry[0]; byte0 += P.carry[1]; }
+      if (l == 0) {
+        w.doc_line_off[d] = line0;
+        w.doc_byte_off[d] = byte0;
+        if (d + 1 == b.n_docs) {
+          w.doc_line_off[b.n_docs] = line0 + nl;
+          w.doc_byte_off[b.n_docs] = byte0 + nb;
+          w.totals[0] = line0 + nl;
+          w.totals[1] = byte0 + nb;
+          w.line_off[min(line0 + nl, (uint64_t)w.desc_cap)] = byte0 + nb;
+        }
       }
+      if (byte0 + nb > w.out_cap || line0 + nl > w.desc_cap) {
+        if (l == 0) atomicOr(w.counters + CTR_OVERFLOW, (byte0 + nb > w.out_cap ? OVF_OUT : 0u) |
+                                                         (line0 + nl > w.desc_cap ? OVF_DESC : 0u));
+      } else {
+        slow_emit(d, b, f, w, nl, line0, byte0);
+      }
+      __syncwarp();
     }
-    if (byte0 + nb > w.out_cap || line0 + nl > w.desc_cap) {
-      if (l == 0) atomicOr(w.counters + CTR_OVERFLOW, (byte0 + nb > w.out_cap ? OVF_OUT : 0u) |
-                                                       (line0 + nl > w.desc_cap ? OVF_DESC : 0u));
-      continue;
-    }
-    slow_emit(d, b, f, w, nl, line0, byte0);
-    __syncwarp();
+    team_sync(team);
   }
 }
 
 }  // namespace
 
-int poll_smem_bytes(const FusedParams &P) { return (int)(CONST_PAD + (POLL_THREADS / 32) * P.warp_bytes); }
+int poll_smem_bytes(const FusedParams &P) { return (int)(CONST_PAD + P.teams * P.warp_bytes); }
 
 void launch_poll(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P, int blocks,
                  cudaStream_t s) {
   cudaFuncSetAttribute(k_poll, cudaFuncAttributeMaxDynamicSharedMemorySize, poll_smem_bytes(P));
-  k_poll<<<blocks, POLL_THREADS, poll_smem_bytes(P), s>>>(b, f, w, P);
+  k_poll<<<blocks, 64 * P.teams, poll_smem_bytes(P), s>>>(b, f, w, P);
 }
 
 }  // namespace kgm

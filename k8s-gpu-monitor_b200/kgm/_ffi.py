@@ -86,7 +86,7 @@ class KgmTiming(C.Structure):
         ("h2d_ms", C.c_float), ("tokenize_ms", C.c_float), ("join_ms", C.c_float),
         ("scan_ms", C.c_float), ("encode_ms", C.c_float), ("d2h_ms", C.c_float),
         ("total_ms", C.c_float), ("launches", C.c_uint32), ("fused", C.c_uint32),
-        ("slow_docs", C.c_uint32),
+        ("slow_docs", C.c_uint32), ("fused_ctas_per_sm", C.c_uint32),
     ]
 
 

@@ -36,5 +36,5 @@ def test_version_strings_and_struct_layout_without_a_gpu():
     assert C.sizeof(_ffi.KgmStrings) == 16
     assert C.sizeof(_ffi.KgmBatch) == 56
     assert C.sizeof(_ffi.KgmResult) == 56
-    assert C.sizeof(_ffi.KgmTiming) == 40
+    assert C.sizeof(_ffi.KgmTiming) == 44
     assert C.sizeof(_ffi.KgmFleet) == 8 + 16 + 8 * 3 + 8 + 8 * 3 + 16 * 4 + 8 + 16 + 8 + 16
