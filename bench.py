@@ -261,9 +261,8 @@ def run_kgm_arm(args):
             local = shard.tensor_of_device_buffer(r.lines, max(int(r.n_bytes), 1), device)
             gather.start(local, int(r.n_bytes), int(r.n_lines))
         if timed:
-            t = mon.timing()
-            for k in keys:
-                acc[k].append(t[k])
+            for k, v in zip(keys, mon.kernel_times()):
+                acc[k].append(v)
             done_samples += samples_step[i % ROTATE]
 
     for i in range(args.warmup):

@@ -101,6 +101,7 @@ struct kgm_ctx {
   std::vector<uint32_t> h_tb_len;
   uint32_t slow_docs = 0;
   bool last_fused = false;
+  bool totals_external = false;            // chunked path: every chunk has its own totals slot
   // chunked end-to-end path: copies and kernels of consecutive chunks overlap
   cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
   cudaEvent_t ev_in[MAX_CHUNKS] = {}, ev_k[MAX_CHUNKS] = {};
@@ -172,9 +173,9 @@ int ensure_workspace(kgm_ctx *ctx) {
   CU(ctx->w_line_off.ensure(((size_t)ctx->desc_cap + 1) * sizeof(uint64_t)));
   {
     const size_t before = ctx->w_counters.cap;
-    CU(ctx->w_counters.ensure(2 * CTR_COUNT * sizeof(uint32_t)));
+    CU(ctx->w_counters.ensure(2 * CTR_SET * sizeof(uint32_t)));
     if (ctx->w_counters.cap != before) {
-      CU(cudaMemsetAsync(ctx->w_counters.p, 0, 2 * CTR_COUNT * sizeof(uint32_t), ctx->stream));
+      CU(cudaMemsetAsync(ctx->w_counters.p, 0, 2 * CTR_SET * sizeof(uint32_t), ctx->stream));
       ctx->counters_clean = true;
     }
     const size_t tb = ctx->w_ticket.cap;
@@ -209,7 +210,7 @@ int ensure_workspace(kgm_ctx *ctx) {
   w.doc_status = ctx->w_status.as<int32_t>();
   w.doc_line_off = ctx->w_doc_line_off.as<uint64_t>();
   w.doc_byte_off = ctx->w_doc_byte_off.as<uint64_t>();
-  w.totals = ctx->w_totals.as<uint64_t>();
+  w.totals = ctx->w_totals.as<uint64_t>();           // launch_pipeline points it into the counter set
   w.line_off = ctx->w_line_off.as<uint64_t>();
   w.out = ctx->w_out.as<uint8_t>(); w.out_cap = ctx->out_cap;
   return KGM_OK;
@@ -232,24 +233,22 @@ int launch_pipeline(kgm_ctx *ctx) {
       CU(cudaMemsetAsync(ctx->w_scan.p, 0, ctx->w_scan.cap, ctx->stream));
     }
     if (!ctx->counters_clean)
-      CU(cudaMemsetAsync(cbase, 0, 2 * CTR_COUNT * sizeof(uint32_t), ctx->stream));
+      CU(cudaMemsetAsync(cbase, 0, 2 * CTR_SET * sizeof(uint32_t), ctx->stream));
     const uint32_t cur = ctx->epoch & 1u;
-    ctx->work.counters = cbase + cur * CTR_COUNT;
+    ctx->work.counters = cbase + cur * CTR_SET;
+    if (!ctx->totals_external) ctx->work.totals = reinterpret_cast<uint64_t *>(ctx->work.counters + CTR_TOTALS);
     FusedParams P = ctx->fused;
     P.epoch = ctx->epoch;
     P.allow_fast = ctx->pipeline == KGM_PIPELINE_FUSED_GENERIC ? 0u : ctx->any_fast;
     P.ticket = ctx->w_ticket.as<unsigned long long>();
     P.ticket_base = ctx->ticket_next;
     P.scan_state = ctx->w_scan.as<unsigned long long>();
-    P.next_counters = cbase + (1u - cur) * CTR_COUNT;
+    P.next_counters = cbase + (1u - cur) * CTR_SET;
     const uint32_t n = ctx->batch.n_docs;
     const int wpb = (int)P.teams;                   // teams (documents in flight) per CTA
     int blocks = (int)((n + wpb - 1) / wpb);
     blocks = std::max(1, std::min(blocks, ctx->sms * ctx->fused_ctas_per_sm));
     ctx->ticket_next += (unsigned long long)n + (unsigned long long)blocks * wpb;
-    CU(cudaEventRecord(ctx->ev[EV_H2D], ctx->stream));
-    CU(cudaEventRecord(ctx->ev[EV_TOK], ctx->stream));
-    CU(cudaEventRecord(ctx->ev[EV_JOIN], ctx->stream));
     CU(cudaEventRecord(ctx->ev[EV_SCAN], ctx->stream));
     launch_poll(ctx->batch, ctx->fleet, ctx->work, P, blocks, ctx->stream);
     CU(cudaEventRecord(ctx->ev[EV_ENC], ctx->stream));
@@ -259,6 +258,7 @@ int launch_pipeline(kgm_ctx *ctx) {
     return KGM_OK;
   }
   ctx->work.counters = cbase;
+  ctx->work.totals = reinterpret_cast<uint64_t *>(cbase + CTR_TOTALS);
   ctx->counters_clean = false;
   ctx->last_fused = false;
   CU(cudaMemsetAsync(ctx->work.counters, 0, CTR_COUNT * sizeof(uint32_t), ctx->stream));
@@ -278,7 +278,7 @@ int launch_pipeline(kgm_ctx *ctx) {
 // Runs the pipeline, growing the workspace and re-running when a capacity guess was low.
 int run_resident(kgm_ctx *ctx, bool with_h2d_event) {
   if (!ctx->fleet_loaded || !ctx->batch_resident) return KGM_E_STATE;
-  CU(ctx->h_small.ensure(64));
+  CU(ctx->h_small.ensure(128));
   for (int attempt = 0; attempt < 6; ++attempt) {
     int rc = ensure_workspace(ctx);
     if (rc) return rc;
@@ -286,9 +286,8 @@ int run_resident(kgm_ctx *ctx, bool with_h2d_event) {
     rc = launch_pipeline(ctx);
     if (rc) return rc;
     uint32_t *hc = ctx->h_small.as<uint32_t>();
-    uint64_t *ht = reinterpret_cast<uint64_t *>(hc + CTR_COUNT);
-    CU(cudaMemcpyAsync(hc, ctx->work.counters, CTR_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-    CU(cudaMemcpyAsync(ht, ctx->work.totals, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    uint64_t *ht = reinterpret_cast<uint64_t *>(hc + CTR_TOTALS);
+    CU(cudaMemcpyAsync(hc, ctx->work.counters, CTR_SET * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     const uint32_t ovf = hc[CTR_OVERFLOW];
     ctx->slow_docs = ctx->last_fused ? hc[CTR_SLOW] : 0;
@@ -309,10 +308,14 @@ int run_resident(kgm_ctx *ctx, bool with_h2d_event) {
 void fill_timing(kgm_ctx *ctx, bool h2d, bool d2h) {
   kgm_timing &t = ctx->timing;
   t = kgm_timing{};
-  if (h2d) cudaEventElapsedTime(&t.h2d_ms, ctx->ev[EV_START], ctx->ev[EV_H2D]);
-  cudaEventElapsedTime(&t.tokenize_ms, ctx->ev[EV_H2D], ctx->ev[EV_TOK]);
-  cudaEventElapsedTime(&t.join_ms, ctx->ev[EV_TOK], ctx->ev[EV_JOIN]);
-  cudaEventElapsedTime(&t.scan_ms, ctx->ev[EV_JOIN], ctx->ev[EV_SCAN]);
+  if (ctx->last_fused) {
+    if (h2d) cudaEventElapsedTime(&t.h2d_ms, ctx->ev[EV_START], ctx->ev[EV_SCAN]);
+  } else {
+    if (h2d) cudaEventElapsedTime(&t.h2d_ms, ctx->ev[EV_START], ctx->ev[EV_H2D]);
+    cudaEventElapsedTime(&t.tokenize_ms, ctx->ev[EV_H2D], ctx->ev[EV_TOK]);
+    cudaEventElapsedTime(&t.join_ms, ctx->ev[EV_TOK], ctx->ev[EV_JOIN]);
+    cudaEventElapsedTime(&t.scan_ms, ctx->ev[EV_JOIN], ctx->ev[EV_SCAN]);
+  }
   cudaEventElapsedTime(&t.encode_ms, ctx->ev[EV_SCAN], ctx->ev[EV_ENC]);
   if (d2h) cudaEventElapsedTime(&t.d2h_ms, ctx->ev[EV_ENC], ctx->ev[EV_D2H]);
   cudaEventElapsedTime(&t.total_ms, ctx->ev[EV_START], ctx->ev[d2h ? EV_D2H : EV_ENC]);
@@ -576,11 +579,12 @@ int encode_pipelined(kgm_ctx *ctx, const kgm_batch *b, uint32_t chunks, kgm_resu
     wd.doc_desc0 += lo; wd.doc_nlines += lo; wd.doc_nbytes += lo; wd.doc_status += lo;
     wd.doc_line_off += lo; wd.doc_byte_off += lo;
     wd.totals = d_tot + 2 * (c + 1);
+    ctx->totals_external = true;
     ctx->fused.carry = c ? reinterpret_cast<const unsigned long long *>(d_tot + 2 * c) : nullptr;
     CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_in[c], 0));
     if (c == 0) CU(cudaEventRecord(ctx->ev[EV_H2D], ctx->stream));
     rc = launch_pipeline(ctx);                     // cn > 0; sets wd.counters to this launch's set
-    if (rc) { ctx->batch = whole; ctx->work = wfull; ctx->fused.carry = nullptr; return rc; }
+    if (rc) { ctx->batch = whole; ctx->work = wfull; ctx->fused.carry = nullptr; ctx->totals_external = false; return rc; }
     CU(cudaMemcpyAsync(h_tot + 2 * c, wd.totals, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaMemcpyAsync(h_cnt + CTR_COUNT * c, wd.counters, CTR_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaEventRecord(ctx->ev_k[c], ctx->stream));
@@ -588,6 +592,7 @@ int encode_pipelined(kgm_ctx *ctx, const kgm_batch *b, uint32_t chunks, kgm_resu
   ctx->batch = whole;
   ctx->work = wfull;
   ctx->fused.carry = nullptr;
+  ctx->totals_external = false;
   CU(cudaEventRecord(ctx->ev[EV_ENC], ctx->stream));
 
   uint64_t lines_done = 0, bytes_done = 0;

@@ -43,7 +43,9 @@ struct FleetDev {
   const uint64_t *vis_hash2;     // fast::key_hash_bytes of every visible uuid
 };
 
-enum : int { CTR_GROW = 0, CTR_PROW = 1, CTR_DESC = 2, CTR_OVERFLOW = 3, CTR_SLOW = 4, CTR_COUNT = 8 };
+enum : int { CTR_GROW = 0, CTR_PROW = 1, CTR_DESC = 2, CTR_OVERFLOW = 3, CTR_SLOW = 4, CTR_COUNT = 8,
+             CTR_TOTALS = 8,   // {lines, bytes} as two u64 right behind the counters: one read-back
+             CTR_SET = 16 };   // u32 words per counter set
 enum : uint32_t { OVF_GROW = 1, OVF_PROW = 2, OVF_DESC = 4, OVF_OUT = 8 };
 
 // Per-batch workspace ("scratch"): token tables, join state, line plan.

@@ -679,7 +679,11 @@ int poll_smem_bytes(const FusedParams &P) { return (int)(CONST_PAD + P.teams * P
 
 void launch_poll(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P, int blocks,
                  cudaStream_t s) {
-  cudaFuncSetAttribute(k_poll, cudaFuncAttributeMaxDynamicSharedMemorySize, poll_smem_bytes(P));
+  static int attr_bytes = -1;                        // (one attribute for all contexts of the process)
+  if (poll_smem_bytes(P) > attr_bytes) {
+    cudaFuncSetAttribute(k_poll, cudaFuncAttributeMaxDynamicSharedMemorySize, poll_smem_bytes(P));
+    attr_bytes = poll_smem_bytes(P);
+  }
   k_poll<<<blocks, 64 * P.teams, poll_smem_bytes(P), s>>>(b, f, w, P);
 }
 

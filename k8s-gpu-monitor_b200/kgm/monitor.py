@@ -129,6 +129,8 @@ class Monitor:
         _check(self._lib.kgm_create(C.byref(self._ctx), device), "kgm_create", None, self._lib)
         self._fleet = None
         self._batch = None
+        self._timing_buf = _ffi.KgmTiming()
+        self._result_buf = _ffi.KgmResult()
 
     # -- lifecycle ------------------------------------------------------------------------
     def close(self):
@@ -183,9 +185,10 @@ class Monitor:
 
     def encode_resident(self) -> _ffi.KgmResult:
         """Runs the pipeline on the resident batch; the result holds DEVICE pointers."""
-        res = _ffi.KgmResult()
-        _check(self._lib.kgm_encode_resident(self._ctx, C.byref(res)), "kgm_encode_resident",
-               self._ctx, self._lib)
+        res = self._result_buf                       # reused: valid until the next call
+        rc = self._lib.kgm_encode_resident(self._ctx, C.byref(res))
+        if rc != _ffi.KGM_OK:
+            _check(rc, "kgm_encode_resident", self._ctx, self._lib)
         return res
 
     def fetch(self) -> HostResult:
@@ -211,6 +214,12 @@ class Monitor:
                                 ("last", C.c_uint32), ("sum", C.c_uint64), ("mean", C.c_double)):
                 out["%s_%s" % (metric, stat)] = view(getattr(w, "m_" + stat)[m], ctype)
         return out
+
+    def kernel_times(self):
+        """(encode_ms, total_ms) of the last run -- the cheap accessor for timed loops."""
+        t = self._timing_buf
+        self._lib.kgm_get_timing(self._ctx, C.byref(t))
+        return t.tokenize_ms, t.join_ms, t.scan_ms, t.encode_ms, t.total_ms
 
     def timing(self) -> dict:
         t = _ffi.KgmTiming()
