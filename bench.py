@@ -218,7 +218,13 @@ def run_kgm_arm(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # stdout carries the one JSON line only
+    # stdout carries the one JSON line only: whatever libraries print there goes to stderr
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+    if world > 1:
+        # leave a few CTA slots of every GPU to the NCCL kernels that move the shards, so that
+        # they run beside the persistent poll kernel of the next step instead of after it
+        os.environ.setdefault("KGM_RESERVE_CTAS", "16")
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -253,13 +259,20 @@ def run_kgm_arm(args):
     acc = {k: [] for k in keys}
     done_samples = 0
 
+    host_s = {"encode_call": 0.0, "gather_call": 0.0}
+
     def step(i, timed):
         nonlocal done_samples
         mon = mons[i % ROTATE]
+        t0 = time.perf_counter()
         r = mon.encode_resident()                    # device time per kernel from the library's CUDA events
+        t1 = time.perf_counter()
         if world > 1:                                # shards -> rank 0, overlapped with the next step
             local = shard.tensor_of_device_buffer(r.lines, max(int(r.n_bytes), 1), device)
             gather.start(local, int(r.n_bytes), int(r.n_lines))
+        if timed:
+            host_s["encode_call"] += t1 - t0
+            host_s["gather_call"] += time.perf_counter() - t1
         if timed:
             for k, v in zip(keys, mon.kernel_times()):
                 acc[k].append(v)
@@ -278,7 +291,7 @@ def run_kgm_arm(args):
         crcs = [None] * world
         dist.all_gather_object(crcs, mine)
         if rank == 0:
-            off = gather.last_offsets[:, 0].tolist()
+            off = gather.shard_offsets()
             whole = gather.body().cpu().numpy().tobytes()
             concat_check = all(zlib.crc32(whole[int(off[r]):int(off[r + 1])]) == crcs[r] for r in range(world))
     sync_all()
@@ -371,12 +384,14 @@ def run_kgm_arm(args):
                        "parallelism": "hosts sharded over %d rank(s); per step every rank all-gathers its "
                                       "{bytes, lines} over NCCL and the encoded shards are gathered to rank 0 "
                                       "(%s; inside the timed bracket, overlapping the next step's kernel); "
-                                      "concatenation verified: %s" % (world, "peer-to-peer copies into rank 0's "
-                                      "buffer mapped through CUDA IPC" if gather.mode == "ipc" else
-                                      "NCCL send/recv", concat_check) if world > 1 else "1 rank"},
+                                      "concatenation verified: %s" % (world, {"ipc": "peer-to-peer copies into rank 0's "
+                                      "buffer mapped through CUDA IPC", "slots": "NCCL send/recv into fixed slots, "
+                                      "packed by kgm_concat_shards from device-side sizes", "p2p": "NCCL send/recv"}
+                                      [gather.mode], concat_check) if world > 1 else "1 rank"},
             "timing": "CUDA events around %d back-to-back steps (barrier + synchronize on both sides), max over "
                       "ranks; kernel_ms from the library's own events on its stream" % args.steps,
             "kernel_ms": {k: round(mean[k], 5) for k in keys},
+            "host_ms_per_step_rank0": {k: round(1e3 * v / args.steps, 4) for k, v in host_s.items()},
             "wall_ms_region": wall_ms,
             "pipeline_frac_of_peak": algo_bytes / (mean["total_ms"] * 1e-3) / 1e9 / peak,
             "pipeline": "fused (k_poll)" if fused else "staged (k_tokenize, k_join, k_scan, k_encode)",
@@ -396,7 +411,7 @@ def run_kgm_arm(args):
         }
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline_single_core(rps[0], host_result)
-        print(json.dumps(line))
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

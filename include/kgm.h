@@ -218,6 +218,19 @@ int  kgm_flush_l2(kgm_ctx *ctx, uint64_t bytes);
 void *kgm_host_alloc(uint64_t bytes);
 void  kgm_host_free(void *p);
 
+/* Multi-GPU assembly (no counterpart in the reference, whose instances never talk to each
+ * other: gpu_monitor.yaml:2 runs one per node).  After the ranks' {bytes, lines} have been
+ * all-gathered and their encoded shards have arrived in fixed-stride slots on one GPU, this
+ * packs the slots into the rank-major concatenation without the host ever learning the
+ * sizes: shard r is slots[r * stride .. + counts[2 * r]).  All pointers are DEVICE pointers
+ * on the current device; `counts` holds world x {int64 bytes, int64 lines}; totals_out (may
+ * be NULL) receives {bytes, lines} of the concatenation.  With counts == NULL every slot
+ * carries its own sizes instead: {int64 bytes, int64 lines} in its first 16 bytes, the
+ * shard behind them (so that sizes and bytes arrive in one transfer).  Asynchronous on
+ * `stream`.                                                                               */
+int  kgm_concat_shards(const uint8_t *slots, uint64_t stride, const int64_t *counts, uint32_t world,
+                       uint8_t *out, uint64_t out_cap, uint64_t *totals_out, void *stream);
+
 /* Stage-1 tokenizer for callers that may not allocate device memory.  (No counterpart in
  * the reference; it exists for deployment reasons only.)
  *

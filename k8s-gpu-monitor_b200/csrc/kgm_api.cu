@@ -108,6 +108,7 @@ struct kgm_ctx {
   HostBuf h_chunk;                         // per chunk: totals {lines, bytes} + counters
   uint32_t last_chunks = 1;
   uint32_t force_teams = 0;                // KGM_FUSED_TEAMS=3|4 (experiments)
+  int reserve_ctas = 0;                    // KGM_RESERVE_CTAS: CTA slots k_poll leaves free (for NCCL kernels)
   // window reductions
   uint32_t max_tick = 0;
   bool have_ticks = false;
@@ -247,7 +248,7 @@ int launch_pipeline(kgm_ctx *ctx) {
     const uint32_t n = ctx->batch.n_docs;
     const int wpb = (int)P.teams;                   // teams (documents in flight) per CTA
     int blocks = (int)((n + wpb - 1) / wpb);
-    blocks = std::max(1, std::min(blocks, ctx->sms * ctx->fused_ctas_per_sm));
+    blocks = std::max(1, std::min(blocks, ctx->sms * ctx->fused_ctas_per_sm - ctx->reserve_ctas));
     ctx->ticket_next += (unsigned long long)n + (unsigned long long)blocks * wpb;
     CU(cudaEventRecord(ctx->ev[EV_SCAN], ctx->stream));
     launch_poll(ctx->batch, ctx->fleet, ctx->work, P, blocks, ctx->stream);
@@ -702,6 +703,7 @@ int kgm_create(kgm_ctx **out, int device) {
   if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
   if (e != cudaSuccess) { kgm_destroy(ctx); cudaGetLastError(); return KGM_E_CUDA; }
   ctx->sms = prop.multiProcessorCount;
+  if (const char *env = getenv("KGM_RESERVE_CTAS")) ctx->reserve_ctas = std::max(0, std::min(atoi(env), 128));
   if (const char *env = getenv("KGM_FUSED_TEAMS")) {
     if (!strcmp(env, "3")) ctx->force_teams = 3;
     else if (!strcmp(env, "4")) ctx->force_teams = 4;

@@ -744,6 +744,60 @@ void launch_flush(uint8_t *buf, uint64_t bytes, int sms, cudaStream_t s) {
 }  // namespace kgm
 
 // ======================================================================================
+// Rank-major packing of fixed-stride shard slots (kgm_concat_shards, include/kgm.h)
+// ======================================================================================
+namespace kgm {
+namespace {
+
+__global__ void k_concat_shards(const uint8_t *slots, uint64_t stride, const long long *counts, uint32_t world,
+                                uint8_t *out, uint64_t out_cap, unsigned long long *totals_out) {
+  // every block handles every shard in turn (grid-stride over 16-byte units); shard sizes
+  // are read from device memory, the destination offset is their running sum
+  uint64_t base = 0, lines = 0;
+  for (uint32_t r = 0; r < world; ++r) {
+    const long long *hdr = counts ? counts + 2 * r : reinterpret_cast<const long long *>(slots + (uint64_t)r * stride);
+    const uint64_t n = (uint64_t)hdr[0];
+    const uint8_t *src = slots + (uint64_t)r * stride + (counts ? 0 : 16);
+    if (base + n <= out_cap) {
+      uint8_t *dst = out + base;
+      const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (uint64_t)gridDim.x * blockDim.x;
+      // bytes up to the destination's 16-byte boundary, realigned vectors, tail bytes
+      const uint64_t head = min(n, (uint64_t)((16u - (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u)) & 15u));
+      if (tid < head) dst[tid] = src[tid];
+      const uint64_t nvec = (n - head) >> 4;
+      const uint32_t sh = 8u * (uint32_t)(head & 3u);
+      const uint32_t *sw = reinterpret_cast<const uint32_t *>(src + (head & ~3ull));   // slots are 16-byte aligned
+      for (uint64_t v = tid; v < nvec; v += nthreads) {
+        const uint32_t *q = sw + 4 * v;
+        const uint32_t a0 = q[0], a1 = q[1], a2 = q[2], a3 = q[3], a4 = sh ? q[4] : 0u;
+        uint4 o;
+        o.x = __funnelshift_r(a0, a1, sh); o.y = __funnelshift_r(a1, a2, sh);
+        o.z = __funnelshift_r(a2, a3, sh); o.w = __funnelshift_r(a3, a4, sh);
+        *reinterpret_cast<uint4 *>(dst + head + 16 * v) = o;
+      }
+      const uint64_t done = head + 16 * nvec;
+      if (tid < n - done) dst[done + tid] = src[done + tid];
+    }
+    base += n;
+    lines += (uint64_t)hdr[1];
+  }
+  if (totals_out && blockIdx.x == 0 && threadIdx.x == 0) { totals_out[0] = base; totals_out[1] = lines; }
+}
+
+}  // namespace
+}  // namespace kgm
+
+extern "C" int kgm_concat_shards(const uint8_t *slots, uint64_t stride, const int64_t *counts, uint32_t world,
+                                 uint8_t *out, uint64_t out_cap, uint64_t *totals_out, void *stream) {
+  if (!slots || !out || !world || (stride & 15) || (reinterpret_cast<uintptr_t>(slots) & 15))
+    return KGM_E_INVALID;
+  kgm::k_concat_shards<<<148 * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      slots, stride, reinterpret_cast<const long long *>(counts), world, out, out_cap,
+      reinterpret_cast<unsigned long long *>(totals_out));
+  return cudaGetLastError() == cudaSuccess ? KGM_OK : KGM_E_CUDA;
+}
+
+// ======================================================================================
 // Allocation-free tokenizer entry point (kgm_tokenize_gpu_noalloc, include/kgm.h)
 // ======================================================================================
 // Some processes that want the per-GPU samples of a batch are not allowed to take device

@@ -79,16 +79,23 @@ class ShardGather:
     Per step: the ranks all-gather their {bytes, lines} (a communicator of its own, so the
     16 bytes never queue behind bulk traffic); every rank copies its bytes into one of two
     exchange buffers (the library may then overwrite its output with the next batch) and
-    sends them to their final offset in rank 0's buffer as NCCL (gloo in the CPU tests)
-    send/recv.  ``use_ipc=True`` (experimental) instead maps rank 0's buffer into every
+    sends them to rank 0.  On CUDA the sizes never visit the host: they are all-gathered on
+    the device, the shards travel as fixed-size NCCL transfers into fixed-stride slots, and
+    the library's kgm_concat_shards kernel packs the slots from the device-side sizes.  In the
+    gloo CPU tests (and with ``host_counts=True``) every shard goes straight to its final
+    offset as a send/recv sized on the host.  ``use_ipc=True`` (experimental) instead maps rank 0's buffer into every
     process through a CUDA IPC handle and writes the shard with a peer ``cudaMemcpyAsync``,
     which needs no SM; on the test pool that path measured slower than NCCL, so it is off.
     ``start`` returns once the local copy is done; ``finish`` waits for every transfer."""
 
-    def __init__(self, cap_bytes: int, device, group=None, use_ipc=False):
+    def __init__(self, cap_bytes: int, device, group=None, use_ipc=False, host_counts=False):
         self.group, self.device = group, device
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.cap = int(cap_bytes)
+        if self.world > 1:                           # every rank must size its buffers alike
+            t = torch.tensor([self.cap], dtype=torch.int64, device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+            self.cap = int(t.item())
         self.xbuf = [torch.empty(self.cap, dtype=torch.uint8, device=device) for _ in range(2)]
         self.final = (torch.empty(self.cap * self.world, dtype=torch.uint8, device=device)
                       if self.rank == 0 else None)
@@ -105,6 +112,8 @@ class ShardGather:
         self.mode = "p2p"
         if self.cuda and use_ipc and self.world > 1:
             self._open_ipc()
+        if self.cuda and self.mode == "p2p" and self.world > 1 and not host_counts:
+            self._init_slots()
 
     def _open_ipc(self):
         """Rank 0 exports its buffer; the others map it (same node, NVLink peers)."""
@@ -126,9 +135,71 @@ class ShardGather:
         dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
         self.mode = "ipc" if int(ok.item()) == 1 else "p2p"
 
+    def _init_slots(self):
+        """CUDA, default mode: fixed-stride slots on rank 0, sizes stay on the device."""
+        from . import _ffi
+        self._lib = _ffi.load()
+        self.stride = (self.cap + 16 + 15) // 16 * 16          # 16-byte size header + shard
+        for i in range(2):
+            self.xbuf[i] = torch.empty(self.stride, dtype=torch.uint8, device=self.device)
+        self.mine_host = [torch.zeros(2, dtype=torch.int64).pin_memory() for _ in range(2)]
+        self.mine_dev = [torch.zeros(2, dtype=torch.int64, device=self.device) for _ in range(2)]
+        self.counts_dev = [torch.zeros((self.world, 2), dtype=torch.int64, device=self.device) for _ in range(2)]
+        self.totals_dev = torch.zeros(2, dtype=torch.int64, device=self.device)
+        if self.rank == 0:
+            self.slots = torch.empty(self.stride * self.world, dtype=torch.uint8, device=self.device)
+            self.own = [torch.empty(self.stride, dtype=torch.uint8, device=self.device) for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(self.device)
+        self.mode = "slots"
+
+    def _start_slots(self, local, n_bytes, n_lines):
+        """No host round trip and no separate exchange for the sizes: every shard travels as one
+        fixed-size transfer into its fixed slot on rank 0 with its {bytes, lines} in front,
+        and a kernel of the library (kgm_concat_shards) packs the slots rank-major."""
+        slot = (self.k - 1) & 1
+        if n_bytes > self.stride:
+            raise ValueError("a shard exceeds the exchange buffer")
+        done = self.copied[slot]
+        # 1. the copy out of the library's buffer, on a stream of its own: the host waits for
+        #    this and nothing else.  The slot starts with its own {bytes, lines}.
+        with torch.cuda.stream(self.copy_stream):
+            for w in self.pending[slot]:
+                w.wait()                             # stream-level: the buffers of step k-2 are free
+            self.pending[slot] = []
+            dst = self.own[slot] if self.rank == 0 else self.xbuf[slot]
+            hdr = self.mine_host[slot]
+            hdr[0] = n_bytes
+            hdr[1] = n_lines
+            dst[:16].view(torch.int64).copy_(hdr, non_blocking=True)
+            dst[16:16 + n_bytes].copy_(local[:n_bytes], non_blocking=True)
+            done.record(self.copy_stream)
+        # 2. the shards, on the communication stream, behind the copy
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(done)
+            if self.rank == 0:
+                self.slots[:16 + n_bytes].copy_(self.own[slot][:16 + n_bytes], non_blocking=True)
+                ops = [dist.P2POp(dist.irecv, self.slots[r * self.stride:(r + 1) * self.stride], r, self.group)
+                       for r in range(1, self.world)]
+                works = dist.batch_isend_irecv(ops) if ops else []
+                for w in works:
+                    w.wait()                         # the packing kernel below is ordered after the receives
+                rc = self._lib.kgm_concat_shards(self.slots.data_ptr(), self.stride, None, self.world,
+                                                 self.final.data_ptr(), self.final.numel(),
+                                                 self.totals_dev.data_ptr(), self.stream.cuda_stream)
+                if rc != 0:
+                    raise RuntimeError("kgm_concat_shards failed: %d" % rc)
+                fin = torch.cuda.Event()
+                fin.record(self.stream)
+                self.pending[slot] = [_EventWork(fin)]
+            else:
+                self.pending[slot] = dist.batch_isend_irecv([dist.P2POp(dist.isend, self.xbuf[slot], 0, self.group)])
+        done.synchronize()                           # the library may now reuse its output buffer
+
     def start(self, local: torch.Tensor, n_bytes: int, n_lines: int):
-        slot = self.k & 1
         self.k += 1
+        if self.mode == "slots":
+            return self._start_slots(local, n_bytes, n_lines)
+        slot = (self.k - 1) & 1
         for w in self.pending[slot]:                 # the exchange buffer of step k-2 is free again
             w.wait()
         self.pending[slot] = []
@@ -186,15 +257,36 @@ class ShardGather:
                 w.wait()
             self.pending[slot] = []
         if self.cuda:
-            self.stream.synchronize()
             torch.cuda.synchronize(self.device)
         if self.world > 1:
             dist.barrier(group=self.ctl_group)       # every shard has landed on rank 0
 
     def body(self):
         """Rank 0: the concatenated bytes of the last finished step."""
+        if self.mode == "slots":
+            return self.final[:int(self.totals_dev[0].item())]
         total = int(self.last_offsets[-1, 0])
         return self.final[:total]
+
+    def shard_offsets(self):
+        """Byte offset of every rank's shard in the concatenation of the last finished step."""
+        if self.mode == "slots":
+            c = self.slots.view(torch.int64).view(self.world, self.stride // 8)[:, 0].cpu().tolist()
+            out = [0]
+            for x in c:
+                out.append(out[-1] + int(x))
+            return out
+        return [int(x) for x in self.last_offsets[:, 0].tolist()]
+
+
+class _EventWork:
+    """A CUDA event behind the `wait()` of a distributed work handle (stream-level wait)."""
+
+    def __init__(self, event):
+        self.event = event
+
+    def wait(self):
+        torch.cuda.current_stream().wait_event(self.event)
 
 
 class DevicePointer:
