@@ -1,8 +1,8 @@
 // k_poll: the whole poll path of one batch in ONE persistent kernel (included by
 // kgm_kernels.cu, after the staged kernels whose device functions it reuses).
 //
-// One warp owns one document at a time (documents are handed out in batch order by a
-// ticket counter).  For a regular document everything happens in the warp's slice of
+// A team of two warps owns one document at a time (documents are handed out in batch order
+// by a ticket counter).  For a regular document everything happens in the team's slice of
 // shared memory:
 //   text windows  <- coalesced 16-byte loads of the two nvidia-smi texts      (gpu.py:104-116)
 //   rows          <- SWAR line-feed scan, one lane per row: cells, digit runs, keys
@@ -15,8 +15,8 @@
 //                                                                          (gpu.py:136-143,206-216,240-250)
 // so the texts are read from HBM once and the line protocol is written once, with no
 // intermediate tables.  A document the fast path cannot take (any raise point of the
-// reference, unusual bytes, duplicate keys, sizes beyond the warp's slice) is re-done from
-// scratch by the generic per-byte code of the staged pipeline inside the same warp, and
+// reference, unusual bytes, duplicate keys, sizes beyond the team's slice) is re-done from
+// scratch by the generic per-byte code of the staged pipeline by one warp of the team, and
 // joins the same look-back chain -- the output is identical either way.
 #pragma once
 
