@@ -197,6 +197,12 @@ typedef struct kgm_windows {
 } kgm_windows;
 int  kgm_window_reduce(kgm_ctx *ctx, uint32_t window_ticks, int want_host_copy, kgm_windows *out);
 
+/* Debug aid (no counterpart in the reference): when the library was built with
+ * -DKGM_PROFILE_STAGES, copies the fused kernel's per-stage SM-clock sums (64 values: 32
+ * stages for each of a team's two warps, accumulated since load) to `out64` and returns 64;
+ * returns 0 in a normal build.                                                            */
+int  kgm_debug_stage_clocks(uint64_t *out64);
+
 /* Which kernels run a batch (no counterpart in the reference; results are identical):
  *   AUTO           one fused single-pass kernel when the batch fits its shared-memory slices,
  *                  the staged kernels otherwise (default)

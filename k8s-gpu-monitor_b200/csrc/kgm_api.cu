@@ -95,6 +95,7 @@ struct kgm_ctx {
   bool counters_clean = false;             // the counter set of the next fused launch is known to be zero
   unsigned long long ticket_next = 0;      // value of the ticket counter when the next launch starts
   DevBuf w_ticket, w_scan;
+  uint64_t scan_docs_cap = 0;              // documents the level-1 scan state has room for
   DevBuf f_node_fast, f_tb_off, f_tb_len, f_tb_pool, f_pid16, f_vis_hash2;
   uint32_t fast_max_nc = 1, fast_max_tb = 0, fast_max_idle = 0, any_fast = 0;
   std::vector<uint8_t> h_node_fast;        // host copies of FleetDev::node_fast / tb_len
@@ -186,8 +187,9 @@ int ensure_workspace(kgm_ctx *ctx) {
       ctx->ticket_next = 0;
     }
     const size_t sb = ctx->w_scan.cap;
-    CU(ctx->w_scan.ensure((size_t)std::max(n, 1u) * 16));
+    CU(ctx->w_scan.ensure(((size_t)std::max(n, 1u) + (size_t)n / 32 + 2) * 16));
     if (ctx->w_scan.cap != sb) CU(cudaMemsetAsync(ctx->w_scan.p, 0, ctx->w_scan.cap, ctx->stream));
+    ctx->scan_docs_cap = std::max<uint64_t>(ctx->scan_docs_cap, std::max(n, 1u));
   }
   CU(ctx->w_doc32.ensure((size_t)std::max(n, 1u) * 8 * sizeof(uint32_t)));
   CU(ctx->w_status.ensure((size_t)std::max(n, 1u) * sizeof(int32_t)));
@@ -244,6 +246,7 @@ int launch_pipeline(kgm_ctx *ctx) {
     P.ticket = ctx->w_ticket.as<unsigned long long>();
     P.ticket_base = ctx->ticket_next;
     P.scan_state = ctx->w_scan.as<unsigned long long>();
+    P.scan_blocks = P.scan_state + 2ull * ctx->scan_docs_cap;
     P.next_counters = cbase + (1u - cur) * CTR_SET;
     const uint32_t n = ctx->batch.n_docs;
     const int wpb = (int)P.teams;                   // teams (documents in flight) per CTA
@@ -1133,6 +1136,10 @@ int kgm_window_reduce(kgm_ctx *ctx, uint32_t window_ticks, int want_host_copy, k
     out->m_last[m] = r.m_last[m]; out->m_sum[m] = r.m_sum[m]; out->m_mean[m] = r.m_mean[m];
   }
   return KGM_OK;
+}
+
+int kgm_debug_stage_clocks(uint64_t *out64) {
+  return out64 ? debug_stage_clocks(reinterpret_cast<unsigned long long *>(out64)) : KGM_E_INVALID;
 }
 
 int kgm_set_pipeline(kgm_ctx *ctx, int mode) {

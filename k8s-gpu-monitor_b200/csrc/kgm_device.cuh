@@ -86,6 +86,7 @@ struct FusedParams {
   unsigned long long ticket_base;
   unsigned long long *ticket;    // monotonic document ticket counter
   unsigned long long *scan_state;   // 2 words per document
+  unsigned long long *scan_blocks;  // 2 words per block of 32 documents
   uint32_t *next_counters;       // the counter set of the next launch (zeroed by this one)
   const unsigned long long *carry;  // {lines, bytes} emitted by earlier launches of the same batch
                                     // (chunked end-to-end path), or null
@@ -94,6 +95,7 @@ struct FusedParams {
 void launch_poll(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P, int blocks,
                  cudaStream_t s);
 int poll_smem_bytes(const FusedParams &P);
+int debug_stage_clocks(unsigned long long *out64);   // 0 unless built with -DKGM_PROFILE_STAGES
 
 void launch_tokenize(const BatchDev &b, const WorkDev &w, int sms, cudaStream_t s);
 void launch_join(const BatchDev &b, const FleetDev &f, const WorkDev &w, int sms, cudaStream_t s);

@@ -244,11 +244,19 @@ KGM_HD bool parse_gpu_row(const uint32_t *W, uint32_t s, uint32_t e, uint32_t no
   if (!digit_run(W, c4 + 1, c5, g.mf)) return false;
   if (g.mt.len == 0 || g.mu.len == 0) return false;               // ValueError gpu.py:133-134
   if (g.mt.len > 18 || g.mu.len > 18) return false;
+  if (run_value(W, g.mt) == 0) return false;                      // ZeroDivisionError gpu.py:135
+  g.flen = 0;
+  g.line_len = node_fixed + 2 * dec_len(sid);                     // completed by finish_gpu_row
+  return true;
+}
+
+// Second half of a gpu row: mem_util = used * 100.0 / total and its repr (gpu.py:135,139), the
+// length of the node_gpu line.  Separate so that the kernel can run it beside other work.
+KGM_HD bool finish_gpu_row(const uint32_t *W, GRec &g) {
   const uint64_t total = run_value(W, g.mt), used = run_value(W, g.mu);
-  if (total == 0) return false;                                   // ZeroDivisionError gpu.py:135
   const int flen = float_repr(mem_util(used, total), g.fstr);
   g.flen = (uint8_t)flen;
-  g.line_len = node_fixed + 2 * dec_len(sid) + g.util.len + (uint32_t)flen + g.mu.len + g.mt.len + g.mf.len + 1;
+  g.line_len += g.util.len + (uint32_t)flen + g.mu.len + g.mt.len + g.mf.len + 1;
   return g.line_len <= MAX_LINE_BYTES;
 }
 

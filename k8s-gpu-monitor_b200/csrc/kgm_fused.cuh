@@ -30,6 +30,21 @@ constexpr uint32_t CONST_PAD = (ConstArea::BYTES + 15u) & ~15u;
 constexpr uint32_t KIND_NODE = 0, KIND_BUSY = 1, KIND_IDLE = 2;
 constexpr uint32_t IDLE_NONE = 0xfffu;
 
+// ---- optional stage clocks (build with -DKGM_PROFILE_STAGES; read with kgm_debug_stage_clocks) --
+#ifdef KGM_PROFILE_STAGES
+__device__ unsigned long long g_stage_clk[64];       // [half * 32 + stage]: SM clocks summed over documents
+#define STAGE_MARK(id)                                                                      \
+  do {                                                                                      \
+    if (lane_id() == 0) {                                                                   \
+      const long long now__ = clock64();                                                    \
+      atomicAdd(&g_stage_clk[half * 32 + (id)], (unsigned long long)(now__ - stage_t));     \
+      stage_t = now__;                                                                      \
+    }                                                                                       \
+  } while (0)
+#else
+#define STAGE_MARK(id) do { (void)stage_t; } while (0)
+#endif
+
 // ---- look-back state: two tagged 64-bit words per document -----------------------------------
 // tag = epoch (16 bits) | status (2 bits); value in the low 46 bits
 constexpr uint64_t ST_AGG = 1, ST_INC = 2;
@@ -59,57 +74,91 @@ __device__ __forceinline__ uint64_t warp_sum64(uint64_t v) {
   return v;
 }
 
-// Device-wide exclusive scan over documents, decoupled look-back.  scan_publish makes the
-// document's (lines, bytes) visible as an aggregate; scan_resolve, called later, sums the
-// predecessors' aggregates back to the nearest inclusive prefix and publishes the
-// document's own inclusive prefix.  Between the two calls the warp composes its lines, so
-// that the predecessors it has to wait for have normally published by then.
-__device__ __forceinline__ void scan_publish(const FusedParams &P, uint32_t d, uint64_t nl, uint64_t nb) {
-  if (lane_id() != 0) return;
-  unsigned long long *st = P.scan_state + 2ull * d;
-  const uint64_t tag = st_tag(P.epoch, d == 0 ? ST_INC : ST_AGG);
-  st_relaxed(st + 1, tag | nb);
-  st_release(st, tag | nl);
+// Device-wide exclusive scan over documents: decoupled look-back on two levels.  Level 1
+// holds every document's (lines, bytes) as an aggregate; level 2 holds, per block of 32
+// consecutive documents, the block's aggregate and then its inclusive prefix.  The team
+// that owns the last document of a block sums the block and looks back over the BLOCK
+// entries (one 32-wide window covers 1024 documents, more than are ever in flight), so a
+// block's inclusive prefix appears a few memory round trips after the block's documents
+// have been planned.  A document's exclusive prefix is then one window of level 1 (its own
+// block) plus one level-2 word pair.  All waits are on values that teams with EARLIER
+// tickets publish right after planning, never on their later stages, so the chain cannot
+// deadlock; scan_resolve is called after the first round of lines has been composed, when
+// those values have normally long been there.
+struct ScanWords { uint64_t l, b; bool inc; };
+
+__device__ __forceinline__ ScanWords scan_wait(const unsigned long long *st, uint64_t agg, uint64_t inc,
+                                               bool need_inc) {
+  const uint64_t VAL = (1ull << 46) - 1ull;
+  for (;;) {
+    const uint64_t w0 = ld_acquire(st);
+    const uint64_t t0 = w0 & ~VAL;
+    if (t0 == inc || (!need_inc && t0 == agg)) {
+      const uint64_t w1 = ld_relaxed(st + 1);
+      if ((w1 & ~VAL) == t0) return ScanWords{w0 & VAL, w1 & VAL, t0 == inc};
+    }
+    __nanosleep(40);
+  }
+}
+__device__ __forceinline__ void scan_store(unsigned long long *st, uint64_t tag, uint64_t l, uint64_t b) {
+  st_relaxed(st + 1, tag | b);
+  st_release(st, tag | l);
+}
+
+// Every lane of the (half 0) warp calls this right after the document has been planned.
+__device__ void scan_publish(const FusedParams &P, uint32_t d, uint32_t n_docs, uint64_t nl, uint64_t nb) {
+  const uint32_t l = lane_id();
+  const uint64_t agg = st_tag(P.epoch, ST_AGG), inc = st_tag(P.epoch, ST_INC);
+  if (l == 0) scan_store(P.scan_state + 2ull * d, agg, nl, nb);
+  if ((d & 31u) != 31u) return;
+  (void)n_docs;
+  // last document of block k: the block's aggregate, then its inclusive prefix
+  const uint32_t k = d >> 5;
+  uint64_t vl = nl, vb = nb;
+  if (l != 31u) {
+    const ScanWords w = scan_wait(P.scan_state + 2ull * (32u * k + l), agg, inc, false);
+    vl = w.l; vb = w.b;
+  }
+  const uint64_t bl = warp_sum64(vl), bb = warp_sum64(vb);
+  unsigned long long *blk = P.scan_blocks;
+  if (l == 0) scan_store(blk + 2ull * k, agg, bl, bb);
+  uint64_t ex_l = 0, ex_b = 0;
+  long long j = (long long)k - 1;
+  while (j >= 0) {
+    const long long idx = j - (long long)l;
+    uint64_t xl = 0, xb = 0;
+    bool is_inc = true;                              // before block 0: prefix 0
+    if (idx >= 0) {
+      const ScanWords w = scan_wait(blk + 2ull * idx, agg, inc, false);
+      xl = w.l; xb = w.b; is_inc = w.inc;
+    }
+    const uint32_t incs = __ballot_sync(FULL, is_inc);
+    const uint32_t first = incs ? (uint32_t)__ffs(incs) - 1u : 32u;
+    if (l > first) { xl = 0; xb = 0; }
+    ex_l += warp_sum64(xl);
+    ex_b += warp_sum64(xb);
+    if (incs) break;
+    j -= 32;
+  }
+  if (l == 0) scan_store(blk + 2ull * k, inc, ex_l + bl, ex_b + bb);
 }
 
 __device__ void scan_resolve(const FusedParams &P, uint32_t d, uint64_t nl, uint64_t nb, uint64_t *line0,
                              uint64_t *byte0) {
+  (void)nl; (void)nb;
   const uint32_t l = lane_id();
-  unsigned long long *st = P.scan_state;
   const uint64_t agg = st_tag(P.epoch, ST_AGG), inc = st_tag(P.epoch, ST_INC);
-  const uint64_t VAL = (1ull << 46) - 1ull;
-  uint64_t ex_l = 0, ex_b = 0;
-  if (d == 0) { *line0 = 0; *byte0 = 0; return; }
-  long long j = (long long)d - 1;
-  for (;;) {
-    const long long idx = j - (long long)l;
-    uint64_t vl = 0, vb = 0;
-    bool is_inc = true;                              // positions before document 0: prefix 0
-    if (idx >= 0) {
-      for (;;) {
-        const uint64_t w0 = ld_acquire(st + 2ull * idx);
-        const uint64_t t0 = w0 & ~VAL;
-        if (t0 == agg || t0 == inc) {
-          const uint64_t w1 = ld_relaxed(st + 2ull * idx + 1);
-          if ((w1 & ~VAL) == t0) { vl = w0 & VAL; vb = w1 & VAL; is_inc = t0 == inc; break; }
-        }
-        __nanosleep(100);
-      }
-    }
-    const uint32_t incs = __ballot_sync(FULL, is_inc);
-    const uint32_t first = incs ? (uint32_t)__ffs(incs) - 1u : 32u;
-    if (l > first) { vl = 0; vb = 0; }
-    ex_l += warp_sum64(vl);
-    ex_b += warp_sum64(vb);
-    if (incs) break;
-    j -= 32;
+  const uint32_t k = d >> 5, p = d & 31u;
+  uint64_t vl = 0, vb = 0;
+  if (l < p) {                                       // earlier documents of the same block
+    const ScanWords w = scan_wait(P.scan_state + 2ull * (32u * k + l), agg, inc, false);
+    vl = w.l; vb = w.b;
+  } else if (l == 31u && k > 0) {                    // everything before the block
+    const ScanWords w = scan_wait(P.scan_blocks + 2ull * (k - 1u), agg, inc, true);
+    vl = w.l; vb = w.b;
   }
-  if (l == 0) {
-    st_relaxed(st + 2ull * d + 1, inc | (ex_b + nb));
-    st_release(st + 2ull * d, inc | (ex_l + nl));
-  }
-  *line0 = ex_l;
-  *byte0 = ex_b;
+  *line0 = warp_sum64(vl);
+  *byte0 = warp_sum64(vb);
 }
 
 // ---- fast path -------------------------------------------------------------------------------
@@ -189,7 +238,7 @@ struct Mailbox {
   uint32_t ng, np;
   uint32_t nl, nb;
   uint32_t total0;              // bytes of the lines half 0 measured
-  uint32_t pad;
+  uint32_t okf;                 // half 0: the floats formatted and the node lines fit
   unsigned long long line0, byte0;
   unsigned long long ticket;
 };
@@ -214,7 +263,7 @@ __device__ __forceinline__ void pid_probe(const FleetDev &f, uint32_t n, uint64_
 // Plans a regular document.  On success the team's slice holds the row records, the line
 // plan and the in-document offsets, and the mailbox its line and byte counts.
 __device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, const FusedParams &P, uint32_t *S,
-                          uint8_t *Sb, const WarpSlice &ws, uint32_t team, uint32_t half) {
+                          uint8_t *Sb, const WarpSlice &ws, uint32_t team, uint32_t half, long long &stage_t) {
   const uint32_t l = lane_id();
   volatile Mailbox *mb = reinterpret_cast<volatile Mailbox *>(Sb + ws.mbox);
   const uint32_t n = b.doc_node[d];
@@ -284,10 +333,12 @@ __device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, cons
     }
     if (l == 0) { mb->ok1 = ok ? 1u : 0u; mb->np = np_local; }
   }
+  STAGE_MARK(1);                                     // stage A work
   team_sync(team);
   if (!(mb->ok0 & mb->ok1)) return false;
   const uint32_t ng = mb->ng, np = mb->np, nc = hd.nc;
   team_sync(team);                                   // the mailbox may be rewritten now
+  STAGE_MARK(2);                                     // waiting for the other half
 
   // ---- stage B (half 1): uuid -> short id (gpu.py:151), pid -> container (gpu.py:177-178),
   //      place inside the container; further chunks of 32 rows are parsed here as well ----
@@ -358,9 +409,17 @@ __device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, cons
       __syncwarp();
     }
     if (l == 0) mb->ok1 = all_ok ? 1u : 0u;
+  } else {
+    // half 0 meanwhile: repr(mem_util) and the node line lengths (gpu.py:135-143)
+    bool fok = true;
+    if (l < ng) fok = finish_gpu_row(TG, grec[l]);
+    fok = __all_sync(FULL, fok);
+    if (l == 0) mb->okf = fok ? 1u : 0u;
   }
+  STAGE_MARK(3);                                     // stage B work (half 1) / floats (half 0)
   team_sync(team);
-  if (!mb->ok1) return false;
+  if (!(mb->okf & mb->ok1)) return false;
+  STAGE_MARK(4);
 
   // ---- stage C (half 0): containers in docker stats order: busy lines, or idle lines
   //      (gpu.py:174-253); node entries and idle entries of the plan ----
@@ -398,9 +457,11 @@ __device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, cons
       }
     }
   }
+  STAGE_MARK(5);                                     // stage C work (half 0)
   team_sync(team);
   if (!mb->ok0) return false;
   const uint32_t nl = mb->nl;
+  STAGE_MARK(6);
   if (half == 1) {                                   // busy entries (needs cstart)
     for (uint32_t r = l; r < np; r += 32) {
       const PRec &p = prec[r];
@@ -409,6 +470,7 @@ __device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, cons
   }
   team_sync(team);
 
+  STAGE_MARK(7);                                     // busy entries + barrier
   // ---- stage D: line lengths -> offsets inside the document; each half measures half of
   //      the lines, half 1 then shifts its offsets by half 0's bytes ----
   const uint32_t mid = (nl + 1u) >> 1;
@@ -448,6 +510,7 @@ __device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, cons
     if (l == 0) loff[nl] = total;
   }
   team_sync(team);
+  STAGE_MARK(8);                                     // stage D
   if (half == 0 && l == 0) { mb->nb = total; }
   team_sync(team);
   return true;
@@ -461,7 +524,8 @@ __device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, cons
 // that copy, so the look-back that yields it (scan_resolve, half 0) runs after the first
 // round of lines has been composed.
 __device__ void fast_emit(const FusedParams &P, const WorkDev &w, uint32_t *S, uint8_t *Sb, const WarpSlice &ws,
-                          uint32_t team, uint32_t half, uint32_t d, uint32_t n_docs, uint32_t nl, uint32_t nb) {
+                          uint32_t team, uint32_t half, uint32_t d, uint32_t n_docs, uint32_t nl, uint32_t nb,
+                          long long &stage_t) {
   const uint32_t l = lane_id();
   volatile Mailbox *mb = reinterpret_cast<volatile Mailbox *>(Sb + ws.mbox);
   const TbHeader &hd = *reinterpret_cast<const TbHeader *>(Sb + ws.tb);
@@ -501,6 +565,7 @@ __device__ void fast_emit(const FusedParams &P, const WorkDev &w, uint32_t *S, u
         write_line(S, ws.stage + (loff[i] - r_lo), segs);
       }
     }
+    STAGE_MARK(9);                                   // segments + compose
     if (!resolved) {
       if (half == 0) {
         scan_resolve(P, d, nl, nb, &line0, &byte0);
@@ -529,6 +594,7 @@ __device__ void fast_emit(const FusedParams &P, const WorkDev &w, uint32_t *S, u
     } else {
       team_sync(team);                               // lines of this round composed
     }
+    STAGE_MARK(10);                                  // look-back + barrier
     if (!fits_out || nl == 0) return;
     for (uint32_t i = i0 + 32u * half + l; i < i1; i += 64u) w.line_off[line0 + i] = byte0 + loff[i];
     // stage -> global, the vectors dealt alternately to the two warps
@@ -552,6 +618,7 @@ __device__ void fast_emit(const FusedParams &P, const WorkDev &w, uint32_t *S, u
     }
     const uint32_t done = head + 16u * nvec;
     if (half == 1 && l < nbytes - done) g[done + l] = st[done + l];
+    STAGE_MARK(11);                                  // line_off + copy-out
     i0 = i1;
     team_sync(team);                                 // the stage may be overwritten
   } while (i0 < nl);
@@ -632,13 +699,18 @@ __global__ void __launch_bounds__(POLL_THREADS, 2) k_poll(BatchDev b, FleetDev f
     const unsigned long long t = mb->ticket;
     if (t >= b.n_docs) break;
     const uint32_t d = (uint32_t)t;
-    const bool fastdoc = P.allow_fast && fast_plan(d, b, f, P, S, Sb, ws, team, half);
+    long long stage_t = 0;
+#ifdef KGM_PROFILE_STAGES
+    stage_t = clock64();
+#endif
+    const bool fastdoc = P.allow_fast && fast_plan(d, b, f, P, S, Sb, ws, team, half, stage_t);
     if (fastdoc) {
       const uint32_t nl = mb->nl, nb = mb->nb;
       team_sync(team);
-      if (half == 0) scan_publish(P, d, nl, nb);
-      fast_emit(P, w, S, Sb, ws, team, half, d, b.n_docs, nl, nb);
+      if (half == 0) scan_publish(P, d, b.n_docs, nl, nb);
+      fast_emit(P, w, S, Sb, ws, team, half, d, b.n_docs, nl, nb, stage_t);
       team_sync(team);
+      STAGE_MARK(12);                                // last barrier
       continue;
     }
     team_sync(team);                                 // both halves have left the fast path
@@ -646,7 +718,7 @@ __global__ void __launch_bounds__(POLL_THREADS, 2) k_poll(BatchDev b, FleetDev f
       uint32_t nl = 0, nb = 0;
       slow_plan(d, b, f, w, S + (ws.stage >> 2), &nl, &nb);
       if (l == 0) atomicAdd(w.counters + CTR_SLOW, 1u);
-      scan_publish(P, d, nl, nb);
+      scan_publish(P, d, b.n_docs, nl, nb);
       uint64_t line0, byte0;
       scan_resolve(P, d, nl, nb, &line0, &byte0);
       if (P.carry) { line0 += P.carry[0]; byte0 += P.carry[1]; }
@@ -674,6 +746,15 @@ __global__ void __launch_bounds__(POLL_THREADS, 2) k_poll(BatchDev b, FleetDev f
 }
 
 }  // namespace
+
+int debug_stage_clocks(unsigned long long *out64) {
+#ifdef KGM_PROFILE_STAGES
+  return cudaMemcpyFromSymbol(out64, g_stage_clk, sizeof(g_stage_clk)) == cudaSuccess ? 64 : -1;
+#else
+  (void)out64;
+  return 0;
+#endif
+}
 
 int poll_smem_bytes(const FusedParams &P) { return (int)(CONST_PAD + P.teams * P.warp_bytes); }
 

@@ -46,7 +46,8 @@ def build_library(force=False, verbose=False):
     deps = srcs + [os.path.join(CSRC, h) for h in HEADERS] + [os.path.join(ROOT, "include", "kgm.h")]
     if force or _stale(LIB, deps):
         nvcc = os.environ.get("NVCC", "nvcc")
-        out = _run([nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + srcs + ["-o", LIB])
+        extra = os.environ.get("KGM_NVCC_DEFINES", "").split()      # e.g. -DKGM_PROFILE_STAGES
+        out = _run([nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + srcs + ["-o", LIB])
         if verbose:
             print(out)
     return LIB

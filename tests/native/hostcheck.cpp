@@ -160,6 +160,7 @@ int hc_fast_node_line(const char *host, const uint8_t *row, uint32_t row_len, ui
   FastSlice sl = make_slice(row, row_len, shift, row, 0, 0, tb);
   fast::GRec g;
   if (!fast::parse_gpu_row(sl.words.data() + sl.tg / 4, shift, shift + row_len, node_fixed, sid, g)) return -1;
+  if (!fast::finish_gpu_row(sl.words.data() + sl.tg / 4, g)) return -1;
   fast::GRec *gr = reinterpret_cast<fast::GRec *>(sl.bytes() + sl.rec);
   *gr = g;
   *planned = g.line_len;
@@ -181,6 +182,7 @@ int hc_fast_busy_line(const char *host, const char *ns, const char *cid, const c
   const uint32_t ashift = (shift * 7 + 3) & 15;
   fast::GRec g;
   if (!fast::parse_gpu_row(sl.words.data() + sl.tg / 4, shift, shift + grow_len, node_fixed, sid, g)) return -1;
+  if (!fast::finish_gpu_row(sl.words.data() + sl.tg / 4, g)) return -1;
   fast::PRec p;
   uint32_t kw[fast::KEY_WORDS], klen;
   uint64_t kh;

@@ -1,0 +1,28 @@
+"""Per-stage SM clocks of the fused kernel (needs a library built with
+KGM_NVCC_DEFINES=-DKGM_PROFILE_STAGES; rebuild without it afterwards)."""
+import ctypes as C, os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "k8s-gpu-monitor_b200"), os.path.join(ROOT, "tests")]
+from kgm import _ffi, monitor, replay
+from fleet_util import entry_of_snap
+rp = replay.make_replay(seed=0, **replay.CONFIGS["config2"])
+names = {1: "A work", 2: "A wait", 3: "B work", 4: "B wait", 5: "C work", 6: "C wait", 7: "busy entries+wait",
+         8: "D lengths", 9: "segments+compose", 10: "look-back+wait", 11: "line_off+copy-out", 12: "last barrier"}
+with monitor.Monitor(0) as mon:
+    mon.load_fleet([entry_of_snap(s) for s in rp.nodes])
+    batch = mon.make_batch(rp.gpu_texts, rp.apps_texts, rp.doc_node, rp.doc_tick, pinned=True)
+    mon.upload(batch)
+    reps = 5
+    for _ in range(reps):
+        mon.encode_resident()
+    buf = (C.c_uint64 * 64)()
+    n = _ffi.load().kgm_debug_stage_clocks(buf)
+    print("values", n, "kernel ms", mon.timing()["encode_ms"])
+    docs = rp.n_docs * reps
+    for half in (0, 1):
+        tot = 0
+        for st in range(1, 13):
+            v = buf[half * 32 + st] / docs
+            tot += v
+            print("half %d  %-22s %8.0f clk/doc" % (half, names[st], v))
+        print("half %d  total %8.0f clk/doc" % (half, tot))
