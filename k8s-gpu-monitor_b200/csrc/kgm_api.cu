@@ -108,7 +108,7 @@ struct kgm_ctx {
   cudaEvent_t ev_in[MAX_CHUNKS] = {}, ev_k[MAX_CHUNKS] = {};
   HostBuf h_chunk;                         // per chunk: totals {lines, bytes} + counters
   uint32_t last_chunks = 1;
-  uint32_t force_teams = 0;                // KGM_FUSED_TEAMS=3|4 (experiments)
+  uint32_t force_teams = 0;                // KGM_FUSED_TEAMS=4..8: documents in flight per SM (experiments)
   int reserve_ctas = 0;                    // KGM_RESERVE_CTAS: CTA slots k_poll leaves free (for NCCL kernels)
   // window reductions
   uint32_t max_tick = 0;
@@ -442,24 +442,36 @@ FusedFit fused_layout(kgm_ctx *ctx, const kgm_batch *b, int ctas, uint32_t teams
 void plan_fused(kgm_ctx *ctx, const kgm_batch *b, uint64_t max_g, uint64_t max_a) {
   ctx->fused_ok = false;
   if (b->n_docs == 0) return;
-  // Four teams per CTA unless the stage of such a slice cannot hold a whole document of this
-  // batch (lines are ~3.4x the text): then the two warps of a team would each compose
-  // half-empty rounds, and three teams with larger slices do better.
+  // Candidates: (CTAs per SM, teams per CTA) = 2x4, 2x3, 1x7, 1x6, 1x5, 1x4, i.e. 8 .. 4
+  // documents in flight per SM with slices of 28 .. 56 KB.  A candidate is usable if at
+  // least 90 % of the documents fit its slices; preferred is the one whose stage holds a
+  // whole document (lines are ~3.4x the text: otherwise the two warps of a team compose
+  // half-empty rounds) and that needs the fewest waves of documents -- the look-back keeps
+  // the teams roughly in step, so a batch takes ceil(documents / teams) waves.
+  static const int cand[][2] = {{2, 4}, {1, 7}, {2, 3}, {1, 6}, {1, 5}, {1, 4}};
   const uint64_t est_out = (max_g + max_a) * 17 / 5 + 256;
-  FusedFit two = fused_layout(ctx, b, 2, ctx->force_teams ? ctx->force_teams : 4, max_g, max_a);
-  if (!ctx->force_teams && two.ok && two.P.stage_bytes < est_out) {
-    const FusedFit three = fused_layout(ctx, b, 2, 3, max_g, max_a);
-    if (three.ok && three.P.stage_bytes >= est_out && three.fits >= two.fits) two = three;
+  FusedFit best{};
+  int best_ctas = 0;
+  double best_cost = 0;
+  uint64_t most_fits = 0;
+  FusedFit fallback{};
+  int fallback_ctas = 0;
+  for (const auto &c : cand) {
+    if (ctx->force_teams && (uint32_t)(c[0] * c[1]) != ctx->force_teams) continue;
+    const FusedFit f = fused_layout(ctx, b, c[0], (uint32_t)c[1], max_g, max_a);
+    if (!f.ok) continue;
+    if (f.fits > most_fits || !fallback.ok) { most_fits = f.fits; fallback = f; fallback_ctas = c[0]; }
+    if (f.fits * 10 < (uint64_t)b->n_docs * 9) continue;
+    const uint64_t teams = (uint64_t)ctx->sms * c[0] * c[1];
+    const double waves = (double)((b->n_docs + teams - 1) / teams);
+    const double rounds = f.P.stage_bytes >= est_out ? 1.0 : 1.35;       // half-empty rounds cost
+    const double cost = waves * rounds * (1.0 + 0.03 * (c[0] * c[1] - 4));   // more in flight: a little slower each
+    if (!best.ok || cost < best_cost) { best = f; best_ctas = c[0]; best_cost = cost; }
   }
-  FusedFit pick = two;
-  int ctas = 2;
-  if (!two.ok || two.fits * 10 < (uint64_t)b->n_docs * 9) {
-    const FusedFit one = fused_layout(ctx, b, 1, 4, max_g, max_a);
-    if (one.ok && (!two.ok || one.fits > two.fits + b->n_docs / 20)) { pick = one; ctas = 1; }
-  }
-  if (!pick.ok) return;
-  ctx->fused = pick.P;
-  ctx->fused_ctas_per_sm = ctas;
+  if (!best.ok) { best = fallback; best_ctas = fallback_ctas; }
+  if (!best.ok) return;
+  ctx->fused = best.P;
+  ctx->fused_ctas_per_sm = best_ctas;
   ctx->fused_ok = true;
 }
 
@@ -708,8 +720,7 @@ int kgm_create(kgm_ctx **out, int device) {
   ctx->sms = prop.multiProcessorCount;
   if (const char *env = getenv("KGM_RESERVE_CTAS")) ctx->reserve_ctas = std::max(0, std::min(atoi(env), 128));
   if (const char *env = getenv("KGM_FUSED_TEAMS")) {
-    if (!strcmp(env, "3")) ctx->force_teams = 3;
-    else if (!strcmp(env, "4")) ctx->force_teams = 4;
+    ctx->force_teams = (uint32_t)std::max(0, std::min(atoi(env), 8));
   }
   if (const char *env = getenv("KGM_PIPELINE")) {
     if (!strcmp(env, "staged")) ctx->pipeline = KGM_PIPELINE_STAGED;

@@ -138,7 +138,9 @@ struct RowShape {
   bool irregular;
 };
 
-// cells of a row [s, e): the first WANT commas are recorded (more are counted, not stored)
+// cells of a row [s, e) (at most 1000 bytes): the first WANT commas are recorded (more are
+// counted, not stored).  Lanes meet commas in different words, so the per-comma work inside
+// the word loop is kept to a shift-or into a packed register (10 bits per position).
 template <int WANT>
 KGM_HD void scan_commas(const uint32_t *W, uint32_t s, uint32_t e, RowShape &r) {
   r.ncommas = 0;
@@ -149,6 +151,7 @@ KGM_HD void scan_commas(const uint32_t *W, uint32_t s, uint32_t e, RowShape &r) 
   for (int i = 0; i < 6; ++i) r.comma[i] = 0;
   if (s >= e) return;
   uint32_t bad = 0, n = 0;
+  uint64_t packed = 0;
   auto word = [&](uint32_t wi, uint32_t w) {
     // any byte >= 0x80, < 0x20 or == '"' makes the row irregular ("any" tests, not positions)
     const uint32_t q = w ^ 0x22222222u;
@@ -162,11 +165,7 @@ KGM_HD void scan_commas(const uint32_t *W, uint32_t s, uint32_t e, RowShape &r) 
       const uint32_t bit = __builtin_ctz(cm);
 #endif
       cm &= cm - 1;
-      const uint32_t pos = (wi << 2) + (bit >> 3);
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-      for (int i = 0; i < WANT; ++i) if (n == (uint32_t)i) r.comma[i] = (uint16_t)pos;
+      if (n < (uint32_t)WANT) packed |= (uint64_t)((wi << 2) + (bit >> 3) - s) << (10u * n);
       ++n;
     }
   };
@@ -179,6 +178,10 @@ KGM_HD void scan_commas(const uint32_t *W, uint32_t s, uint32_t e, RowShape &r) 
   for (uint32_t wi = a + 1; wi < z; ++wi) word(wi, W[wi]);
   if (z > a) word(z, (W[z] & keep_z) | (0x61616161u & ~keep_z));
   bad &= 0x80808080u;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int i = 0; i < WANT; ++i) r.comma[i] = (uint16_t)(s + ((uint32_t)(packed >> (10 * i)) & 0x3ffu));
   r.ncommas = n;
   r.irregular = bad != 0;
 }
@@ -225,7 +228,7 @@ KGM_HD uint64_t run_value(const uint32_t *W, Run r) {               // int(digit
 // mem_util) for rows on which the reference raises nothing.
 KGM_HD bool parse_gpu_row(const uint32_t *W, uint32_t s, uint32_t e, uint32_t node_fixed,
                           uint32_t sid, GRec &g) {
-  if (e <= s || e - s > 4000) return false;
+  if (e <= s || e - s > 1000) return false;
   RowShape sh;
   scan_commas<6>(W, s, e, sh);
   if (sh.irregular || sh.ncommas < 5) return false;               // fewer than 6 cells: KeyError
@@ -264,7 +267,7 @@ KGM_HD bool finish_gpu_row(const uint32_t *W, GRec &g) {
 // dictionary lookup), `klen` its length.  Returns false = irregular.
 KGM_HD bool parse_proc_row(const uint32_t *W, uint32_t s, uint32_t e, PRec &p, uint32_t *kw,
                            uint32_t *klen, uint64_t *khash) {
-  if (e <= s || e - s > 4000) return false;
+  if (e <= s || e - s > 1000) return false;
   RowShape sh;
   scan_commas<4>(W, s, e, sh);
   if (sh.irregular || sh.ncommas < 3) return false;               // KeyError gpu.py:53 / 204
@@ -281,27 +284,14 @@ KGM_HD bool parse_proc_row(const uint32_t *W, uint32_t s, uint32_t e, PRec &p, u
   } else {
     p.pidkey = ~0ull;
   }
-  // process name: runs between spaces (gpu.py:203 .replace(' ', ''))
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-  for (int i = 0; i < NAME_RUNS; ++i) { p.name[i].off = (uint16_t)(c0 + 1); p.name[i].len = 0; }
+  // process name: runs between spaces (gpu.py:203 .replace(' ', '')).  The positions of up
+  // to NAME_RUNS-1 spaces are packed into one register inside the word loop (lanes meet
+  // their spaces in different words); the runs are cut afterwards.
   {
-    uint32_t nruns = 0, start = c0 + 1;
-    bool many = false;
-    auto close_run = [&](uint32_t pos) {
-      if (pos > start) {
-        if (nruns >= (uint32_t)NAME_RUNS) many = true;
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-        for (int i = 0; i < NAME_RUNS; ++i)
-          if (nruns == (uint32_t)i) { p.name[i].off = (uint16_t)start; p.name[i].len = (uint16_t)(pos - start); }
-        ++nruns;
-      }
-      start = pos + 1;
-    };
-    const uint32_t lo = c0 + 1, hi = c1;
+    uint32_t lo = c0 + 1;
+    const uint32_t hi = c1;
+    if (lo < hi && load1(W, lo) == 32u) ++lo;                     // the cell's usual leading space
+    uint32_t sp = 0, ns = 0;
     for (uint32_t wi = lo >> 2; lo < hi && wi <= (hi - 1) >> 2; ++wi) {
       uint32_t w = W[wi];
       const uint32_t base = wi << 2;
@@ -317,11 +307,22 @@ KGM_HD bool parse_proc_row(const uint32_t *W, uint32_t s, uint32_t e, PRec &p, u
         const uint32_t bit = __builtin_ctz(sm);
 #endif
         sm &= sm - 1;
-        close_run(base + (bit >> 3));
+        if (ns < (uint32_t)NAME_RUNS - 1u) sp |= (base + (bit >> 3) - lo) << (10u * ns);
+        ++ns;
       }
     }
-    close_run(hi);
-    if (many) return false;
+    if (ns > (uint32_t)NAME_RUNS - 1u) return false;
+    uint32_t start = lo;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int i = 0; i < NAME_RUNS; ++i) {
+      const uint32_t end = (uint32_t)i < ns ? lo + ((sp >> (10 * i)) & 0x3ffu) : hi;
+      const bool live = (uint32_t)i <= ns && lo <= hi;
+      p.name[i].off = (uint16_t)(live ? start : lo);
+      p.name[i].len = (uint16_t)(live && end > start ? end - start : 0u);
+      start = end + 1;
+    }
   }
   // gpu_uuid = lstrip(cell 2) (gpu.py:115)
   uint32_t k = c1 + 1;

@@ -25,7 +25,7 @@ namespace {
 
 using namespace fast;
 
-constexpr int POLL_THREADS = 256;                   // at most 4 teams of 2 warps per CTA; a team owns a document
+constexpr int POLL_THREADS = 512;                   // at most 8 teams of 2 warps per CTA (128 registers per thread)
 constexpr uint32_t CONST_PAD = (ConstArea::BYTES + 15u) & ~15u;
 constexpr uint32_t KIND_NODE = 0, KIND_BUSY = 1, KIND_IDLE = 2;
 constexpr uint32_t IDLE_NONE = 0xfffu;
@@ -524,8 +524,8 @@ __device__ bool fast_plan(uint32_t d, const BatchDev &b, const FleetDev &f, cons
 // that copy, so the look-back that yields it (scan_resolve, half 0) runs after the first
 // round of lines has been composed.
 __device__ void fast_emit(const FusedParams &P, const WorkDev &w, uint32_t *S, uint8_t *Sb, const WarpSlice &ws,
-                          uint32_t team, uint32_t half, uint32_t d, uint32_t n_docs, uint32_t nl, uint32_t nb,
-                          long long &stage_t) {
+                          uint32_t team, uint32_t half, uint32_t d, uint32_t n_docs, uint32_t ng, uint32_t nl,
+                          uint32_t nb, long long &stage_t) {
   const uint32_t l = lane_id();
   volatile Mailbox *mb = reinterpret_cast<volatile Mailbox *>(Sb + ws.mbox);
   const TbHeader &hd = *reinterpret_cast<const TbHeader *>(Sb + ws.tb);
@@ -546,7 +546,13 @@ __device__ void fast_emit(const FusedParams &P, const WorkDev &w, uint32_t *S, u
       r_lo = loff[i0];
       // the next `per` lines, fewer if their bytes exceed the stage (both warps compute the same)
       while (i1 > i0 + 1 && loff[i1] - r_lo + 64u > P.stage_bytes) i1 = i0 + ((i1 - i0) >> 1);
-      const uint32_t cnt = i1 - i0, first = half ? (cnt + 1u) >> 1 : 0u, last = half ? cnt : (cnt + 1u) >> 1;
+      // split of the round between the two warps: the node lines (a different segment
+      // list, so mixing them with pod lines in one warp costs both code paths) go to half 0
+      // alone when the pod lines of the round fit one warp; otherwise half and half
+      const uint32_t cnt = i1 - i0;
+      uint32_t cut = (cnt + 1u) >> 1;
+      if (i0 < ng && i1 > ng && ng - i0 <= 32u && i1 - ng <= 32u) cut = ng - i0;
+      const uint32_t first = half ? cut : 0u, last = half ? cnt : cut;
       const uint32_t i = i0 + first + l;
       if (i < i0 + last) {
         const uint32_t pl = plan[i], kind = pl >> 30;
@@ -671,7 +677,7 @@ __device__ void slow_emit(uint32_t d, const BatchDev &b, const FleetDev &f, cons
   }
 }
 
-__global__ void __launch_bounds__(POLL_THREADS, 2) k_poll(BatchDev b, FleetDev f, WorkDev w, FusedParams P) {
+__global__ void __launch_bounds__(POLL_THREADS, 1) k_poll(BatchDev b, FleetDev f, WorkDev w, FusedParams P) {
   extern __shared__ __align__(16) uint32_t S[];
   uint8_t *Sb = reinterpret_cast<uint8_t *>(S);
   // constant strings (same for every CTA)
@@ -705,10 +711,10 @@ __global__ void __launch_bounds__(POLL_THREADS, 2) k_poll(BatchDev b, FleetDev f
 #endif
     const bool fastdoc = P.allow_fast && fast_plan(d, b, f, P, S, Sb, ws, team, half, stage_t);
     if (fastdoc) {
-      const uint32_t nl = mb->nl, nb = mb->nb;
+      const uint32_t ng = mb->ng, nl = mb->nl, nb = mb->nb;
       team_sync(team);
       if (half == 0) scan_publish(P, d, b.n_docs, nl, nb);
-      fast_emit(P, w, S, Sb, ws, team, half, d, b.n_docs, nl, nb, stage_t);
+      fast_emit(P, w, S, Sb, ws, team, half, d, b.n_docs, ng, nl, nb, stage_t);
       team_sync(team);
       STAGE_MARK(12);                                // last barrier
       continue;

@@ -206,7 +206,7 @@ def test_full_config2_properties_and_sampled_parity(mon):
         # the clean fleet batch goes through the fast path entirely (or not at all when it is off)
         assert t["launches"] == 1 and t["fused"] == 1
         assert t["slow_docs"] == (0 if mon.pipeline_name == "fused" else rp.n_docs)
-        assert t["fused_ctas_per_sm"] == 2                          # the fleet batch fits two CTAs per SM
+        assert t["fused_ctas_per_sm"] in (1, 2)                     # 1 x 7 or 2 x 3/4 teams per SM
 
 
 def test_mem_util_floats_parse_back_within_tolerance(mon):
