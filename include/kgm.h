@@ -149,7 +149,9 @@ int  kgm_load_fleet(kgm_ctx *ctx, const kgm_fleet *fleet);
 
 /* Replaces gpu.py:104-256 (parse both nvidia-smi texts, node lines, join, pod lines) for
  * a batch held in HOST memory: copies the batch to the device, runs the pipeline and, if
- * want_host_copy != 0, copies lines / offsets / statuses back into pinned host buffers.  */
+ * want_host_copy != 0, copies lines / offsets / statuses back into pinned host buffers.
+ * A large batch is cut into chunks whose text copies, kernels and result copies overlap;
+ * the result is the same bytes.  The batch is resident afterwards.                        */
 int  kgm_encode_batch(kgm_ctx *ctx, const kgm_batch *batch, int want_host_copy, kgm_result *out);
 
 /* The same in two steps, for callers that keep a batch resident in HBM and run it more
@@ -202,6 +204,12 @@ int  kgm_window_reduce(kgm_ctx *ctx, uint32_t window_ticks, int want_host_copy, 
  * stages for each of a team's two warps, accumulated since load) to `out64` and returns 64;
  * returns 0 in a normal build.                                                            */
 int  kgm_debug_stage_clocks(uint64_t *out64);
+
+/* Debug aid (no counterpart in the reference): after a chunked end-to-end kgm_encode_batch
+ * call, the times (ms since the call's first device operation) at which each chunk's text
+ * had arrived (`text_in_ms`) and its kernel had finished (`kernel_done_ms`); both arrays take
+ * up to `cap` values.  Returns the number of chunks of the last call (1: not chunked).      */
+int  kgm_debug_chunk_times(kgm_ctx *ctx, float *text_in_ms, float *kernel_done_ms, uint32_t cap);
 
 /* Which kernels run a batch (no counterpart in the reference; results are identical):
  *   AUTO           one fused single-pass kernel when the batch fits its shared-memory slices,

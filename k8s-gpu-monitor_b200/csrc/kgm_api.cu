@@ -4,10 +4,13 @@
 // kgm_kernels.cu.  There is deliberately no CPU implementation behind these entry points.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <new>
 #include <string>
 #include <vector>
@@ -45,7 +48,7 @@ struct HostBuf {
     if (p) cudaFreeHost(p);
     p = nullptr; cap = 0;
     bytes = (bytes + 4095) & ~(size_t)4095;
-    cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocDefault);
+    cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocMapped);      // kernels may write it (unified addressing)
     if (e == cudaSuccess) cap = bytes;
     return e;
   }
@@ -55,6 +58,8 @@ struct HostBuf {
 
 enum { EV_START = 0, EV_H2D, EV_TOK, EV_JOIN, EV_SCAN, EV_ENC, EV_D2H, EV_COUNT };
 constexpr int MAX_CHUNKS = 8;
+constexpr uint32_t CTR_RING = 16;        // counter sets: launch e uses set e % CTR_RING and zeroes the next one,
+                                         // so the sets of the last CTR_RING - 1 launches can still be read
 
 }  // namespace
 
@@ -99,14 +104,18 @@ struct kgm_ctx {
   DevBuf f_node_fast, f_tb_off, f_tb_len, f_tb_pool, f_pid16, f_vis_hash2;
   uint32_t fast_max_nc = 1, fast_max_tb = 0, fast_max_idle = 0, any_fast = 0;
   std::vector<uint8_t> h_node_fast;        // host copies of FleetDev::node_fast / tb_len
+  bool all_nodes_fast = false;
   std::vector<uint32_t> h_tb_len;
   uint32_t slow_docs = 0;
   bool last_fused = false;
   bool totals_external = false;            // chunked path: every chunk has its own totals slot
+  bool chunk_launch = false;               // chunked path: no timing events around the single launches
   // chunked end-to-end path: copies and kernels of consecutive chunks overlap
   cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
   cudaEvent_t ev_in[MAX_CHUNKS] = {}, ev_k[MAX_CHUNKS] = {};
-  HostBuf h_chunk;                         // per chunk: totals {lines, bytes} + counters
+  HostBuf h_chunk;                         // per chunk: posted totals {lines, bytes, seq} + counters
+  HostBuf h_docarr;                        // staging of the per-document arrays
+  uint64_t post_seq = 0;
   uint32_t last_chunks = 1;
   uint32_t force_teams = 0;                // KGM_FUSED_TEAMS=4..8: documents in flight per SM (experiments)
   int reserve_ctas = 0;                    // KGM_RESERVE_CTAS: CTA slots k_poll leaves free (for NCCL kernels)
@@ -175,9 +184,9 @@ int ensure_workspace(kgm_ctx *ctx) {
   CU(ctx->w_line_off.ensure(((size_t)ctx->desc_cap + 1) * sizeof(uint64_t)));
   {
     const size_t before = ctx->w_counters.cap;
-    CU(ctx->w_counters.ensure(2 * CTR_SET * sizeof(uint32_t)));
+    CU(ctx->w_counters.ensure(CTR_RING * CTR_SET * sizeof(uint32_t)));
     if (ctx->w_counters.cap != before) {
-      CU(cudaMemsetAsync(ctx->w_counters.p, 0, 2 * CTR_SET * sizeof(uint32_t), ctx->stream));
+      CU(cudaMemsetAsync(ctx->w_counters.p, 0, CTR_RING * CTR_SET * sizeof(uint32_t), ctx->stream));
       ctx->counters_clean = true;
     }
     const size_t tb = ctx->w_ticket.cap;
@@ -236,8 +245,8 @@ int launch_pipeline(kgm_ctx *ctx) {
       CU(cudaMemsetAsync(ctx->w_scan.p, 0, ctx->w_scan.cap, ctx->stream));
     }
     if (!ctx->counters_clean)
-      CU(cudaMemsetAsync(cbase, 0, 2 * CTR_SET * sizeof(uint32_t), ctx->stream));
-    const uint32_t cur = ctx->epoch & 1u;
+      CU(cudaMemsetAsync(cbase, 0, CTR_RING * CTR_SET * sizeof(uint32_t), ctx->stream));
+    const uint32_t cur = ctx->epoch % CTR_RING;
     ctx->work.counters = cbase + cur * CTR_SET;
     if (!ctx->totals_external) ctx->work.totals = reinterpret_cast<uint64_t *>(ctx->work.counters + CTR_TOTALS);
     FusedParams P = ctx->fused;
@@ -247,15 +256,15 @@ int launch_pipeline(kgm_ctx *ctx) {
     P.ticket_base = ctx->ticket_next;
     P.scan_state = ctx->w_scan.as<unsigned long long>();
     P.scan_blocks = P.scan_state + 2ull * ctx->scan_docs_cap;
-    P.next_counters = cbase + (1u - cur) * CTR_SET;
+    P.next_counters = cbase + ((cur + 1u) % CTR_RING) * CTR_SET;
     const uint32_t n = ctx->batch.n_docs;
     const int wpb = (int)P.teams;                   // teams (documents in flight) per CTA
     int blocks = (int)((n + wpb - 1) / wpb);
     blocks = std::max(1, std::min(blocks, ctx->sms * ctx->fused_ctas_per_sm - ctx->reserve_ctas));
     ctx->ticket_next += (unsigned long long)n + (unsigned long long)blocks * wpb;
-    CU(cudaEventRecord(ctx->ev[EV_SCAN], ctx->stream));
+    if (!ctx->chunk_launch) CU(cudaEventRecord(ctx->ev[EV_SCAN], ctx->stream));
     launch_poll(ctx->batch, ctx->fleet, ctx->work, P, blocks, ctx->stream);
-    CU(cudaEventRecord(ctx->ev[EV_ENC], ctx->stream));
+    if (!ctx->chunk_launch) CU(cudaEventRecord(ctx->ev[EV_ENC], ctx->stream));
     CU(cudaGetLastError());
     ctx->counters_clean = true;                     // k_poll zeroed the other set
     ctx->last_fused = true;
@@ -299,7 +308,7 @@ int run_resident(kgm_ctx *ctx, bool with_h2d_event) {
       ctx->n_lines = ht[0];
       ctx->n_bytes = ht[1];
       ctx->have_result = true;
-      return KGM_OK;
+          return KGM_OK;
     }
     if (ovf & OVF_GROW) ctx->grow_cap = std::max(ctx->grow_cap * 2, hc[CTR_GROW] + 64);
     if (ovf & OVF_PROW) ctx->prow_cap = std::max(ctx->prow_cap * 2, hc[CTR_PROW] + 64);
@@ -337,6 +346,16 @@ void fill_result_dev(kgm_ctx *ctx, kgm_result *out) {
   out->n_lines = ctx->n_lines;
   out->doc_line_off = ctx->work.doc_line_off;
   out->doc_status = ctx->work.doc_status;
+  out->n_docs = ctx->batch.n_docs;
+}
+
+void fill_result_host(kgm_ctx *ctx, kgm_result *out) {
+  out->lines = ctx->h_lines.as<uint8_t>();
+  out->n_bytes = ctx->n_bytes;
+  out->line_off = ctx->h_line_off.as<uint64_t>();
+  out->n_lines = ctx->n_lines;
+  out->doc_line_off = ctx->h_doc_line_off.as<uint64_t>();
+  out->doc_status = ctx->h_status.as<int32_t>();
   out->n_docs = ctx->batch.n_docs;
 }
 
@@ -425,7 +444,14 @@ FusedFit fused_layout(kgm_ctx *ctx, const kgm_batch *b, int ctas, uint32_t teams
   P.warp_bytes = warp_bytes;
   P.stage_bytes = warp_bytes - o;
   P.teams = teams;
-  // how many documents can take the fast path with these caps (same tests as fast_plan)
+  // how many documents can take the fast path with these caps (same tests as fast_plan);
+  // no need to look at them one by one when even the longest texts and blocks fit
+  if (ctx->all_nodes_fast && max_g + 30 + 32 <= P.cap_g && max_a + 30 + 32 <= P.cap_a &&
+      (uint64_t)ctx->fast_max_tb + 16 <= P.cap_t) {
+    f.fits = b->n_docs;
+    f.ok = true;
+    return f;
+  }
   for (uint32_t d = 0; d < b->n_docs; ++d) {
     const uint32_t nd = b->doc_node[d];
     const uint64_t g_lo = b->gpu_off[d], g_hi = b->gpu_off[d + 1], a_lo = b->apps_off[d], a_hi = b->apps_off[d + 1];
@@ -549,40 +575,99 @@ int upload_batch(kgm_ctx *ctx, const kgm_batch *b) {
 }
 
 // End-to-end path for a large batch in host memory: the batch is cut into up to
-// MAX_CHUNKS runs of documents; the text copy of chunk c+1, the fused kernel of chunk c and
-// the result copy of chunk c-1 run at the same time on three streams.  Every kernel takes
-// the running {lines, bytes} of its predecessors from device memory, so the chunks write
-// one contiguous result, identical to the one-launch result.  Returns 1 if a workspace
-// guess was too small (the caller then runs the plain path on the resident batch).
+// MAX_CHUNKS runs of documents (small ones first and last, so that the copies start early
+// and the tail is short); the text copy of chunk c+1, the fused kernel of chunk c and the
+// result copy of chunk c-1 run at the same time on three streams.  Every kernel takes the
+// running {lines, bytes} of its predecessors from device memory, so the chunks write one
+// contiguous result, identical to the one-launch result, and posts its own running totals
+// into mapped host memory: the host learns the size of a chunk's lines without a stream
+// synchronisation or a small copy queued behind the large ones, and queues the copy of
+// chunk c while that of chunk c-1 is still running.  Returns 1 if a workspace guess was too
+// small (the caller then runs the plain path on the resident batch).
 int encode_pipelined(kgm_ctx *ctx, const kgm_batch *b, uint32_t chunks, kgm_result *out) {
   uint64_t gb = 0, ab = 0;
+  static const bool trace = getenv("KGM_TRACE_HOST") != nullptr;
+  auto now = []() { return std::chrono::steady_clock::now(); };
+  auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b2) {
+    return std::chrono::duration<double, std::micro>(b2 - a).count();
+  };
+  const auto t_begin = now();
   int rc = prepare_batch(ctx, b, &gb, &ab);
+  const auto t_prepared = now();
   if (rc) return rc;
-  if (!use_fused(ctx) || b->n_docs < chunks) { rc = upload_batch(ctx, b); return rc ? rc : 1; }
+  if (!use_fused(ctx) || b->n_docs < 4 * chunks) { rc = upload_batch(ctx, b); return rc ? rc : 1; }
   const uint32_t n = b->n_docs;
   if ((rc = ensure_workspace(ctx))) return rc;
-  CU(ctx->h_chunk.ensure(MAX_CHUNKS * (2 * sizeof(uint64_t) + CTR_COUNT * sizeof(uint32_t))));
+  constexpr size_t POST_WORDS = 8;                 // one 64-byte line per chunk
+  CU(ctx->h_chunk.ensure(MAX_CHUNKS * (POST_WORDS * sizeof(uint64_t) + CTR_COUNT * sizeof(uint32_t))));
   CU(ctx->h_lines.ensure(ctx->out_cap + 16));
   CU(ctx->h_line_off.ensure(((size_t)ctx->desc_cap + 1) * sizeof(uint64_t)));
   CU(ctx->h_doc_line_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
   CU(ctx->h_status.ensure(std::max<size_t>(n, 1) * sizeof(int32_t)));
-  uint64_t *h_tot = ctx->h_chunk.as<uint64_t>();
-  uint32_t *h_cnt = reinterpret_cast<uint32_t *>(h_tot + 2 * MAX_CHUNKS);
+  volatile uint64_t *h_post = ctx->h_chunk.as<uint64_t>();
+  uint32_t *h_cnt = reinterpret_cast<uint32_t *>(ctx->h_chunk.as<uint64_t>() + POST_WORDS * MAX_CHUNKS);
+  void *d_post_v = nullptr;
+  CU(cudaHostGetDevicePointer(&d_post_v, ctx->h_chunk.p, 0));
+  unsigned long long *d_post = static_cast<unsigned long long *>(d_post_v);
+  uint64_t *d_tot = ctx->w_totals.as<uint64_t>();
+
+  // chunk boundaries: weights 1, 2, 3, 3, ..., 3, 2, 1
+  uint32_t c0[MAX_CHUNKS + 1];
+  {
+    uint32_t wsum = 0, acc = 0;
+    for (uint32_t c = 0; c < chunks; ++c) wsum += std::min({c + 1, chunks - c, 3u});
+    c0[0] = 0;
+    for (uint32_t c = 0; c < chunks; ++c) {
+      acc += std::min({c + 1, chunks - c, 3u});
+      c0[c + 1] = (uint32_t)((uint64_t)n * acc / wsum);
+    }
+  }
 
   CU(cudaEventRecord(ctx->ev[EV_START], ctx->stream));
-  if ((rc = upload_doc_arrays(ctx, b))) return rc;
-  uint64_t *d_tot = ctx->w_totals.as<uint64_t>();
-  uint32_t c0[MAX_CHUNKS + 1];
-  for (uint32_t c = 0; c <= chunks; ++c) c0[c] = (uint32_t)((uint64_t)n * c / chunks);
-  for (uint32_t c = 0; c < chunks; ++c) {
-    const uint64_t g0 = b->gpu_off[c0[c]], g1 = b->gpu_off[c0[c + 1]];
-    const uint64_t a0 = b->apps_off[c0[c]], a1 = b->apps_off[c0[c + 1]];
-    if (g1 > g0) CU(cudaMemcpyAsync(ctx->b_gpu.as<uint8_t>() + g0, b->gpu_csv + g0, g1 - g0, cudaMemcpyHostToDevice, ctx->s_h2d));
-    if (a1 > a0) CU(cudaMemcpyAsync(ctx->b_apps.as<uint8_t>() + a0, b->apps_csv + a0, a1 - a0, cudaMemcpyHostToDevice, ctx->s_h2d));
-    CU(cudaEventRecord(ctx->ev_in[c], ctx->s_h2d));
+  CU(cudaStreamWaitEvent(ctx->s_h2d, ctx->ev[EV_START], 0));      // earlier work on the buffers is done
+  {
+    // the small per-document arrays go through one pinned staging buffer (the caller's may
+    // be pageable, and a pageable copy blocks the host), ahead of the first chunk's text
+    const size_t o_g = 0, o_a = o_g + ((size_t)n + 1) * 8, o_n = o_a + ((size_t)n + 1) * 8, o_t = o_n + (size_t)n * 4;
+    CU(ctx->h_docarr.ensure(o_t + (size_t)n * 4));
+    uint8_t *st = ctx->h_docarr.as<uint8_t>();
+    memcpy(st + o_g, b->gpu_off, ((size_t)n + 1) * 8);
+    memcpy(st + o_a, b->apps_off, ((size_t)n + 1) * 8);
+    memcpy(st + o_n, b->doc_node, (size_t)n * 4);
+    if (b->doc_tick) memcpy(st + o_t, b->doc_tick, (size_t)n * 4);
+    CU(cudaMemcpyAsync(ctx->b_gpu_off.p, st + o_g, ((size_t)n + 1) * 8, cudaMemcpyHostToDevice, ctx->s_h2d));
+    CU(cudaMemcpyAsync(ctx->b_apps_off.p, st + o_a, ((size_t)n + 1) * 8, cudaMemcpyHostToDevice, ctx->s_h2d));
+    CU(cudaMemcpyAsync(ctx->b_node.p, st + o_n, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->s_h2d));
+    if (b->doc_tick) CU(cudaMemcpyAsync(ctx->b_tick.p, st + o_t, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->s_h2d));
+  }
+  // The text goes up in few, growing pieces (chunk 0 alone, then two chunks, then the rest):
+  // while the result copy saturates the other direction every copy command is slow to
+  // start, and the text of all chunks must be in long before the last kernels need it.
+  uint32_t piece_of[MAX_CHUNKS];
+  {
+    const uint32_t piece_end[3] = {1u, std::min(3u, chunks), chunks};
+    uint32_t from = 0;
+    for (uint32_t p = 0; p < 3 && from < chunks; ++p) {
+      const uint32_t to = piece_end[p];
+      if (to <= from) continue;
+      const uint64_t g0 = b->gpu_off[c0[from]], g1 = b->gpu_off[c0[to]];
+      const uint64_t a0 = b->apps_off[c0[from]], a1 = b->apps_off[c0[to]];
+      if (g1 > g0) CU(cudaMemcpyAsync(ctx->b_gpu.as<uint8_t>() + g0, b->gpu_csv + g0, g1 - g0, cudaMemcpyHostToDevice, ctx->s_h2d));
+      if (a1 > a0) CU(cudaMemcpyAsync(ctx->b_apps.as<uint8_t>() + a0, b->apps_csv + a0, a1 - a0, cudaMemcpyHostToDevice, ctx->s_h2d));
+      CU(cudaEventRecord(ctx->ev_in[p], ctx->s_h2d));
+      for (uint32_t c = from; c < to; ++c) piece_of[c] = p;
+      from = to;
+    }
   }
   const BatchDev whole = ctx->batch;
   const WorkDev wfull = ctx->work;
+  auto restore = [&]() {
+    ctx->batch = whole; ctx->work = wfull; ctx->totals_external = false; ctx->chunk_launch = false;
+    ctx->fused.carry = nullptr; ctx->fused.post = nullptr;
+  };
+  uint64_t seq[MAX_CHUNKS];
+  const uint32_t *d_cnt[MAX_CHUNKS];
+  static_assert(CTR_RING > MAX_CHUNKS + 1, "the counter sets of all chunks must survive the call");
   for (uint32_t c = 0; c < chunks; ++c) {
     const uint32_t lo = c0[c], cn = c0[c + 1] - c0[c];
     BatchDev &bd = ctx->batch;
@@ -596,62 +681,84 @@ int encode_pipelined(kgm_ctx *ctx, const kgm_batch *b, uint32_t chunks, kgm_resu
     wd.doc_line_off += lo; wd.doc_byte_off += lo;
     wd.totals = d_tot + 2 * (c + 1);
     ctx->totals_external = true;
+    ctx->chunk_launch = true;
     ctx->fused.carry = c ? reinterpret_cast<const unsigned long long *>(d_tot + 2 * c) : nullptr;
-    CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_in[c], 0));
+    seq[c] = 1 + (ctx->post_seq++ % 65535u);
+    h_post[POST_WORDS * c] = 0; h_post[POST_WORDS * c + 1] = 0;
+    ctx->fused.post = d_post + POST_WORDS * c;
+    ctx->fused.post_seq = seq[c];
+    if (c == 0 || piece_of[c] != piece_of[c - 1]) CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_in[piece_of[c]], 0));
     if (c == 0) CU(cudaEventRecord(ctx->ev[EV_H2D], ctx->stream));
     rc = launch_pipeline(ctx);                     // cn > 0; sets wd.counters to this launch's set
-    if (rc) { ctx->batch = whole; ctx->work = wfull; ctx->fused.carry = nullptr; ctx->totals_external = false; return rc; }
-    CU(cudaMemcpyAsync(h_tot + 2 * c, wd.totals, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
-    CU(cudaMemcpyAsync(h_cnt + CTR_COUNT * c, wd.counters, CTR_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    if (rc) { restore(); return rc; }
+    d_cnt[c] = wd.counters;
     CU(cudaEventRecord(ctx->ev_k[c], ctx->stream));
   }
-  ctx->batch = whole;
-  ctx->work = wfull;
-  ctx->fused.carry = nullptr;
-  ctx->totals_external = false;
+  restore();
   CU(cudaEventRecord(ctx->ev[EV_ENC], ctx->stream));
+  const auto t_queued = now();
 
   uint64_t lines_done = 0, bytes_done = 0;
-  uint32_t slow = 0;
   bool overflow = false;
-  for (uint32_t c = 0; c < chunks; ++c) {
-    CU(cudaEventSynchronize(ctx->ev_k[c]));
-    const uint32_t *cnt = h_cnt + CTR_COUNT * c;
-    if (cnt[CTR_OVERFLOW]) {
-      overflow = true;
-      if (cnt[CTR_OVERFLOW] & OVF_GROW) ctx->grow_cap = std::max(ctx->grow_cap * 2, cnt[CTR_GROW] + 64);
-      if (cnt[CTR_OVERFLOW] & OVF_PROW) ctx->prow_cap = std::max(ctx->prow_cap * 2, cnt[CTR_PROW] + 64);
-      if (cnt[CTR_OVERFLOW] & OVF_DESC) ctx->desc_cap = std::max<uint64_t>(ctx->desc_cap * 2, cnt[CTR_DESC] + 64);
-      if (cnt[CTR_OVERFLOW] & OVF_OUT) ctx->out_cap = ctx->out_cap * 2;
-      break;
+  for (uint32_t c = 0; c < chunks && !overflow; ++c) {
+    volatile uint64_t *post = h_post + POST_WORDS * c;
+    auto posted = [&]() { return (post[0] >> 48) == seq[c] && (post[1] >> 48) == seq[c]; };
+    for (uint32_t spins = 0; !posted(); ++spins) {
+      if ((spins & 1023u) == 1023u) {              // a failed launch never posts
+        const cudaError_t q = cudaEventQuery(ctx->ev_k[c]);
+        if (q == cudaSuccess) break;
+        if (q != cudaErrorNotReady) return cuda_fail(ctx, q, "k_poll (chunked)");
+      }
+#if defined(__x86_64__) || defined(__i386__)
+      __builtin_ia32_pause();
+#endif
     }
-    slow += cnt[CTR_SLOW];
-    const uint64_t nl = h_tot[2 * c], nb = h_tot[2 * c + 1];
+    if (!posted()) { overflow = true; break; }     // finished without totals: take the plain path
+    const uint64_t nl = post[0] & 0xffffffffffffull, nb = post[1] & 0xffffffffffffull;
+    if (nb > ctx->out_cap || nl > ctx->desc_cap) { overflow = true; break; }
+    CU(cudaStreamWaitEvent(ctx->s_d2h, ctx->ev_k[c], 0));
     if (nb > bytes_done)
       CU(cudaMemcpyAsync(ctx->h_lines.as<uint8_t>() + bytes_done, ctx->work.out + bytes_done, nb - bytes_done,
                          cudaMemcpyDeviceToHost, ctx->s_d2h));
-    if (nl > lines_done)
-      CU(cudaMemcpyAsync(ctx->h_line_off.as<uint64_t>() + lines_done, ctx->work.line_off + lines_done,
-                         (nl - lines_done) * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->s_d2h));
     lines_done = nl; bytes_done = nb;
   }
+  if (!overflow) {
+    // the line offsets (8 bytes per line) go in one copy at the end: under load every copy
+    // command costs more than its bytes
+    if (lines_done)
+      CU(cudaMemcpyAsync(ctx->h_line_off.p, ctx->work.line_off, lines_done * sizeof(uint64_t), cudaMemcpyDeviceToHost,
+                         ctx->s_d2h));
+    for (uint32_t c = 0; c < chunks; ++c)
+      CU(cudaMemcpyAsync(h_cnt + CTR_COUNT * c, d_cnt[c], CTR_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->s_d2h));
+    CU(cudaMemcpyAsync(ctx->h_doc_line_off.p, ctx->work.doc_line_off, ((size_t)n + 1) * sizeof(uint64_t),
+                       cudaMemcpyDeviceToHost, ctx->s_d2h));
+    CU(cudaMemcpyAsync(ctx->h_status.p, ctx->work.doc_status, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                       ctx->s_d2h));
+    CU(cudaEventRecord(ctx->ev[EV_D2H], ctx->s_d2h));
+  }
+  const auto t_copies = now();
+  CU(cudaStreamSynchronize(ctx->s_d2h));
+  CU(cudaStreamSynchronize(ctx->s_h2d));
+  CU(cudaStreamSynchronize(ctx->stream));
+  if (trace)
+    fprintf(stderr, "kgm host us: prepare %.1f, queue %.1f, posts+copies %.1f, final sync %.1f\n",
+            us(t_begin, t_prepared), us(t_prepared, t_queued), us(t_queued, t_copies), us(t_copies, now()));
+  ctx->batch_resident = true;                      // every text byte has been copied
+  uint32_t slow = 0;
+  if (!overflow) {
+    for (uint32_t c = 0; c < chunks; ++c) {
+      const uint32_t *cnt = h_cnt + CTR_COUNT * c;
+      if (cnt[CTR_OVERFLOW]) overflow = true;
+      slow += cnt[CTR_SLOW];
+    }
+  }
   if (overflow) {
-    CU(cudaStreamSynchronize(ctx->s_h2d));
-    CU(cudaStreamSynchronize(ctx->stream));
-    CU(cudaStreamSynchronize(ctx->s_d2h));
-    ctx->batch_resident = true;                    // every text byte has been copied
+    // the plain path re-runs the batch and grows whichever guess was too small
     return 1;
   }
-  CU(cudaMemcpyAsync(ctx->h_doc_line_off.p, ctx->work.doc_line_off, ((size_t)n + 1) * sizeof(uint64_t),
-                     cudaMemcpyDeviceToHost, ctx->s_d2h));
-  CU(cudaMemcpyAsync(ctx->h_status.p, ctx->work.doc_status, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost,
-                     ctx->s_d2h));
-  CU(cudaEventRecord(ctx->ev[EV_D2H], ctx->s_d2h));
-  CU(cudaStreamSynchronize(ctx->s_d2h));
   ctx->h_line_off.as<uint64_t>()[lines_done] = bytes_done;
   ctx->n_lines = lines_done; ctx->n_bytes = bytes_done;
   ctx->slow_docs = slow;
-  ctx->batch_resident = true;
   ctx->have_result = true;
   ctx->last_chunks = chunks;
   out->lines = ctx->h_lines.as<uint8_t>();
@@ -711,8 +818,8 @@ int kgm_create(kgm_ctx **out, int device) {
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->s_h2d, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->s_d2h, cudaStreamNonBlocking);
   for (int i = 0; i < MAX_CHUNKS && e == cudaSuccess; ++i) {
-    e = cudaEventCreateWithFlags(&ctx->ev_in[i], cudaEventDisableTiming);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_k[i], cudaEventDisableTiming);
+    e = cudaEventCreate(&ctx->ev_in[i]);
+    if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev_k[i]);
   }
   cudaDeviceProp prop;
   if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
@@ -747,7 +854,7 @@ void kgm_destroy(kgm_ctx *ctx) {
                    &ctx->f_vis_hash2, &ctx->w_win_samples, &ctx->w_win_groups, &ctx->w_win_temp};
   for (DevBuf *b : dev) b->release();
   HostBuf *host[] = {&ctx->h_small, &ctx->h_lines, &ctx->h_line_off, &ctx->h_doc_line_off, &ctx->h_status,
-                     &ctx->h_chunk, &ctx->h_win_groups};
+                     &ctx->h_chunk, &ctx->h_docarr, &ctx->h_win_groups};
   for (HostBuf *b : host) b->release();
   for (int i = 0; i < EV_COUNT; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
   for (int i = 0; i < MAX_CHUNKS; ++i) {
@@ -957,6 +1064,7 @@ int kgm_load_fleet(kgm_ctx *ctx, const kgm_fleet *fl) {
   ctx->fast_max_nc = fast_max_nc; ctx->fast_max_tb = fast_max_tb; ctx->fast_max_idle = fast_max_idle;
   ctx->any_fast = any_fast;
   ctx->h_node_fast = node_fast;
+  ctx->all_nodes_fast = std::all_of(node_fast.begin(), node_fast.end(), [](uint8_t v) { return v != 0; });
   ctx->h_tb_len = tb_len;
   ctx->fused_ok = false;
   ctx->fleet_loaded = true;
@@ -998,13 +1106,19 @@ int kgm_encode_batch(kgm_ctx *ctx, const kgm_batch *b, int want_host_copy, kgm_r
       b->gpu_off && b->apps_off && b->doc_node &&
       b->gpu_off[b->n_docs] + b->apps_off[b->n_docs] >= (4u << 20)) {
     const uint64_t total = b->gpu_off[b->n_docs] + b->apps_off[b->n_docs];
-    const uint32_t chunks = (uint32_t)std::min<uint64_t>(MAX_CHUNKS, std::max<uint64_t>(2, total / (2u << 20)));
+    uint32_t chunks = (uint32_t)std::min<uint64_t>(MAX_CHUNKS, std::max<uint64_t>(2, total / (1u << 20)));
+    if (const char *env = getenv("KGM_CHUNKS")) chunks = (uint32_t)std::max(2, std::min(atoi(env), MAX_CHUNKS));
     int rc = encode_pipelined(ctx, b, chunks, out);
     if (rc <= 0) {
       if (rc == KGM_OK) {
         ctx->timing = kgm_timing{};
         cudaEventElapsedTime(&ctx->timing.total_ms, ctx->ev[EV_START], ctx->ev[EV_D2H]);   // copies and kernels overlap
-        ctx->timing.launches = chunks;
+        // the three phases overlap; these are the spans that do not: until the first
+        // chunk's text is in, from there to the last kernel, and the copy tail after it
+        cudaEventElapsedTime(&ctx->timing.h2d_ms, ctx->ev[EV_START], ctx->ev[EV_H2D]);
+        cudaEventElapsedTime(&ctx->timing.encode_ms, ctx->ev[EV_H2D], ctx->ev[EV_ENC]);
+        cudaEventElapsedTime(&ctx->timing.d2h_ms, ctx->ev[EV_ENC], ctx->ev[EV_D2H]);
+        ctx->timing.launches = ctx->last_chunks;
         ctx->timing.fused = 1;
         ctx->timing.slow_docs = ctx->slow_docs;
         ctx->timing.fused_ctas_per_sm = (uint32_t)ctx->fused_ctas_per_sm;
@@ -1151,6 +1265,17 @@ int kgm_window_reduce(kgm_ctx *ctx, uint32_t window_ticks, int want_host_copy, k
 
 int kgm_debug_stage_clocks(uint64_t *out64) {
   return out64 ? debug_stage_clocks(reinterpret_cast<unsigned long long *>(out64)) : KGM_E_INVALID;
+}
+
+int kgm_debug_chunk_times(kgm_ctx *ctx, float *text_in_ms, float *kernel_done_ms, uint32_t cap) {
+  if (!ctx || !text_in_ms || !kernel_done_ms) return KGM_E_INVALID;
+  if (ctx->last_chunks <= 1) return 1;
+  for (uint32_t c = 0; c < ctx->last_chunks && c < cap; ++c) {
+    cudaEventElapsedTime(text_in_ms + c, ctx->ev[EV_START], ctx->ev_in[c == 0 ? 0 : c < 3 ? 1 : 2]);
+    cudaEventElapsedTime(kernel_done_ms + c, ctx->ev[EV_START], ctx->ev_k[c]);
+  }
+  cudaGetLastError();
+  return (int)ctx->last_chunks;
 }
 
 int kgm_set_pipeline(kgm_ctx *ctx, int mode) {

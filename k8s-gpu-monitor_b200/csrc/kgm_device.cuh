@@ -89,6 +89,8 @@ struct FusedParams {
   unsigned long long *scan_blocks;  // 2 words per block of 32 documents
   uint32_t *next_counters;       // the counter set of the next launch (zeroed by this one)
   const unsigned long long *carry;  // {lines, bytes} emitted by earlier launches of the same batch
+  unsigned long long *post;         // mapped host memory (or null): {tag:16 | lines:48, tag:16 | bytes:48} once the totals are known
+  unsigned long long post_seq;      // the tag (1 .. 65535)
                                     // (chunked end-to-end path), or null
 };
 

@@ -167,6 +167,18 @@ struct WarpSlice {                                   // byte offsets from the CT
 };
 
 // Coalesced copy of the 16-byte aligned window that covers text[lo, hi) into shared memory.
+// The chunked end-to-end path: the host waits for the totals of a launch in mapped host
+// memory (no copy engine, no stream synchronisation) so that it can queue the copy of this
+// launch's lines while the previous copy is still running.  Each value is one 8-byte store
+// carrying the launch's 16-bit tag, so no system-scope fence is needed (such a fence would
+// wait behind the result copy that saturates the same PCIe direction).
+__device__ __forceinline__ void post_totals(const FusedParams &P, uint64_t lines, uint64_t bytes) {
+  if (!P.post) return;
+  volatile unsigned long long *q = P.post;
+  q[0] = (P.post_seq << 48) | lines;
+  q[1] = (P.post_seq << 48) | bytes;
+}
+
 __device__ __forceinline__ void load_window(const uint8_t *text, uint64_t lo, uint64_t hi, uint8_t *dst,
                                             uint32_t *s, uint32_t *e) {
   const uint64_t w0 = lo & ~15ull;
@@ -586,6 +598,7 @@ __device__ void fast_emit(const FusedParams &P, const WorkDev &w, uint32_t *S, u
             w.doc_byte_off[n_docs] = byte0 + nb;
             w.totals[0] = line0 + nl;
             w.totals[1] = byte0 + nb;
+            post_totals(P, line0 + nl, byte0 + nb);
             w.line_off[min(line0 + nl, (uint64_t)w.desc_cap)] = byte0 + nb;
           }
           if (byte0 + nb > w.out_cap || line0 + nl > w.desc_cap)
@@ -736,6 +749,7 @@ __global__ void __launch_bounds__(POLL_THREADS, 1) k_poll(BatchDev b, FleetDev f
           w.doc_byte_off[b.n_docs] = byte0 + nb;
           w.totals[0] = line0 + nl;
           w.totals[1] = byte0 + nb;
+          post_totals(P, line0 + nl, byte0 + nb);
           w.line_off[min(line0 + nl, (uint64_t)w.desc_cap)] = byte0 + nb;
         }
       }

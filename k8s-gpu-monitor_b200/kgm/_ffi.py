@@ -105,6 +105,7 @@ SIGNATURES = {
     "kgm_get_timing": (C.c_int, [C.c_void_p, C.POINTER(KgmTiming)]),
     "kgm_set_pipeline": (C.c_int, [C.c_void_p, C.c_int]),
     "kgm_debug_stage_clocks": (C.c_int, [C.c_void_p]),
+    "kgm_debug_chunk_times": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
     "kgm_concat_shards": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64,
                                     C.c_void_p, C.c_void_p]),
     "kgm_window_reduce": (C.c_int, [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]),
