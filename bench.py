@@ -276,26 +276,81 @@ def run_kgm_arm(args):
 
     host_s = {"encode_call": 0.0, "gather_call": 0.0}
 
+    # Steps are queued without waiting for their results: every context has at most one
+    # kgm_encode_resident_async in flight, finished (sizes, overflow check, kernel times)
+    # when the rotation comes back to it, so the host runs up to `rotate` steps ahead of the
+    # GPU.  With more than one rank the shard is handed to the gather on the device: the
+    # sizes travel in the 16-byte header in front of the lines.
+    use_async = gather is None or gather.mode == "slots"
+    ext = [torch.cuda.ExternalStream(m.stream_handle, device=device) for m in mons]
+    inflight = [None] * rotate                       # (timed, event after which the output buffer is free)
+    # Each context has its own stream, so the persistent kernel of the next step starts on
+    # the SMs the previous one has already left (its last wave of documents is only partly
+    # full): consecutive launches overlap at their tails, as they would in a service that
+    # streams batches.  The duration of a launch that has the GPU to itself -- what the
+    # roofline is computed from -- is therefore measured in a synchronous pass right after the
+    # timed region.  KGM_BENCH_SERIALIZE=1 instead chains the steps of the timed region one
+    # after the other.
+    serialize = os.environ.get("KGM_BENCH_SERIALIZE") == "1"
+    last_launch = [None]
+    if gather is not None and use_async:
+        for m in mons:
+            assert gather.stride <= m.output_capacity, (gather.stride, m.output_capacity)
+
+    def finish(v):
+        nonlocal done_samples
+        if inflight[v] is None:
+            return
+        timed, fin = inflight[v]
+        inflight[v] = None
+        mons[v].encode_finish()
+        if fin is not None:
+            ext[v].wait_event(fin)                   # the shard has left the output buffer
+        if timed:
+            for k, val in zip(keys, mons[v].kernel_times()):
+                acc[k].append(val)
+            done_samples += samples_step[v]
+
     def step(i, timed):
         nonlocal done_samples
-        mon = mons[i % rotate]
+        v = i % rotate
+        mon = mons[v]
         t0 = time.perf_counter()
+        if use_async:
+            finish(v)
+            if serialize and last_launch[0] is not None:
+                ext[v].wait_event(last_launch[0])    # k_poll launches of different contexts do not overlap
+            r = mon.encode_resident_async()
+            if serialize:
+                last_launch[0] = torch.cuda.Event()
+                last_launch[0].record(ext[v])
+            t1 = time.perf_counter()
+            fin = gather.start_device(int(r.lines), ext[v]) if gather is not None else None
+            inflight[v] = (timed, fin)
+            if timed:
+                host_s["encode_call"] += t1 - t0
+                host_s["gather_call"] += time.perf_counter() - t1
+            return
         r = mon.encode_resident()                    # device time per kernel from the library's CUDA events
         t1 = time.perf_counter()
-        if world > 1:                                # shards -> rank 0, overlapped with the next step
-            local = shard.tensor_of_device_buffer(r.lines, max(int(r.n_bytes), 1), device)
-            gather.start(local, int(r.n_bytes), int(r.n_lines))
+        local = shard.tensor_of_device_buffer(r.lines, max(int(r.n_bytes), 1), device)
+        gather.start(local, int(r.n_bytes), int(r.n_lines))
         if timed:
             host_s["encode_call"] += t1 - t0
             host_s["gather_call"] += time.perf_counter() - t1
-        if timed:
-            for k, v in zip(keys, mon.kernel_times()):
-                acc[k].append(v)
-            done_samples += samples_step[i % rotate]
+            for k, val in zip(keys, mon.kernel_times()):
+                acc[k].append(val)
+            done_samples += samples_step[v]
+
+    def drain():
+        for v in range(rotate):
+            finish(v)
 
     for i in range(args.warmup):
         step(i, False)
+    drain()
     concat_check = None
+    pack_ms = None
     if gather:
         gather.finish()
         # one untimed check that rank 0 really holds the rank-major concatenation
@@ -309,6 +364,15 @@ def run_kgm_arm(args):
             off = gather.shard_offsets()
             whole = gather.body().cpu().numpy().tobytes()
             concat_check = all(zlib.crc32(whole[int(off[r]):int(off[r + 1])]) == crcs[r] for r in range(world))
+            # what closing the gaps between the slots costs when it has the GPU to itself
+            pe = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+            gather.pack()
+            pe[0].record(gather.stream)
+            for _ in range(3):
+                gather.pack()
+            pe[1].record(gather.stream)
+            gather.stream.synchronize()
+            pack_ms = pe[0].elapsed_time(pe[1]) / 3
     sync_all()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     wall0 = time.perf_counter()
@@ -316,6 +380,7 @@ def run_kgm_arm(args):
         ev0.record()
         for i in range(args.steps):
             step(args.warmup + i, True)
+        drain()
         if gather:
             gather.finish()
         ev1.record()
@@ -327,6 +392,18 @@ def run_kgm_arm(args):
     region_ms = ev0.elapsed_time(ev1)
     step_ms = region_ms / args.steps
     mean = {k: sum(v) / len(v) for k, v in acc.items()}
+    if not serialize:
+        # the launches of the timed region overlap, so their own event times include waiting
+        # for SMs: the duration of a launch that has the GPU to itself is measured right after,
+        # on the same resident batches, one synchronous call at a time
+        iso = {k: [] for k in keys}
+        for i in range(max(8, min(args.steps, 40))):
+            mons[i % rotate].encode_resident()
+            if i >= 4:
+                for k, val in zip(keys, mons[i % rotate].kernel_times()):
+                    iso[k].append(val)
+        in_region = mean
+        mean = {k: sum(v) / len(v) for k, v in iso.items()}
     last_t = mons[0].timing()
     fused = bool(last_t["fused"])
     launches_per_step = int(last_t["launches"])
@@ -396,15 +473,26 @@ def run_kgm_arm(args):
                        "output_bytes_per_gpu": n_bytes,
                        "l2": "%d distinct resident batches per GPU visited round-robin (%d MB working set > 126 MB "
                              "L2), no flush inside the timed bracket" % (rotate, rotate * algo_bytes // 1000000),
-                       "parallelism": "hosts sharded over %d rank(s); per step every rank all-gathers its "
-                                      "{bytes, lines} over NCCL and the encoded shards are gathered to rank 0 "
-                                      "(%s; inside the timed bracket, overlapping the next step's kernel); "
-                                      "concatenation verified: %s" % (world, {"ipc": "peer-to-peer copies into rank 0's "
-                                      "buffer mapped through CUDA IPC", "slots": "NCCL send/recv into fixed slots, "
-                                      "packed by kgm_concat_shards from device-side sizes", "p2p": "NCCL send/recv"}
-                                      [gather.mode], concat_check) if world > 1 else "1 rank"},
+                       "parallelism": ("hosts sharded over %d ranks, no data-path collective inside the poll path; "
+                                       "per step every rank's encoded shard and its {bytes, lines} header are "
+                                       "gathered (%s; inside the timed bracket, queued on the device behind the "
+                                       "step's kernel and overlapping the next step's); rank-major concatenation "
+                                       "of the gathered slots verified against every rank's own result: %s; "
+                                       "packing the slots into one contiguous buffer (kgm_concat_shards) is done "
+                                       "on demand, not per step: %s ms when it has the GPU to itself"
+                                       % (world, {"ipc": "peer-to-peer copies into rank 0's buffer mapped through "
+                                                         "CUDA IPC",
+                                                  "slots": "one fixed-size NCCL all-gather straight out of the "
+                                                           "library's output buffers into fixed-stride slots, sizes "
+                                                           "never visit the host",
+                                                  "p2p": "NCCL send/recv"}[gather.mode], concat_check,
+                                          "%.3f" % pack_ms if pack_ms is not None else "n/a"))
+                       if world > 1 else "1 rank"},
             "timing": "CUDA events around %d back-to-back steps (barrier + synchronize on both sides), max over "
-                      "ranks; kernel_ms from the library's own events on its stream" % args.steps,
+                      "ranks; steps are queued asynchronously, every context on its own stream and finished when "
+                      "the rotation returns to it%s; kernel_ms from the library's own events on its stream%s"
+                      % (args.steps, ", launches chained one after the other" if serialize else "",
+                         "" if serialize else " in a synchronous pass after the region"),
             "kernel_ms": {k: round(mean[k], 5) for k in keys},
             "host_ms_per_step_rank0": {k: round(1e3 * v / args.steps, 4) for k, v in host_s.items()},
             "wall_ms_region": wall_ms,
@@ -415,7 +503,13 @@ def run_kgm_arm(args):
             "roofline": {"bound": "hbm", "kernel": "k_poll" if fused else "k_encode", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                          "algorithmic_bytes_per_launch": algo_bytes, "peak_source": peak_src,
-                         "frac_of_nominal_8TBs": achieved / 8000.0},
+                         "frac_of_nominal_8TBs": achieved / 8000.0,
+                         "launch_ms": enc_ms,
+                         "launch_ms_source": "library CUDA events around the kernel on its stream, " + (
+                             "timed region (launches chained)" if serialize else
+                             "synchronous pass right after the timed region (in the region consecutive launches "
+                             "overlap at their tails)"),
+                         "achieved_in_region": algo_bytes / (step_ms * 1e-3) / 1e9 if world == 1 else None},
             "e2e": {"value": samples_one_step / (e2e_ms * 1e-3), "unit": "samples/s",
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms,
                     "d2h_copy_alone_ms": d2h_only_ms,

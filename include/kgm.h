@@ -160,6 +160,26 @@ int  kgm_encode_batch(kgm_ctx *ctx, const kgm_batch *batch, int want_host_copy, 
 int  kgm_upload_batch(kgm_ctx *ctx, const kgm_batch *batch);
 int  kgm_encode_resident(kgm_ctx *ctx, kgm_result *out);
 
+/* kgm_encode_resident in two halves (no counterpart in the reference), for callers that
+ * keep several contexts busy or hand the lines to device-side consumers: _async queues the
+ * kernels on the context's stream and returns at once -- `out` holds the DEVICE pointers the
+ * result will be at, with n_bytes = n_lines = 0; kgm_encode_finish waits, re-runs the batch if
+ * a workspace guess was too small (the pointers may then differ) and fills in the sizes.
+ * In every device result the 16 bytes in front of `lines` hold {uint64 n_bytes, uint64
+ * n_lines}, written by the kernels in stream order, so a consumer queued behind the
+ * context's stream needs no host round trip for the sizes.  One async call per context at
+ * a time; any other encode/upload call on the context completes it first.                */
+int  kgm_encode_resident_async(kgm_ctx *ctx, kgm_result *out);
+int  kgm_encode_finish(kgm_ctx *ctx, kgm_result *out);
+
+/* The CUDA stream (cudaStream_t) the context queues its work on, for ordering a caller's
+ * own streams against it with events.                                                     */
+void *kgm_stream(kgm_ctx *ctx);
+
+/* Bytes that may be read at a device result's `lines` (>= n_bytes rounded up to 16): the
+ * size of the context's output buffer, for consumers that move fixed-size slots.          */
+uint64_t kgm_output_capacity(kgm_ctx *ctx);
+
 /* Copies the last result of kgm_encode_resident to pinned host memory.                  */
 int  kgm_fetch_result(kgm_ctx *ctx, kgm_result *out_host);
 

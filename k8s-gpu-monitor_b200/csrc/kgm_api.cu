@@ -58,6 +58,7 @@ struct HostBuf {
 
 enum { EV_START = 0, EV_H2D, EV_TOK, EV_JOIN, EV_SCAN, EV_ENC, EV_D2H, EV_COUNT };
 constexpr int MAX_CHUNKS = 8;
+constexpr size_t OUT_HEADER = 16;          // bytes in front of the lines: {n_bytes, n_lines} of the last run
 constexpr uint32_t CTR_RING = 16;        // counter sets: launch e uses set e % CTR_RING and zeroes the next one,
                                          // so the sets of the last CTR_RING - 1 launches can still be read
 
@@ -127,6 +128,7 @@ struct kgm_ctx {
 
   // results
   bool have_result = false;
+  bool async_pending = false;              // kgm_encode_resident_async without its kgm_encode_finish
   uint64_t n_lines = 0, n_bytes = 0;
   HostBuf h_small, h_lines, h_line_off, h_doc_line_off, h_status;
   kgm_timing timing{};
@@ -205,7 +207,7 @@ int ensure_workspace(kgm_ctx *ctx) {
   CU(ctx->w_doc_line_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
   CU(ctx->w_doc_byte_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
   CU(ctx->w_totals.ensure(2 * (MAX_CHUNKS + 1) * sizeof(uint64_t)));
-  CU(ctx->w_out.ensure((size_t)ctx->out_cap + 16));
+  CU(ctx->w_out.ensure((size_t)ctx->out_cap + 16 + OUT_HEADER));
   w.grow = ctx->w_grow.as<GpuRow>(); w.grow_cap = ctx->grow_cap;
   w.prow = ctx->w_prow.as<ProcRow>(); w.prow_cap = ctx->prow_cap;
   w.uniq = ctx->w_uniq.as<uint32_t>();
@@ -224,7 +226,7 @@ int ensure_workspace(kgm_ctx *ctx) {
   w.doc_byte_off = ctx->w_doc_byte_off.as<uint64_t>();
   w.totals = ctx->w_totals.as<uint64_t>();           // launch_pipeline points it into the counter set
   w.line_off = ctx->w_line_off.as<uint64_t>();
-  w.out = ctx->w_out.as<uint8_t>(); w.out_cap = ctx->out_cap;
+  w.out = ctx->w_out.as<uint8_t>() + OUT_HEADER; w.out_cap = ctx->out_cap;   // {bytes, lines} go in front of the lines
   return KGM_OK;
 }
 
@@ -288,34 +290,57 @@ int launch_pipeline(kgm_ctx *ctx) {
   return KGM_OK;
 }
 
-// Runs the pipeline, growing the workspace and re-running when a capacity guess was low.
-int run_resident(kgm_ctx *ctx, bool with_h2d_event) {
+// Grows the guesses an overflow word names.
+void grow_after_overflow(kgm_ctx *ctx, const uint32_t *hc) {
+  const uint32_t ovf = hc[CTR_OVERFLOW];
+  const uint64_t *ht = reinterpret_cast<const uint64_t *>(hc + CTR_TOTALS);
+  if (ovf & OVF_GROW) ctx->grow_cap = std::max(ctx->grow_cap * 2, hc[CTR_GROW] + 64);
+  if (ovf & OVF_PROW) ctx->prow_cap = std::max(ctx->prow_cap * 2, hc[CTR_PROW] + 64);
+  if (ovf & OVF_DESC) ctx->desc_cap = std::max(ctx->desc_cap * 2, hc[CTR_DESC] + 64);
+  if (ovf & OVF_OUT) ctx->out_cap = ht[1] + ht[1] / 8 + 4096;
+}
+
+// Launches the pipeline on the resident batch and queues the read-back of its counters;
+// does not wait.
+int launch_resident(kgm_ctx *ctx, bool record_start) {
   if (!ctx->fleet_loaded || !ctx->batch_resident) return KGM_E_STATE;
   CU(ctx->h_small.ensure(128));
+  int rc = ensure_workspace(ctx);
+  if (rc) return rc;
+  if (record_start) CU(cudaEventRecord(ctx->ev[EV_START], ctx->stream));
+  if (ctx->batch.n_docs == 0)                      // no kernel writes the size header of an empty batch
+    CU(cudaMemsetAsync(ctx->work.out - OUT_HEADER, 0, OUT_HEADER, ctx->stream));
+  rc = launch_pipeline(ctx);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(ctx->h_small.p, ctx->work.counters, CTR_SET * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  return KGM_OK;
+}
+
+// Waits for launch_resident's work; re-runs with a larger workspace while a capacity guess
+// was too low.
+int finish_resident(kgm_ctx *ctx) {
   for (int attempt = 0; attempt < 6; ++attempt) {
-    int rc = ensure_workspace(ctx);
-    if (rc) return rc;
-    if (!with_h2d_event || attempt) CU(cudaEventRecord(ctx->ev[EV_START], ctx->stream));
-    rc = launch_pipeline(ctx);
-    if (rc) return rc;
-    uint32_t *hc = ctx->h_small.as<uint32_t>();
-    uint64_t *ht = reinterpret_cast<uint64_t *>(hc + CTR_TOTALS);
-    CU(cudaMemcpyAsync(hc, ctx->work.counters, CTR_SET * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
-    const uint32_t ovf = hc[CTR_OVERFLOW];
+    const uint32_t *hc = ctx->h_small.as<uint32_t>();
+    const uint64_t *ht = reinterpret_cast<const uint64_t *>(hc + CTR_TOTALS);
     ctx->slow_docs = ctx->last_fused ? hc[CTR_SLOW] : 0;
-    if (!ovf) {
+    if (!hc[CTR_OVERFLOW]) {
       ctx->n_lines = ht[0];
       ctx->n_bytes = ht[1];
       ctx->have_result = true;
-          return KGM_OK;
+      return KGM_OK;
     }
-    if (ovf & OVF_GROW) ctx->grow_cap = std::max(ctx->grow_cap * 2, hc[CTR_GROW] + 64);
-    if (ovf & OVF_PROW) ctx->prow_cap = std::max(ctx->prow_cap * 2, hc[CTR_PROW] + 64);
-    if (ovf & OVF_DESC) ctx->desc_cap = std::max(ctx->desc_cap * 2, hc[CTR_DESC] + 64);
-    if (ovf & OVF_OUT) ctx->out_cap = ht[1] + ht[1] / 8 + 4096;
+    grow_after_overflow(ctx, hc);
+    int rc = launch_resident(ctx, true);
+    if (rc) return rc;
   }
   return KGM_E_LIMIT;
+}
+
+// Runs the pipeline, growing the workspace and re-running when a capacity guess was low.
+int run_resident(kgm_ctx *ctx, bool with_h2d_event) {
+  int rc = launch_resident(ctx, !with_h2d_event);
+  return rc ? rc : finish_resident(ctx);
 }
 
 void fill_timing(kgm_ctx *ctx, bool h2d, bool d2h) {
@@ -527,6 +552,7 @@ int prepare_batch(kgm_ctx *ctx, const kgm_batch *b, uint64_t *gb_out, uint64_t *
   if ((gb && !b->gpu_csv) || (ab && !b->apps_csv)) return KGM_E_INVALID;
   ctx->batch_resident = false;
   ctx->have_result = false;
+  if (ctx->async_pending) { CU(cudaStreamSynchronize(ctx->stream)); ctx->async_pending = false; }
   CU(ctx->b_gpu.ensure(std::max<uint64_t>(gb, 1)));
   CU(ctx->b_apps.ensure(std::max<uint64_t>(ab, 1)));
   CU(ctx->b_gpu_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
@@ -1083,12 +1109,41 @@ int kgm_upload_batch(kgm_ctx *ctx, const kgm_batch *b) {
 int kgm_encode_resident(kgm_ctx *ctx, kgm_result *out) {
   if (!ctx || !out) return KGM_E_INVALID;
   CU(cudaSetDevice(ctx->device));
+  ctx->async_pending = false;
   int rc = run_resident(ctx, false);
   if (rc) return rc;
   fill_timing(ctx, false, false);
   fill_result_dev(ctx, out);
   return KGM_OK;
 }
+
+int kgm_encode_resident_async(kgm_ctx *ctx, kgm_result *out) {
+  if (!ctx || !out) return KGM_E_INVALID;
+  CU(cudaSetDevice(ctx->device));
+  ctx->have_result = false;
+  int rc = launch_resident(ctx, true);
+  if (rc) return rc;
+  ctx->async_pending = true;
+  ctx->n_lines = 0; ctx->n_bytes = 0;
+  fill_result_dev(ctx, out);                        // the buffers are known, the sizes are not
+  return KGM_OK;
+}
+
+int kgm_encode_finish(kgm_ctx *ctx, kgm_result *out) {
+  if (!ctx || !out) return KGM_E_INVALID;
+  if (!ctx->async_pending) return KGM_E_STATE;
+  CU(cudaSetDevice(ctx->device));
+  ctx->async_pending = false;
+  int rc = finish_resident(ctx);
+  if (rc) return rc;
+  fill_timing(ctx, false, false);
+  fill_result_dev(ctx, out);
+  return KGM_OK;
+}
+
+void *kgm_stream(kgm_ctx *ctx) { return ctx ? static_cast<void *>(ctx->stream) : nullptr; }
+
+uint64_t kgm_output_capacity(kgm_ctx *ctx) { return ctx && ctx->work.out ? ctx->out_cap + 16 : 0; }
 
 int kgm_fetch_result(kgm_ctx *ctx, kgm_result *out) {
   if (!ctx || !out) return KGM_E_INVALID;

@@ -69,6 +69,14 @@ struct WorkDev {
   uint64_t out_cap;
 };
 
+// The 16 bytes in front of the lines hold {n_bytes, n_lines} of the run that wrote them, so
+// that device-side consumers (the shard gather) need no host round trip for the sizes.
+__device__ __forceinline__ void write_out_header(const WorkDev &w, uint64_t lines, uint64_t bytes) {
+  uint64_t *h = reinterpret_cast<uint64_t *>(w.out) - 2;
+  h[0] = bytes;
+  h[1] = lines;
+}
+
 // Launch parameters of k_poll (kgm_fused.cuh): the layout of a warp's shared-memory slice
 // (byte offsets from the slice start, all 16-byte aligned) and the scan / ticket state.
 struct FusedParams {

@@ -599,6 +599,7 @@ __device__ void fast_emit(const FusedParams &P, const WorkDev &w, uint32_t *S, u
             w.totals[0] = line0 + nl;
             w.totals[1] = byte0 + nb;
             post_totals(P, line0 + nl, byte0 + nb);
+            write_out_header(w, line0 + nl, byte0 + nb);
             w.line_off[min(line0 + nl, (uint64_t)w.desc_cap)] = byte0 + nb;
           }
           if (byte0 + nb > w.out_cap || line0 + nl > w.desc_cap)
@@ -750,6 +751,7 @@ __global__ void __launch_bounds__(POLL_THREADS, 1) k_poll(BatchDev b, FleetDev f
           w.totals[0] = line0 + nl;
           w.totals[1] = byte0 + nb;
           post_totals(P, line0 + nl, byte0 + nb);
+          write_out_header(w, line0 + nl, byte0 + nb);
           w.line_off[min(line0 + nl, (uint64_t)w.desc_cap)] = byte0 + nb;
         }
       }

@@ -602,6 +602,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan(uint32_t n_docs, WorkDev 
     w.doc_byte_off[n_docs] = carry_b;
     w.totals[0] = carry_l;
     w.totals[1] = carry_b;
+    write_out_header(w, carry_l, carry_b);
   }
 }
 

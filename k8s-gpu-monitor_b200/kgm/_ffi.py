@@ -101,6 +101,10 @@ SIGNATURES = {
     "kgm_encode_batch": (C.c_int, [C.c_void_p, C.POINTER(KgmBatch), C.c_int, C.POINTER(KgmResult)]),
     "kgm_upload_batch": (C.c_int, [C.c_void_p, C.POINTER(KgmBatch)]),
     "kgm_encode_resident": (C.c_int, [C.c_void_p, C.POINTER(KgmResult)]),
+    "kgm_encode_resident_async": (C.c_int, [C.c_void_p, C.POINTER(KgmResult)]),
+    "kgm_encode_finish": (C.c_int, [C.c_void_p, C.POINTER(KgmResult)]),
+    "kgm_stream": (C.c_void_p, [C.c_void_p]),
+    "kgm_output_capacity": (C.c_uint64, [C.c_void_p]),
     "kgm_fetch_result": (C.c_int, [C.c_void_p, C.POINTER(KgmResult)]),
     "kgm_get_timing": (C.c_int, [C.c_void_p, C.POINTER(KgmTiming)]),
     "kgm_set_pipeline": (C.c_int, [C.c_void_p, C.c_int]),

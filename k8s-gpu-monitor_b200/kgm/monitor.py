@@ -131,6 +131,7 @@ class Monitor:
         self._batch = None
         self._timing_buf = _ffi.KgmTiming()
         self._result_buf = _ffi.KgmResult()
+        self._async_buf = _ffi.KgmResult()
 
     # -- lifecycle ------------------------------------------------------------------------
     def close(self):
@@ -190,6 +191,32 @@ class Monitor:
         if rc != _ffi.KGM_OK:
             _check(rc, "kgm_encode_resident", self._ctx, self._lib)
         return res
+
+    def encode_resident_async(self) -> _ffi.KgmResult:
+        """Queues the pipeline on the resident batch and returns at once: the result holds the
+        DEVICE pointers, sizes 0; the 16 bytes in front of ``lines`` receive {n_bytes,
+        n_lines} in stream order.  ``encode_finish`` waits and returns the sized result."""
+        res = self._async_buf
+        rc = self._lib.kgm_encode_resident_async(self._ctx, C.byref(res))
+        if rc != _ffi.KGM_OK:
+            _check(rc, "kgm_encode_resident_async", self._ctx, self._lib)
+        return res
+
+    def encode_finish(self) -> _ffi.KgmResult:
+        res = self._result_buf
+        rc = self._lib.kgm_encode_finish(self._ctx, C.byref(res))
+        if rc != _ffi.KGM_OK:
+            _check(rc, "kgm_encode_finish", self._ctx, self._lib)
+        return res
+
+    @property
+    def stream_handle(self) -> int:
+        """The cudaStream_t the context queues its work on (kgm_stream)."""
+        return int(self._lib.kgm_stream(self._ctx) or 0)
+
+    @property
+    def output_capacity(self) -> int:
+        return int(self._lib.kgm_output_capacity(self._ctx))
 
     def fetch(self) -> HostResult:
         res = _ffi.KgmResult()

@@ -11,6 +11,8 @@ from __future__ import annotations
 
 import hashlib
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -150,6 +152,9 @@ class ShardGather:
             self.slots = torch.empty(self.stride * self.world, dtype=torch.uint8, device=self.device)
             self.own = [torch.empty(self.stride, dtype=torch.uint8, device=self.device) for _ in range(2)]
         self.copy_stream = torch.cuda.Stream(self.device)
+        self._views = {}                             # start_device: tensor views of the library's buffers
+        self.all_slots = None                        # start_device: every rank's slot, on every rank
+        self._packed = True                          # (the per-step path of start() packs every step)
         self.mode = "slots"
 
     def _start_slots(self, local, n_bytes, n_lines):
@@ -191,9 +196,47 @@ class ShardGather:
                 fin = torch.cuda.Event()
                 fin.record(self.stream)
                 self.pending[slot] = [_EventWork(fin)]
+                self._packed = True
             else:
                 self.pending[slot] = dist.batch_isend_irecv([dist.P2POp(dist.isend, self.xbuf[slot], 0, self.group)])
         done.synchronize()                           # the library may now reuse its output buffer
+
+    def start_device(self, lines_ptr: int, producer):
+        """Slots mode with nothing known on the host: ``lines_ptr`` is a device result of the
+        library (kgm_encode_resident_async), whose 16 bytes in front hold {n_bytes, n_lines};
+        both are written by work already queued on the CUDA stream ``producer``.  The shards
+        travel straight out of the library's buffers as ONE fixed-size NCCL all-gather into
+        fixed-stride slots, rank-major, each slot = its {n_bytes, n_lines} header + its lines
+        (on NVSwitch an all-gather costs rank 0 what a gather would: its ingress is the bound
+        either way; it is one collective call instead of world - 1 point-to-point operations,
+        no local copy and no host wait are needed, and every rank ends up holding the whole
+        result).  The slots ARE the gathered result; ``pack()`` / ``body()`` close the gaps
+        between them with kgm_concat_shards when a consumer wants one contiguous buffer --
+        not per step: behind the persistent poll kernel of the next step a packing pass over
+        every byte only finds a few free SMs and costs more than the step itself.  At least
+        ``stride`` bytes must be readable at ``lines_ptr - 16`` (kgm_output_capacity).
+        Returns a CUDA event: once it has fired the buffer may be overwritten and the slots
+        of this step are complete."""
+        if self.mode != "slots":
+            raise RuntimeError("start_device needs the slots mode (CUDA, world > 1)")
+        self.k += 1
+        src = self._views.get(lines_ptr)
+        if src is None:
+            src = self._views[lines_ptr] = tensor_of_device_buffer(lines_ptr - 16, self.stride, self.device)
+        if self.all_slots is None:
+            self.all_slots = torch.empty(self.stride * self.world, dtype=torch.uint8, device=self.device)
+            if self.rank == 0:
+                self.slots = self.all_slots
+        ready = torch.cuda.Event()
+        ready.record(producer)
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(ready)
+            dist.all_gather_into_tensor(self.all_slots, src, group=self.group)
+            fin = torch.cuda.Event()
+            fin.record(self.stream)
+        self._packed = False
+        self.pending[(self.k - 1) & 1] = [_EventWork(fin)]
+        return fin
 
     def start(self, local: torch.Tensor, n_bytes: int, n_lines: int):
         self.k += 1
@@ -261,9 +304,25 @@ class ShardGather:
         if self.world > 1:
             dist.barrier(group=self.ctl_group)       # every shard has landed on rank 0
 
+    def pack(self):
+        """Rank 0, slots mode: packs the slots of the last step rank-major without gaps into
+        ``final`` (kgm_concat_shards, sizes from the slot headers, on the gather's stream)."""
+        if self.mode != "slots" or self.rank != 0:
+            return
+        slots = self.all_slots if self.all_slots is not None else self.slots
+        rc = self._lib.kgm_concat_shards(slots.data_ptr(), self.stride, None, self.world,
+                                         self.final.data_ptr(), self.final.numel(),
+                                         self.totals_dev.data_ptr(), self.stream.cuda_stream)
+        if rc != 0:
+            raise RuntimeError("kgm_concat_shards failed: %d" % rc)
+        self._packed = True
+
     def body(self):
         """Rank 0: the concatenated bytes of the last finished step."""
         if self.mode == "slots":
+            if not self._packed:
+                self.pack()
+                self.stream.synchronize()
             return self.final[:int(self.totals_dev[0].item())]
         total = int(self.last_offsets[-1, 0])
         return self.final[:total]
