@@ -262,7 +262,8 @@ def run_kgm_arm(args):
         sizes.append((int(r.n_bytes), int(r.n_lines)))
     n_bytes, n_lines = sizes[0]
     gather = (shard.ShardGather(max(s[0] for s in sizes) + (1 << 20), device,
-                                 use_ipc=os.environ.get("KGM_SHARD_IPC") == "1") if world > 1 else None)
+                                 use_ipc=os.environ.get("KGM_SHARD_IPC") == "1",
+                                 push=os.environ.get("KGM_SHARD_PUSH", "1") == "1") if world > 1 else None)
 
     def sync_all():
         torch.cuda.synchronize(device)
@@ -281,7 +282,7 @@ def run_kgm_arm(args):
     # when the rotation comes back to it, so the host runs up to `rotate` steps ahead of the
     # GPU.  With more than one rank the shard is handed to the gather on the device: the
     # sizes travel in the 16-byte header in front of the lines.
-    use_async = gather is None or gather.mode == "slots"
+    use_async = gather is None or gather.mode in ("slots", "push")
     ext = [torch.cuda.ExternalStream(m.stream_handle, device=device) for m in mons]
     inflight = [None] * rotate                       # (timed, event after which the output buffer is free)
     # Each context has its own stream, so the persistent kernel of the next step starts on
@@ -293,7 +294,7 @@ def run_kgm_arm(args):
     # after the other.
     serialize = os.environ.get("KGM_BENCH_SERIALIZE") == "1"
     last_launch = [None]
-    if gather is not None and use_async:
+    if gather is not None and gather.mode == "slots":
         for m in mons:
             assert gather.stride <= m.output_capacity, (gather.stride, m.output_capacity)
 
@@ -320,12 +321,23 @@ def run_kgm_arm(args):
             finish(v)
             if serialize and last_launch[0] is not None:
                 ext[v].wait_event(last_launch[0])    # k_poll launches of different contexts do not overlap
+            push = gather is not None and gather.mode == "push"
+            if push:                                 # the kernels write this step's shard straight into its slot on rank 0
+                ptr, nbytes = gather.push_slot()
+                free = gather.push_wait()
+                if free is not None:
+                    ext[v].wait_event(free)
+                mon.set_output_buffer(ptr, nbytes)
             r = mon.encode_resident_async()
             if serialize:
                 last_launch[0] = torch.cuda.Event()
                 last_launch[0].record(ext[v])
             t1 = time.perf_counter()
-            fin = gather.start_device(int(r.lines), ext[v]) if gather is not None else None
+            fin = None
+            if push:
+                fin = gather.start_push(ext[v])
+            elif gather is not None:
+                fin = gather.start_device(int(r.lines), ext[v])
             inflight[v] = (timed, fin)
             if timed:
                 host_s["encode_call"] += t1 - t0
@@ -345,6 +357,9 @@ def run_kgm_arm(args):
     def drain():
         for v in range(rotate):
             finish(v)
+        if gather is not None and gather.mode == "push":
+            for m in mons:
+                m.set_output_buffer(0, 0)            # synchronous calls write the context's own buffer again
 
     for i in range(args.warmup):
         step(i, False)
@@ -485,6 +500,10 @@ def run_kgm_arm(args):
                                                   "slots": "one fixed-size NCCL all-gather straight out of the "
                                                            "library's output buffers into fixed-stride slots, sizes "
                                                            "never visit the host",
+                                                  "push": "k_poll itself writes every shard into its fixed-stride slot "
+                                                          "on rank 0 over NVLink peer memory (CUDA IPC) while it "
+                                                          "encodes; NCCL carries one 4-byte all-reduce per step as "
+                                                          "the landed / slot-free signal",
                                                   "p2p": "NCCL send/recv"}[gather.mode], concat_check,
                                           "%.3f" % pack_ms if pack_ms is not None else "n/a"))
                        if world > 1 else "1 rank"},

@@ -172,6 +172,15 @@ int  kgm_encode_resident(kgm_ctx *ctx, kgm_result *out);
 int  kgm_encode_resident_async(kgm_ctx *ctx, kgm_result *out);
 int  kgm_encode_finish(kgm_ctx *ctx, kgm_result *out);
 
+/* Where the resident encodes (kgm_encode_resident, _async) write their result (no
+ * counterpart in the reference): `dev_ptr` is any 16-byte aligned memory the context's
+ * device can write -- its own, or a peer GPU's mapped into this process (CUDA IPC, peer
+ * access), which is how the shards of a multi-GPU job land on the gathering GPU while the
+ * kernel that encodes them is still running.  The 16-byte {n_bytes, n_lines} header goes
+ * to dev_ptr, the lines to dev_ptr + 16 (kgm_result.lines).  A result that does not fit
+ * fails with KGM_E_LIMIT.  NULL switches back to the context's own buffer.                */
+int  kgm_set_output_buffer(kgm_ctx *ctx, void *dev_ptr, uint64_t bytes);
+
 /* The CUDA stream (cudaStream_t) the context queues its work on, for ordering a caller's
  * own streams against it with events.                                                     */
 void *kgm_stream(kgm_ctx *ctx);

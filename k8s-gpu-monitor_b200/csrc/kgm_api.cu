@@ -128,6 +128,8 @@ struct kgm_ctx {
 
   // results
   bool have_result = false;
+  uint8_t *ext_out = nullptr;              // kgm_set_output_buffer: the caller's buffer instead of w_out
+  uint64_t ext_out_bytes = 0;
   bool async_pending = false;              // kgm_encode_resident_async without its kgm_encode_finish
   uint64_t n_lines = 0, n_bytes = 0;
   HostBuf h_small, h_lines, h_line_off, h_doc_line_off, h_status;
@@ -207,7 +209,7 @@ int ensure_workspace(kgm_ctx *ctx) {
   CU(ctx->w_doc_line_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
   CU(ctx->w_doc_byte_off.ensure(((size_t)n + 1) * sizeof(uint64_t)));
   CU(ctx->w_totals.ensure(2 * (MAX_CHUNKS + 1) * sizeof(uint64_t)));
-  CU(ctx->w_out.ensure((size_t)ctx->out_cap + 16 + OUT_HEADER));
+  if (!ctx->ext_out) CU(ctx->w_out.ensure((size_t)ctx->out_cap + 16 + OUT_HEADER));
   w.grow = ctx->w_grow.as<GpuRow>(); w.grow_cap = ctx->grow_cap;
   w.prow = ctx->w_prow.as<ProcRow>(); w.prow_cap = ctx->prow_cap;
   w.uniq = ctx->w_uniq.as<uint32_t>();
@@ -227,6 +229,7 @@ int ensure_workspace(kgm_ctx *ctx) {
   w.totals = ctx->w_totals.as<uint64_t>();           // launch_pipeline points it into the counter set
   w.line_off = ctx->w_line_off.as<uint64_t>();
   w.out = ctx->w_out.as<uint8_t>() + OUT_HEADER; w.out_cap = ctx->out_cap;   // {bytes, lines} go in front of the lines
+  if (ctx->ext_out) { w.out = ctx->ext_out + OUT_HEADER; w.out_cap = ctx->ext_out_bytes - OUT_HEADER; }
   return KGM_OK;
 }
 
@@ -330,6 +333,7 @@ int finish_resident(kgm_ctx *ctx) {
       ctx->have_result = true;
       return KGM_OK;
     }
+    if ((hc[CTR_OVERFLOW] & OVF_OUT) && ctx->ext_out) return KGM_E_LIMIT;    // the caller's buffer is too small
     grow_after_overflow(ctx, hc);
     int rc = launch_resident(ctx, true);
     if (rc) return rc;
@@ -1141,9 +1145,30 @@ int kgm_encode_finish(kgm_ctx *ctx, kgm_result *out) {
   return KGM_OK;
 }
 
+int kgm_set_output_buffer(kgm_ctx *ctx, void *dev_ptr, uint64_t bytes) {
+  if (!ctx) return KGM_E_INVALID;
+  if (!dev_ptr) { ctx->ext_out = nullptr; ctx->ext_out_bytes = 0; return KGM_OK; }
+  if (((uintptr_t)dev_ptr & 15u) || bytes < 64) return KGM_E_INVALID;
+  CU(cudaSetDevice(ctx->device));
+  cudaPointerAttributes attr{};
+  if (cudaPointerGetAttributes(&attr, dev_ptr) != cudaSuccess) { cudaGetLastError(); return KGM_E_INVALID; }
+  if (attr.type == cudaMemoryTypeDevice && attr.device != ctx->device) {
+    // a peer GPU's memory: this context's kernels need peer access to it
+    const cudaError_t e = cudaDeviceEnablePeerAccess(attr.device, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return cuda_fail(ctx, e, "cudaDeviceEnablePeerAccess");
+    cudaGetLastError();
+  }
+  ctx->ext_out = static_cast<uint8_t *>(dev_ptr);
+  ctx->ext_out_bytes = bytes & ~15ull;
+  return KGM_OK;
+}
+
 void *kgm_stream(kgm_ctx *ctx) { return ctx ? static_cast<void *>(ctx->stream) : nullptr; }
 
-uint64_t kgm_output_capacity(kgm_ctx *ctx) { return ctx && ctx->work.out ? ctx->out_cap + 16 : 0; }
+uint64_t kgm_output_capacity(kgm_ctx *ctx) {
+  if (!ctx || !ctx->work.out) return 0;
+  return ctx->ext_out ? ctx->ext_out_bytes - OUT_HEADER : ctx->out_cap + 16;
+}
 
 int kgm_fetch_result(kgm_ctx *ctx, kgm_result *out) {
   if (!ctx || !out) return KGM_E_INVALID;

@@ -103,6 +103,7 @@ SIGNATURES = {
     "kgm_encode_resident": (C.c_int, [C.c_void_p, C.POINTER(KgmResult)]),
     "kgm_encode_resident_async": (C.c_int, [C.c_void_p, C.POINTER(KgmResult)]),
     "kgm_encode_finish": (C.c_int, [C.c_void_p, C.POINTER(KgmResult)]),
+    "kgm_set_output_buffer": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
     "kgm_stream": (C.c_void_p, [C.c_void_p]),
     "kgm_output_capacity": (C.c_uint64, [C.c_void_p]),
     "kgm_fetch_result": (C.c_int, [C.c_void_p, C.POINTER(KgmResult)]),

@@ -209,6 +209,11 @@ class Monitor:
             _check(rc, "kgm_encode_finish", self._ctx, self._lib)
         return res
 
+    def set_output_buffer(self, dev_ptr: int, nbytes: int):
+        """kgm_set_output_buffer: resident encodes write {header, lines} at ``dev_ptr`` (0: own buffer)."""
+        _check(self._lib.kgm_set_output_buffer(self._ctx, C.c_void_p(dev_ptr or None), int(nbytes)),
+               "kgm_set_output_buffer", self._ctx, self._lib)
+
     @property
     def stream_handle(self) -> int:
         """The cudaStream_t the context queues its work on (kgm_stream)."""

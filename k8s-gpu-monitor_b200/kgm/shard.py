@@ -90,7 +90,7 @@ class ShardGather:
     which needs no SM; on the test pool that path measured slower than NCCL, so it is off.
     ``start`` returns once the local copy is done; ``finish`` waits for every transfer."""
 
-    def __init__(self, cap_bytes: int, device, group=None, use_ipc=False, host_counts=False):
+    def __init__(self, cap_bytes: int, device, group=None, use_ipc=False, host_counts=False, push=False):
         self.group, self.device = group, device
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.cap = int(cap_bytes)
@@ -116,6 +116,8 @@ class ShardGather:
             self._open_ipc()
         if self.cuda and self.mode == "p2p" and self.world > 1 and not host_counts:
             self._init_slots()
+            if push:
+                self._open_push()
 
     def _open_ipc(self):
         """Rank 0 exports its buffer; the others map it (same node, NVLink peers)."""
@@ -136,6 +138,85 @@ class ShardGather:
             self.peer_final = None
         dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
         self.mode = "ipc" if int(ok.item()) == 1 else "p2p"
+
+    PUSH_SETS = 3
+
+    def _open_push(self):
+        """Push mode: rank 0 owns PUSH_SETS sets of fixed-stride slots and every rank maps
+        them (CUDA IPC, NVLink peer access); the library's kernels then write each shard and
+        its size header straight into its slot on rank 0 while they encode
+        (kgm_set_output_buffer), and the only per-step collective is a tiny all-reduce that
+        tells rank 0 the step has landed and the writers that an older set is free again."""
+        ok = torch.ones(1, dtype=torch.int32, device=self.device)
+        total = self.PUSH_SETS * self.world * self.stride
+        self.push_buf = None
+        try:
+            if self.rank == 0:
+                self.push_buf = torch.zeros(total, dtype=torch.uint8, device=self.device)
+            box = [self.push_buf.untyped_storage()._share_cuda_() if self.rank == 0 else None]
+            dist.broadcast_object_list(box, src=0, group=self.group)
+            if self.rank != 0:
+                # open the handle on THIS rank's device (not on the exporter's index): the
+                # mapping must belong to the context whose kernels will write through it
+                handle = (self.device.index,) + tuple(box[0][1:])
+                with torch.cuda.device(self.device):
+                    storage = torch.UntypedStorage._new_shared_cuda(*handle)
+                self.push_buf = torch.empty(0, dtype=torch.uint8, device=storage.device).set_(storage)
+                if self.push_buf.numel() < total:
+                    raise RuntimeError("mapped buffer is smaller than expected")
+                probe = torch.zeros(16, dtype=torch.uint8, device=self.device)
+                mine = (self.rank * self.stride)
+                self.push_buf[mine:mine + 16].copy_(probe)        # peer access works?
+                torch.cuda.synchronize(self.device)
+        except Exception:
+            ok.zero_()
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+        if int(ok.item()) != 1:
+            self.push_buf = None
+            return
+        self.flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.push_fin = {}                           # step -> event after its all-reduce
+        self.push_step = 0
+        self.mode = "push"
+
+    def push_slot(self):
+        """(device pointer, bytes) of this rank's slot for the NEXT step: hand it to
+        kgm_set_output_buffer, wait for ``push_wait()`` on the producer's stream, queue the
+        encode, then call ``start_push``."""
+        k = self.push_step
+        off = ((k % self.PUSH_SETS) * self.world + self.rank) * self.stride
+        return self.push_buf.data_ptr() + off, self.stride
+
+    def push_wait(self):
+        """The event after which the next step's slot may be written again (None: at once):
+        the all-reduce of step k-2 -- rank 0 entered it after whatever it did with the set
+        that step k reuses (PUSH_SETS = 3), and it completed long before step k starts, so
+        consecutive steps still overlap."""
+        return self.push_fin.get(self.push_step - (self.PUSH_SETS - 1))
+
+    def start_push(self, producer):
+        """After the encode of this step has been queued on ``producer``: tells every rank,
+        on the device, that this rank's shard has landed.  Returns the event after which rank
+        0 holds every shard of the step."""
+        k = self.push_step
+        self.push_step += 1
+        self.k += 1
+        ready = torch.cuda.Event()
+        ready.record(producer)
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(ready)
+            dist.all_reduce(self.flag, group=self.group)
+            fin = torch.cuda.Event()
+            fin.record(self.stream)
+        self.push_fin[k] = fin
+        self.push_fin.pop(k - 4, None)
+        self._packed = False
+        self.pending[k & 1] = [_EventWork(fin)]
+        if self.rank == 0:
+            base = (k % self.PUSH_SETS) * self.world * self.stride
+            self.slots = self.push_buf[base:base + self.world * self.stride]
+            self.all_slots = self.slots
+        return fin
 
     def _init_slots(self):
         """CUDA, default mode: fixed-stride slots on rank 0, sizes stay on the device."""
@@ -307,7 +388,7 @@ class ShardGather:
     def pack(self):
         """Rank 0, slots mode: packs the slots of the last step rank-major without gaps into
         ``final`` (kgm_concat_shards, sizes from the slot headers, on the gather's stream)."""
-        if self.mode != "slots" or self.rank != 0:
+        if self.mode not in ("slots", "push") or self.rank != 0:
             return
         slots = self.all_slots if self.all_slots is not None else self.slots
         rc = self._lib.kgm_concat_shards(slots.data_ptr(), self.stride, None, self.world,
@@ -319,7 +400,7 @@ class ShardGather:
 
     def body(self):
         """Rank 0: the concatenated bytes of the last finished step."""
-        if self.mode == "slots":
+        if self.mode in ("slots", "push"):
             if not self._packed:
                 self.pack()
                 self.stream.synchronize()
@@ -329,7 +410,7 @@ class ShardGather:
 
     def shard_offsets(self):
         """Byte offset of every rank's shard in the concatenation of the last finished step."""
-        if self.mode == "slots":
+        if self.mode in ("slots", "push"):
             c = self.slots.view(torch.int64).view(self.world, self.stride // 8)[:, 0].cpu().tolist()
             out = [0]
             for x in c:
