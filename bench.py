@@ -263,7 +263,8 @@ def run_kgm_arm(args):
     n_bytes, n_lines = sizes[0]
     gather = (shard.ShardGather(max(s[0] for s in sizes) + (1 << 20), device,
                                  use_ipc=os.environ.get("KGM_SHARD_IPC") == "1",
-                                 push=os.environ.get("KGM_SHARD_PUSH", "1") == "1") if world > 1 else None)
+                                 push=os.environ.get("KGM_SHARD_PUSH", "1") == "1",
+                                 rotate_root=os.environ.get("KGM_GATHER_ROTATE", "1") == "1") if world > 1 else None)
 
     def sync_all():
         torch.cuda.synchronize(device)
@@ -293,6 +294,7 @@ def run_kgm_arm(args):
     # timed region.  KGM_BENCH_SERIALIZE=1 instead chains the steps of the timed region one
     # after the other.
     serialize = os.environ.get("KGM_BENCH_SERIALIZE") == "1"
+    stagger_us = float(os.environ.get("KGM_STAGGER_US", "0"))
     last_launch = [None]
     if gather is not None and gather.mode == "slots":
         for m in mons:
@@ -335,7 +337,7 @@ def run_kgm_arm(args):
             t1 = time.perf_counter()
             fin = None
             if push:
-                fin = gather.start_push(ext[v])
+                gather.start_push(ext[v])            # (slot reuse is governed by push_wait, not by the context)
             elif gather is not None:
                 fin = gather.start_device(int(r.lines), ext[v])
             inflight[v] = (timed, fin)
@@ -368,14 +370,15 @@ def run_kgm_arm(args):
     pack_ms = None
     if gather:
         gather.finish()
-        # one untimed check that rank 0 really holds the rank-major concatenation
+        # one untimed check that the gathering rank really holds the rank-major concatenation
         import zlib
         last = (args.warmup - 1) % rotate
         mons[last].encode_resident()
         mine = zlib.crc32(mons[last].fetch().body)
         crcs = [None] * world
         dist.all_gather_object(crcs, mine)
-        if rank == 0:
+        holder = gather.last_root if gather.mode == "push" else 0      # the rank the last step was gathered on
+        if rank == holder:
             off = gather.shard_offsets()
             whole = gather.body().cpu().numpy().tobytes()
             concat_check = all(zlib.crc32(whole[int(off[r]):int(off[r + 1])]) == crcs[r] for r in range(world))
@@ -388,11 +391,20 @@ def run_kgm_arm(args):
             pe[1].record(gather.stream)
             gather.stream.synchronize()
             pack_ms = pe[0].elapsed_time(pe[1]) / 3
+        seen = [None] * world
+        dist.all_gather_object(seen, (concat_check, pack_ms))
+        concat_check, pack_ms = seen[holder]
     sync_all()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     wall0 = time.perf_counter()
     with ClockSampler(local_rank) as clocks:
         ev0.record()
+        if stagger_us and world > 1:
+            # rotating gather root: ranks that are a step or more apart write to different
+            # GPUs at any moment instead of all to the same one (inside the timed region)
+            t_go = time.perf_counter() + 1e-6 * stagger_us * rank
+            while time.perf_counter() < t_go:
+                pass
         for i in range(args.steps):
             step(args.warmup + i, True)
         drain()
@@ -501,9 +513,12 @@ def run_kgm_arm(args):
                                                            "library's output buffers into fixed-stride slots, sizes "
                                                            "never visit the host",
                                                   "push": "k_poll itself writes every shard into its fixed-stride slot "
-                                                          "on rank 0 over NVLink peer memory (CUDA IPC) while it "
-                                                          "encodes; NCCL carries one 4-byte all-reduce per step as "
-                                                          "the landed / slot-free signal",
+                                                          "on the step's gathering rank (%s) over NVLink peer memory "
+                                                          "(CUDA IPC) while it encodes; NCCL carries one 4-byte "
+                                                          "all-reduce per step as the landed / slot-free signal"
+                                                          % ("step k's whole concatenation lands on rank k mod N, so "
+                                                             "the ingress is spread over all NVLink ports"
+                                                             if gather.rotate_root else "always rank 0"),
                                                   "p2p": "NCCL send/recv"}[gather.mode], concat_check,
                                           "%.3f" % pack_ms if pack_ms is not None else "n/a"))
                        if world > 1 else "1 rank"},

@@ -90,8 +90,10 @@ class ShardGather:
     which needs no SM; on the test pool that path measured slower than NCCL, so it is off.
     ``start`` returns once the local copy is done; ``finish`` waits for every transfer."""
 
-    def __init__(self, cap_bytes: int, device, group=None, use_ipc=False, host_counts=False, push=False):
+    def __init__(self, cap_bytes: int, device, group=None, use_ipc=False, host_counts=False, push=False,
+                 rotate_root=False):
         self.group, self.device = group, device
+        self.rotate_root = bool(rotate_root)
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.cap = int(cap_bytes)
         if self.world > 1:                           # every rank must size its buffers alike
@@ -139,65 +141,88 @@ class ShardGather:
         dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
         self.mode = "ipc" if int(ok.item()) == 1 else "p2p"
 
-    PUSH_SETS = 3
 
     def _open_push(self):
-        """Push mode: rank 0 owns PUSH_SETS sets of fixed-stride slots and every rank maps
-        them (CUDA IPC, NVLink peer access); the library's kernels then write each shard and
-        its size header straight into its slot on rank 0 while they encode
-        (kgm_set_output_buffer), and the only per-step collective is a tiny all-reduce that
-        tells rank 0 the step has landed and the writers that an older set is free again."""
+        """Push mode: every gathering rank owns PUSH_SETS sets of fixed-stride slots and every
+        other rank maps them (CUDA IPC, NVLink peer access); the library's kernels then write
+        each shard and its size header straight into its slot on the step's gathering rank
+        while they encode (kgm_set_output_buffer), and the only per-step collective is a tiny
+        all-reduce that tells the gathering rank the step has landed and the writers that an
+        older set is free again.  With ``rotate_root`` the gathering rank of step k is k mod
+        world: every step's concatenation still lands whole on one GPU, but the ingress of
+        (world - 1) shards per step is spread over all NVLink ports instead of one."""
         ok = torch.ones(1, dtype=torch.int32, device=self.device)
+        # How far a rank may run ahead of the last step that has landed everywhere.  With a
+        # rotating root the windows differ by rank (rank r: world - r + 1 steps): every rank
+        # runs as far ahead as it may, so the ranks settle one step apart and at any moment
+        # write to `world` different gathering GPUs instead of all to the same one.
+        skew = self.rotate_root and os.environ.get("KGM_PUSH_SKEW", "1") == "1"
+        self.push_ahead = (self.world - self.rank + 1) if skew else 3
+        self.PUSH_SETS = (self.world + 2) if skew else 4
         total = self.PUSH_SETS * self.world * self.stride
-        self.push_buf = None
+        roots = range(self.world) if self.rotate_root else (0,)
+        self.push_bufs = {}
         try:
-            if self.rank == 0:
-                self.push_buf = torch.zeros(total, dtype=torch.uint8, device=self.device)
-            box = [self.push_buf.untyped_storage()._share_cuda_() if self.rank == 0 else None]
-            dist.broadcast_object_list(box, src=0, group=self.group)
-            if self.rank != 0:
+            mine = None
+            if self.rank in roots:
+                mine = torch.zeros(total, dtype=torch.uint8, device=self.device)
+                self.push_bufs[self.rank] = mine
+            boxes = [None] * self.world
+            dist.all_gather_object(boxes, mine.untyped_storage()._share_cuda_() if mine is not None else None,
+                                   group=self.group)
+            for r in roots:
+                if r == self.rank:
+                    continue
                 # open the handle on THIS rank's device (not on the exporter's index): the
                 # mapping must belong to the context whose kernels will write through it
-                handle = (self.device.index,) + tuple(box[0][1:])
+                handle = (self.device.index,) + tuple(boxes[r][1:])
                 with torch.cuda.device(self.device):
                     storage = torch.UntypedStorage._new_shared_cuda(*handle)
-                self.push_buf = torch.empty(0, dtype=torch.uint8, device=storage.device).set_(storage)
-                if self.push_buf.numel() < total:
+                buf = torch.empty(0, dtype=torch.uint8, device=storage.device).set_(storage)
+                if buf.numel() < total:
                     raise RuntimeError("mapped buffer is smaller than expected")
-                probe = torch.zeros(16, dtype=torch.uint8, device=self.device)
-                mine = (self.rank * self.stride)
-                self.push_buf[mine:mine + 16].copy_(probe)        # peer access works?
-                torch.cuda.synchronize(self.device)
+                self.push_bufs[r] = buf
         except Exception:
             ok.zero_()
         dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
         if int(ok.item()) != 1:
-            self.push_buf = None
+            self.push_bufs = {}
             return
         self.flag = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.push_fin = {}                           # step -> event after its all-reduce
         self.push_step = 0
+        self.last_root = 0
         self.mode = "push"
+
+    def push_root(self, k=None):
+        """The rank that gathers step k (default: the next step)."""
+        k = self.push_step if k is None else k
+        return k % self.world if self.rotate_root else 0
+
+    def _push_offset(self, k):
+        uses = k // self.world if self.rotate_root else k          # how often this root has gathered before
+        return (uses % self.PUSH_SETS) * self.world * self.stride
 
     def push_slot(self):
         """(device pointer, bytes) of this rank's slot for the NEXT step: hand it to
         kgm_set_output_buffer, wait for ``push_wait()`` on the producer's stream, queue the
         encode, then call ``start_push``."""
         k = self.push_step
-        off = ((k % self.PUSH_SETS) * self.world + self.rank) * self.stride
-        return self.push_buf.data_ptr() + off, self.stride
+        buf = self.push_bufs[self.push_root(k)]
+        return buf.data_ptr() + self._push_offset(k) + self.rank * self.stride, self.stride
 
     def push_wait(self):
         """The event after which the next step's slot may be written again (None: at once):
-        the all-reduce of step k-2 -- rank 0 entered it after whatever it did with the set
-        that step k reuses (PUSH_SETS = 3), and it completed long before step k starts, so
-        consecutive steps still overlap."""
-        return self.push_fin.get(self.push_step - (self.PUSH_SETS - 1))
+        the all-reduce of step k - push_ahead.  The set step k writes was last used at least
+        PUSH_SETS steps earlier; its gathering rank entered the all-reduce of the step after
+        that behind whatever it did with the set, and the awaited all-reduce completed long
+        before step k starts, so consecutive steps still overlap."""
+        return self.push_fin.get(self.push_step - self.push_ahead)
 
     def start_push(self, producer):
         """After the encode of this step has been queued on ``producer``: tells every rank,
-        on the device, that this rank's shard has landed.  Returns the event after which rank
-        0 holds every shard of the step."""
+        on the device, that this rank's shard has landed.  Returns the event after which the
+        step's gathering rank holds every shard."""
         k = self.push_step
         self.push_step += 1
         self.k += 1
@@ -209,13 +234,16 @@ class ShardGather:
             fin = torch.cuda.Event()
             fin.record(self.stream)
         self.push_fin[k] = fin
-        self.push_fin.pop(k - 4, None)
+        self.push_fin.pop(k - 2 * self.PUSH_SETS, None)
         self._packed = False
         self.pending[k & 1] = [_EventWork(fin)]
-        if self.rank == 0:
-            base = (k % self.PUSH_SETS) * self.world * self.stride
-            self.slots = self.push_buf[base:base + self.world * self.stride]
+        self.last_root = self.push_root(k)
+        if self.rank == self.last_root:
+            base = self._push_offset(k)
+            self.slots = self.push_bufs[self.rank][base:base + self.world * self.stride]
             self.all_slots = self.slots
+            if self.final is None:
+                self.final = torch.empty(self.cap * self.world, dtype=torch.uint8, device=self.device)
         return fin
 
     def _init_slots(self):
@@ -388,7 +416,7 @@ class ShardGather:
     def pack(self):
         """Rank 0, slots mode: packs the slots of the last step rank-major without gaps into
         ``final`` (kgm_concat_shards, sizes from the slot headers, on the gather's stream)."""
-        if self.mode not in ("slots", "push") or self.rank != 0:
+        if self.mode not in ("slots", "push") or self.rank != (self.last_root if self.mode == "push" else 0):
             return
         slots = self.all_slots if self.all_slots is not None else self.slots
         rc = self._lib.kgm_concat_shards(slots.data_ptr(), self.stride, None, self.world,
