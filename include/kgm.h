@@ -177,8 +177,8 @@ int  kgm_encode_finish(kgm_ctx *ctx, kgm_result *out);
  * device can write -- its own, or a peer GPU's mapped into this process (CUDA IPC, peer
  * access), which is how the shards of a multi-GPU job land on the gathering GPU while the
  * kernel that encodes them is still running.  The 16-byte {n_bytes, n_lines} header goes
- * to dev_ptr, the lines to dev_ptr + 16 (kgm_result.lines).  A result that does not fit
- * fails with KGM_E_LIMIT.  NULL switches back to the context's own buffer.                */
+ * to dev_ptr, the lines to dev_ptr + 16 (kgm_result.lines); `bytes` counts in whole
+ * 16-byte units.  A result that does not fit fails with KGM_E_LIMIT.  NULL switches back to the context's own buffer.                */
 int  kgm_set_output_buffer(kgm_ctx *ctx, void *dev_ptr, uint64_t bytes);
 
 /* The CUDA stream (cudaStream_t) the context queues its work on, for ordering a caller's

@@ -62,3 +62,39 @@ def test_finish_without_async_is_a_state_error():
         res = _ffi.KgmResult()
         assert mon._lib.kgm_encode_finish(mon._ctx, C.byref(res)) == _ffi.E_STATE
         assert mon._lib.kgm_encode_resident_async(mon._ctx, C.byref(res)) == _ffi.E_STATE   # nothing loaded
+
+
+def test_output_into_a_callers_buffer():
+    """kgm_set_output_buffer: header at the pointer, lines 16 bytes in; too small a buffer is
+    KGM_E_LIMIT, never a write past its end; NULL goes back to the context's own buffer."""
+    rp = replay.make_replay(seed=12, nodes=12, ticks=5, gpus=8, containers=10, procs_per_container=4)
+    dev = torch.device("cuda", 0)
+    with monitor.Monitor(0) as mon:
+        mon.load_fleet([entry_of_snap(s) for s in rp.nodes])
+        mon.upload(mon.make_batch(rp.gpu_texts, rp.apps_texts, rp.doc_node, rp.doc_tick))
+        own = mon.encode_resident()
+        want = mon.fetch()
+        own_ptr = int(own.lines)
+        guard = 4096
+        ext = torch.full((want.n_bytes + 16 + guard,), 0xEE, dtype=torch.uint8, device=dev)
+        mon.set_output_buffer(ext.data_ptr(), want.n_bytes + 32)          # just enough (whole 16-byte units count)
+        for _ in range(2):
+            mon.encode_resident_async()
+            r = mon.encode_finish()
+            assert int(r.lines) == ext.data_ptr() + 16 and int(r.n_bytes) == want.n_bytes
+            host = ext.cpu().numpy()
+            assert host[:16].view(np.int64).tolist() == [want.n_bytes, want.n_lines]
+            assert host[16:16 + want.n_bytes].tobytes() == want.body
+            assert (host[32 + want.n_bytes:] == 0xEE).all()               # nothing past the end
+            assert mon.fetch().body == want.body
+        assert want.n_bytes <= mon.output_capacity < want.n_bytes + 32
+        small = torch.full((want.n_bytes // 2 + guard,), 0xEE, dtype=torch.uint8, device=dev)
+        mon.set_output_buffer(small.data_ptr(), want.n_bytes // 2)
+        res = _ffi.KgmResult()
+        assert mon._lib.kgm_encode_resident(mon._ctx, C.byref(res)) == _ffi.E_LIMIT
+        torch.cuda.synchronize()
+        assert (small.cpu().numpy()[(want.n_bytes // 2) // 16 * 16:] == 0xEE).all()
+        assert mon._lib.kgm_set_output_buffer(mon._ctx, C.c_void_p(ext.data_ptr() + 4), 1 << 20) == _ffi.E_INVALID
+        mon.set_output_buffer(0, 0)
+        r = mon.encode_resident()
+        assert int(r.lines) == own_ptr and mon.fetch().body == want.body
