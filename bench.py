@@ -236,9 +236,10 @@ def run_kgm_arm(args):
     json_fd = os.dup(1)
     os.dup2(2, 1)
     if world > 1:
-        # leave a few CTA slots of every GPU to the NCCL kernels that move the shards, so that
-        # they run beside the persistent poll kernel of the next step instead of after it
-        os.environ.setdefault("KGM_RESERVE_CTAS", "16")
+        # leave a few CTA slots of every GPU to the NCCL kernel that signals a landed step
+        # (push gather: a 4-byte all-reduce), so that it runs beside the persistent poll
+        # kernel of the next step instead of after it
+        os.environ.setdefault("KGM_RESERVE_CTAS", "6")
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -262,7 +263,6 @@ def run_kgm_arm(args):
         sizes.append((int(r.n_bytes), int(r.n_lines)))
     n_bytes, n_lines = sizes[0]
     gather = (shard.ShardGather(max(s[0] for s in sizes) + (1 << 20), device,
-                                 use_ipc=os.environ.get("KGM_SHARD_IPC") == "1",
                                  push=os.environ.get("KGM_SHARD_PUSH", "1") == "1",
                                  rotate_root=os.environ.get("KGM_GATHER_ROTATE", "1") == "1") if world > 1 else None)
 
@@ -507,9 +507,7 @@ def run_kgm_arm(args):
                                        "of the gathered slots verified against every rank's own result: %s; "
                                        "packing the slots into one contiguous buffer (kgm_concat_shards) is done "
                                        "on demand, not per step: %s ms when it has the GPU to itself"
-                                       % (world, {"ipc": "peer-to-peer copies into rank 0's buffer mapped through "
-                                                         "CUDA IPC",
-                                                  "slots": "one fixed-size NCCL all-gather straight out of the "
+                                       % (world, {"slots": "one fixed-size NCCL all-gather straight out of the "
                                                            "library's output buffers into fixed-stride slots, sizes "
                                                            "never visit the host",
                                                   "push": "k_poll itself writes every shard into its fixed-stride slot "

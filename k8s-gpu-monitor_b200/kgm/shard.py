@@ -76,21 +76,28 @@ def concat_encoded(local: torch.Tensor, counts: torch.Tensor, out: torch.Tensor 
 
 
 class ShardGather:
-    """Concatenation of every rank's encoded buffer on rank 0, rank-major, without padding.
+    """Brings every step's encoded shards together on one GPU, rank-major.
 
-    Per step: the ranks all-gather their {bytes, lines} (a communicator of its own, so the
-    16 bytes never queue behind bulk traffic); every rank copies its bytes into one of two
-    exchange buffers (the library may then overwrite its output with the next batch) and
-    sends them to rank 0.  On CUDA the sizes never visit the host: they are all-gathered on
-    the device, the shards travel as fixed-size NCCL transfers into fixed-stride slots, and
-    the library's kgm_concat_shards kernel packs the slots from the device-side sizes.  In the
-    gloo CPU tests (and with ``host_counts=True``) every shard goes straight to its final
-    offset as a send/recv sized on the host.  ``use_ipc=True`` (experimental) instead maps rank 0's buffer into every
-    process through a CUDA IPC handle and writes the shard with a peer ``cudaMemcpyAsync``,
-    which needs no SM; on the test pool that path measured slower than NCCL, so it is off.
-    ``start`` returns once the local copy is done; ``finish`` waits for every transfer."""
+    Three ways, chosen at construction:
 
-    def __init__(self, cap_bytes: int, device, group=None, use_ipc=False, host_counts=False, push=False,
+    ``push`` (CUDA, ``push=True``, needs CUDA IPC between the ranks): the gathering GPU owns
+    fixed-stride slots that every rank maps; the library's kernels write each shard and its
+    {n_bytes, n_lines} header straight into its slot while they encode
+    (``push_slot`` / ``push_wait`` / ``start_push``), NCCL carries a 4-byte all-reduce per
+    step.  With ``rotate_root`` step k is gathered on rank k mod world.
+
+    ``slots`` (CUDA otherwise): the shards travel as fixed-size NCCL transfers into the
+    fixed-stride slots -- ``start_device``: one all-gather straight out of the library's
+    buffers, sizes in the headers, nothing known on the host; ``start``: the older per-step
+    path with a local copy, a host wait and the packing kernel every step.
+
+    ``p2p`` (gloo CPU tests, ``host_counts=True``): all-gather of {bytes, lines}, then every
+    shard goes to its final offset on rank 0 as a send/recv sized on the host.
+
+    In the slot modes the slots are the gathered result; ``pack()`` / ``body()`` close the
+    gaps with the library's kgm_concat_shards kernel.  ``finish`` waits for every transfer."""
+
+    def __init__(self, cap_bytes: int, device, group=None, host_counts=False, push=False,
                  rotate_root=False):
         self.group, self.device = group, device
         self.rotate_root = bool(rotate_root)
@@ -112,35 +119,11 @@ class ShardGather:
         self.cuda = device.type == "cuda"
         self.stream = torch.cuda.Stream(device) if self.cuda else None
         self.copied = [torch.cuda.Event(), torch.cuda.Event()] if self.cuda else None
-        self.peer_final = None
         self.mode = "p2p"
-        if self.cuda and use_ipc and self.world > 1:
-            self._open_ipc()
         if self.cuda and self.mode == "p2p" and self.world > 1 and not host_counts:
             self._init_slots()
             if push:
                 self._open_push()
-
-    def _open_ipc(self):
-        """Rank 0 exports its buffer; the others map it (same node, NVLink peers)."""
-        ok = torch.ones(1, dtype=torch.int32, device=self.device)
-        try:
-            box = [self.final.untyped_storage()._share_cuda_() if self.rank == 0 else None]
-            dist.broadcast_object_list(box, src=0, group=self.group)
-            if self.rank != 0:
-                storage = torch.UntypedStorage._new_shared_cuda(*box[0])
-                self.peer_final = torch.empty(0, dtype=torch.uint8, device=storage.device).set_(storage)
-                if self.peer_final.numel() < self.cap * self.world:
-                    raise RuntimeError("mapped buffer is smaller than expected")
-                probe = torch.zeros(16, dtype=torch.uint8, device=self.device)
-                self.peer_final[:16].copy_(probe)                 # peer access works?
-                torch.cuda.synchronize(self.device)
-        except Exception:
-            ok.zero_()
-            self.peer_final = None
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
-        self.mode = "ipc" if int(ok.item()) == 1 else "p2p"
-
 
     def _open_push(self):
         """Push mode: every gathering rank owns PUSH_SETS sets of fixed-stride slots and every
@@ -365,17 +348,12 @@ class ShardGather:
         if self.cuda:
             ev = self.copied[slot]
             with torch.cuda.stream(self.stream):
-                if self.mode == "ipc" and self.rank != 0:
-                    ev.synchronize()                 # the peer write of step k-2 has left xb
                 if self.rank == 0:
                     self.final[mine:mine + n_bytes].copy_(local[:n_bytes], non_blocking=True)
                 else:
                     xb[:n_bytes].copy_(local[:n_bytes], non_blocking=True)
                 done = torch.cuda.Event()
                 done.record(self.stream)
-                if self.mode == "ipc" and self.rank != 0 and n_bytes:
-                    self.peer_final[mine:mine + n_bytes].copy_(xb[:n_bytes], non_blocking=True)
-                    ev.record(self.stream)
             if self.mode == "p2p":
                 ops = []
                 if self.rank == 0:
