@@ -8,17 +8,21 @@ all of it inside the one fused kernel k_poll, `--pipeline staged` runs the four 
 kernels) over one batch of synthetic replayed nvidia-smi text.  At N=1 the workload is BASELINE.json
 `configs[1]`: 64 nodes x 8 GPUs x 60 ticks = 3840 documents, 30720 samples, 2048 pods.
 At N>1 (torchrun, one rank per GPU) every rank holds its own 64-node shards ("weak"
-scaling; hosts are the partition unit) and the step additionally all-gathers
-the per-rank byte/line counts and gathers the encoded shards to rank 0 over NCCL.
+scaling; hosts are the partition unit) and the step additionally gathers the
+encoded shards and their sizes on one GPU: k_poll writes them straight into slots on the
+step's gathering rank over NVLink peer memory, NCCL carries a 4-byte all-reduce per step
+(fallback without CUDA IPC: one NCCL all-gather of fixed-size slots).
 
 Printed JSON (one line, rank 0):
   value   whole-job samples/s with the batches already resident in HBM: CUDA events around
-          K back-to-back steps (barrier + synchronize on both sides), max over ranks; every
-          rank rotates over 4 distinct resident batches (240 MB > L2) instead of flushing
+          K steps (barrier + synchronize on both sides, every step finished inside), max
+          over ranks; every rank rotates over 4 distinct resident batches (240 MB > L2)
+          instead of flushing, each in its own context, queued asynchronously
   e2e     the same through kgm_encode_batch with pinned HOST buffers: H2D of the texts and
           D2H of lines/offsets/statuses inside the timed region (wall clock around the call)
   roofline  the dominant kernel (k_poll: the whole fused pass; k_encode when staged):
-          algorithmic bytes per launch / its CUDA-event time
+          algorithmic bytes per launch / its CUDA-event time with the GPU to itself
+          (roofline.launch_ms_source says where that time was taken)
   cpu_baseline  the oracle port of gpu.py timed on this box's host cores (N=1, rank 0)
 
 `--impl reference` times the reference's CPU implementation of the path (the oracle port of
