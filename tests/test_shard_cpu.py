@@ -116,3 +116,37 @@ def test_shards_cover_every_document_once():
     bodies, lines, owner, names, _ = _shard_bodies(2)
     assert len(owner) == len(names) and set(owner) == {0, 1}
     assert sum(lines) > 0 and all(len(b) > 0 for b in bodies)
+
+
+def test_push_mode_slot_arithmetic():
+    """Push gather (CUDA only at run time): which slot a rank writes at step k, on which
+    gathering rank, and that a slot set is never reused inside any rank's run-ahead window."""
+    from kgm.shard import ShardGather
+    for world in (2, 3, 4, 8):
+        for rotate in (False, True):
+            stride = 4096
+            sets = (world + 2) if rotate else 4
+            ahead = [(world - r + 1) if rotate else 3 for r in range(world)]
+            gs = []
+            for r in range(world):
+                g = ShardGather.__new__(ShardGather)
+                g.world, g.rank, g.stride, g.rotate_root, g.PUSH_SETS = world, r, stride, rotate, sets
+                gs.append(g)
+            last_use = {}                                # (root, set offset) -> step
+            for k in range(6 * world * sets):
+                roots = {g.push_root(k) for g in gs}
+                assert len(roots) == 1                   # every rank agrees on the gathering rank
+                root = roots.pop()
+                assert root == (k % world if rotate else 0)
+                off = {g._push_offset(k) for g in gs}
+                assert len(off) == 1                     # ... and on the slot set
+                base = off.pop()
+                assert base % (world * stride) == 0 and base + world * stride <= sets * world * stride
+                spans = sorted((base + g.rank * stride, base + (g.rank + 1) * stride) for g in gs)
+                assert all(a[1] <= b[0] for a, b in zip(spans, spans[1:]))     # the ranks' slots are disjoint
+                if (root, base) in last_use:
+                    # the gathering rank is done with the set once the all-reduce of the step
+                    # after its last use has completed; a writer of step k has waited for the
+                    # all-reduce of step k - ahead
+                    assert k - max(ahead) >= last_use[(root, base)] + 1
+                last_use[(root, base)] = k
