@@ -367,7 +367,8 @@ def run_kgm_arm(args):
             for m in mons:
                 m.set_output_buffer(0, 0)            # synchronous calls write the context's own buffer again
 
-    for i in range(args.warmup):
+    n_warm = max(args.warmup, rotate)                # every context runs at least once before the timed region
+    for i in range(n_warm):
         step(i, False)
     drain()
     concat_check = None
@@ -376,7 +377,7 @@ def run_kgm_arm(args):
         gather.finish()
         # one untimed check that the gathering rank really holds the rank-major concatenation
         import zlib
-        last = (args.warmup - 1) % rotate
+        last = (n_warm - 1) % rotate
         mons[last].encode_resident()
         mine = zlib.crc32(mons[last].fetch().body)
         crcs = [None] * world
@@ -410,7 +411,7 @@ def run_kgm_arm(args):
             while time.perf_counter() < t_go:
                 pass
         for i in range(args.steps):
-            step(args.warmup + i, True)
+            step(n_warm + i, True)
         drain()
         if gather:
             gather.finish()
@@ -442,13 +443,14 @@ def run_kgm_arm(args):
 
     # ---- end to end through the C ABI with host buffers ----
     e2e_times = []
-    for i in range(args.warmup + args.steps):
+    e2e_warm = max(args.warmup, rotate)              # every context's first call allocates its pinned result buffers
+    for i in range(e2e_warm + args.steps):
         if world > 1:
             dist.barrier()
         t0 = time.perf_counter()
         mons[i % rotate].encode_raw(batches[i % rotate], want_host_copy=True)
         dt = time.perf_counter() - t0
-        if i >= args.warmup:
+        if i >= e2e_warm:
             e2e_times.append(dt)
     e2e_ms = 1e3 * sum(e2e_times) / len(e2e_times)
     b0 = batches[0]

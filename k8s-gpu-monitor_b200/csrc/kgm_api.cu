@@ -130,6 +130,7 @@ struct kgm_ctx {
   bool have_result = false;
   uint8_t *ext_out = nullptr;              // kgm_set_output_buffer: the caller's buffer instead of w_out
   uint64_t ext_out_bytes = 0;
+  uint64_t peers_enabled = 0;              // devices cudaDeviceEnablePeerAccess has been called for
   bool async_pending = false;              // kgm_encode_resident_async without its kgm_encode_finish
   uint64_t n_lines = 0, n_bytes = 0;
   HostBuf h_small, h_lines, h_line_off, h_doc_line_off, h_status;
@@ -1152,11 +1153,13 @@ int kgm_set_output_buffer(kgm_ctx *ctx, void *dev_ptr, uint64_t bytes) {
   CU(cudaSetDevice(ctx->device));
   cudaPointerAttributes attr{};
   if (cudaPointerGetAttributes(&attr, dev_ptr) != cudaSuccess) { cudaGetLastError(); return KGM_E_INVALID; }
-  if (attr.type == cudaMemoryTypeDevice && attr.device != ctx->device) {
+  if (attr.type == cudaMemoryTypeDevice && attr.device != ctx->device && attr.device >= 0 && attr.device < 64 &&
+      !((ctx->peers_enabled >> attr.device) & 1ull)) {
     // a peer GPU's memory: this context's kernels need peer access to it
     const cudaError_t e = cudaDeviceEnablePeerAccess(attr.device, 0);
     if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return cuda_fail(ctx, e, "cudaDeviceEnablePeerAccess");
     cudaGetLastError();
+    ctx->peers_enabled |= 1ull << attr.device;
   }
   ctx->ext_out = static_cast<uint8_t *>(dev_ptr);
   ctx->ext_out_bytes = bytes & ~15ull;
