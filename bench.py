@@ -298,7 +298,6 @@ def run_kgm_arm(args):
     # timed region.  KGM_BENCH_SERIALIZE=1 instead chains the steps of the timed region one
     # after the other.
     serialize = os.environ.get("KGM_BENCH_SERIALIZE") == "1"
-    stagger_us = float(os.environ.get("KGM_STAGGER_US", "0"))
     last_launch = [None]
     if gather is not None and gather.mode == "slots":
         for m in mons:
@@ -404,12 +403,6 @@ def run_kgm_arm(args):
     wall0 = time.perf_counter()
     with ClockSampler(local_rank) as clocks:
         ev0.record()
-        if stagger_us and world > 1:
-            # rotating gather root: ranks that are a step or more apart write to different
-            # GPUs at any moment instead of all to the same one (inside the timed region)
-            t_go = time.perf_counter() + 1e-6 * stagger_us * rank
-            while time.perf_counter() < t_go:
-                pass
         for i in range(args.steps):
             step(n_warm + i, True)
         drain()
