@@ -531,6 +531,7 @@ def run_kgm_arm(args):
             "pipeline": "fused (k_poll)" if fused else "staged (k_tokenize, k_join, k_scan, k_encode)",
             "slow_docs_per_step": slow_docs,
             "fused_ctas_per_sm": int(last_t.get("fused_ctas_per_sm", 0)),
+            "docs_in_flight_per_sm": int(last_t.get("docs_in_flight_per_sm", 0)),
             "roofline": {"bound": "hbm", "kernel": "k_poll" if fused else "k_encode", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                          "algorithmic_bytes_per_launch": algo_bytes, "peak_source": peak_src,

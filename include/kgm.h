@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define KGM_ABI_VERSION 2
+#define KGM_ABI_VERSION 3
 
 /* ---- call status ---------------------------------------------------------------- */
 #define KGM_OK          0
@@ -133,6 +133,7 @@ typedef struct kgm_timing {
                           reported as encode_ms and tokenize/join/scan are 0                  */
   uint32_t slow_docs;  /* fused kernel: documents that took the generic per-byte path inside it */
   uint32_t fused_ctas_per_sm;  /* fused kernel: resident CTAs per SM its shared-memory slices allowed */
+  uint32_t docs_in_flight_per_sm;  /* fused kernel: documents its CTAs of one SM work on at a time     */
 } kgm_timing;
 
 int  kgm_abi_version(void);
@@ -250,6 +251,7 @@ int  kgm_debug_chunk_times(kgm_ctx *ctx, float *text_in_ms, float *kernel_done_m
 #define KGM_PIPELINE_AUTO          0
 #define KGM_PIPELINE_STAGED        1
 #define KGM_PIPELINE_FUSED_GENERIC 2
+#define KGM_PIPELINE_FUSED_V1      3   /* the round-1 fused kernel (two-warp teams), kept for comparison */
 int  kgm_set_pipeline(kgm_ctx *ctx, int mode);
 
 /* Writes `bytes` of device scratch on the context's stream so that the L2 holds none of

@@ -109,6 +109,7 @@ struct kgm_ctx {
   std::vector<uint32_t> h_tb_len;
   uint32_t slow_docs = 0;
   bool last_fused = false;
+  bool last_poll2 = false;
   bool totals_external = false;            // chunked path: every chunk has its own totals slot
   bool chunk_launch = false;               // chunked path: no timing events around the single launches
   // chunked end-to-end path: copies and kernels of consecutive chunks overlap
@@ -118,6 +119,15 @@ struct kgm_ctx {
   HostBuf h_docarr;                        // staging of the per-document arrays
   uint64_t post_seq = 0;
   uint32_t last_chunks = 1;
+  // k_poll2 (one warp per document)
+  bool poll2_ok = false;                   // the current batch fits k_poll2's slices
+  Poll2Params poll2{};
+  DevBuf f_node_fast2, f_nslot_off, f_tslot_off, f_slot_pool;
+  uint32_t p2_max_nc = 1, p2_max_slot = 64, p2_max_fixed = 0, p2_max_idle = 0, p2_any = 0;
+  std::vector<uint8_t> h_node_fast2;
+  bool all_nodes_fast2 = false;
+  uint32_t force_jobs = 0;                 // KGM_POLL2_JOBS=4|8: jobs per line (experiments)
+  uint32_t force_warps = 0;                // KGM_POLL2_WARPS: documents in flight per SM (experiments)
   uint32_t force_teams = 0;                // KGM_FUSED_TEAMS=4..8: documents in flight per SM (experiments)
   int reserve_ctas = 0;                    // KGM_RESERVE_CTAS: CTA slots k_poll leaves free (for NCCL kernels)
   // window reductions
@@ -235,8 +245,11 @@ int ensure_workspace(kgm_ctx *ctx) {
 }
 
 // The batch goes through the fused kernel unless it was switched off or does not fit.
+bool use_poll2(const kgm_ctx *ctx) {
+  return ctx->pipeline != KGM_PIPELINE_STAGED && ctx->pipeline != KGM_PIPELINE_FUSED_V1 && ctx->poll2_ok;
+}
 bool use_fused(const kgm_ctx *ctx) {
-  return ctx->pipeline != KGM_PIPELINE_STAGED && ctx->fused_ok;
+  return use_poll2(ctx) || (ctx->pipeline != KGM_PIPELINE_STAGED && ctx->fused_ok);
 }
 
 // Launches the pipeline on the context's stream: the fused kernel (one launch), or the four
@@ -255,21 +268,24 @@ int launch_pipeline(kgm_ctx *ctx) {
     const uint32_t cur = ctx->epoch % CTR_RING;
     ctx->work.counters = cbase + cur * CTR_SET;
     if (!ctx->totals_external) ctx->work.totals = reinterpret_cast<uint64_t *>(ctx->work.counters + CTR_TOTALS);
+    const bool v2 = use_poll2(ctx);
     FusedParams P = ctx->fused;
     P.epoch = ctx->epoch;
-    P.allow_fast = ctx->pipeline == KGM_PIPELINE_FUSED_GENERIC ? 0u : ctx->any_fast;
+    P.allow_fast = ctx->pipeline == KGM_PIPELINE_FUSED_GENERIC ? 0u : (v2 ? ctx->p2_any : ctx->any_fast);
     P.ticket = ctx->w_ticket.as<unsigned long long>();
     P.ticket_base = ctx->ticket_next;
     P.scan_state = ctx->w_scan.as<unsigned long long>();
     P.scan_blocks = P.scan_state + 2ull * ctx->scan_docs_cap;
     P.next_counters = cbase + ((cur + 1u) % CTR_RING) * CTR_SET;
     const uint32_t n = ctx->batch.n_docs;
-    const int wpb = (int)P.teams;                   // teams (documents in flight) per CTA
+    const int wpb = v2 ? (int)ctx->poll2.warps : (int)P.teams;   // documents in flight per CTA
     int blocks = (int)((n + wpb - 1) / wpb);
-    blocks = std::max(1, std::min(blocks, ctx->sms * ctx->fused_ctas_per_sm - ctx->reserve_ctas));
+    blocks = std::max(1, std::min(blocks, ctx->sms * (v2 ? 1 : ctx->fused_ctas_per_sm) - ctx->reserve_ctas));
     ctx->ticket_next += (unsigned long long)n + (unsigned long long)blocks * wpb;
     if (!ctx->chunk_launch) CU(cudaEventRecord(ctx->ev[EV_SCAN], ctx->stream));
-    launch_poll(ctx->batch, ctx->fleet, ctx->work, P, blocks, ctx->stream);
+    if (v2) launch_poll2(ctx->batch, ctx->fleet, ctx->work, P, ctx->poll2, blocks, ctx->device, ctx->stream);
+    else launch_poll(ctx->batch, ctx->fleet, ctx->work, P, blocks, ctx->stream);
+    ctx->last_poll2 = v2;
     if (!ctx->chunk_launch) CU(cudaEventRecord(ctx->ev[EV_ENC], ctx->stream));
     CU(cudaGetLastError());
     ctx->counters_clean = true;                     // k_poll zeroed the other set
@@ -365,7 +381,8 @@ void fill_timing(kgm_ctx *ctx, bool h2d, bool d2h) {
   t.launches = ctx->last_fused ? 1 : 4;
   t.fused = ctx->last_fused ? 1 : 0;
   t.slow_docs = ctx->slow_docs;
-  t.fused_ctas_per_sm = ctx->last_fused ? (uint32_t)ctx->fused_ctas_per_sm : 0u;
+  t.fused_ctas_per_sm = ctx->last_fused ? (ctx->last_poll2 ? 1u : (uint32_t)ctx->fused_ctas_per_sm) : 0u;
+  t.docs_in_flight_per_sm = ctx->last_fused ? (ctx->last_poll2 ? ctx->poll2.warps : ctx->fused.teams * ctx->fused_ctas_per_sm) : 0u;
   cudaGetLastError();
 }
 
@@ -531,6 +548,84 @@ void plan_fused(kgm_ctx *ctx, const kgm_batch *b, uint64_t max_g, uint64_t max_a
   ctx->fused_ok = true;
 }
 
+// Lays out a warp's shared-memory slice of k_poll2 for this batch.  Persistent part: the two text
+// windows, the row records, the per-container and per-line tables; behind them the template
+// slots and the stage of a round, which double as the parse-time tables (row starts, join
+// words) and as the generic path's scratch.  Text windows are clamped so that at least a few
+// documents stay in flight per SM; a document that does not fit takes the generic path.
+bool poll2_layout(kgm_ctx *ctx, uint32_t jshift, uint64_t max_g, uint64_t max_a, Poll2Params *out) {
+  auto r16 = [](uint64_t v) { return (uint32_t)((v + 15) & ~15ull); };
+  const uint32_t ca = (p2::CA2::BYTES + 15u) & ~15u;
+  const uint32_t dyn_max = 232448u - ca;
+  uint64_t g = std::min<uint64_t>(max_g, 6144), a = std::min<uint64_t>(max_a, 36864);
+  Poll2Params Q{};
+  for (int round = 0; round < 8; ++round) {
+    Q = Poll2Params{};
+    Q.jshift = jshift;
+    const uint32_t R = 32u >> jshift;
+    Q.cap_g = r16(g + 30) + 48;
+    Q.cap_a = r16(a + 30) + 48;
+    // rows of the two texts are rarely shorter than 80 / 72 bytes (uuid 40 + five cells; pid, name,
+    // uuid 40, memory); a document with more rows than that takes the generic path
+    Q.cap_ng = (uint32_t)std::min<uint64_t>(32, std::max<uint64_t>(8, g / 80 + 2));
+    Q.cap_np = (uint32_t)std::min<uint64_t>(4096, std::max<uint64_t>(8, a / 72 + 2));
+    const uint32_t cap_idle = std::min(ctx->p2_max_idle, 1024u);
+    Q.cap_rec = Q.cap_np + cap_idle;
+    Q.cap_c = std::min(512u, std::max(1u, ctx->p2_max_nc));
+    Q.cap_lines = Q.cap_ng + Q.cap_np + cap_idle;
+    Q.slot_bytes = r16(std::max(ctx->p2_max_slot, 64u));
+    Q.slot_magic = (uint32_t)(((1ull << 32) + (Q.slot_bytes >> 4) - 1) / (Q.slot_bytes >> 4));
+    const uint32_t est_line = ctx->p2_max_fixed + 80u;         // constant bytes + typical variable cells
+    Q.stage_bytes = r16((uint64_t)R * est_line + 64);
+    uint32_t o = 0;
+    Q.off_tg = o; o += Q.cap_g;
+    Q.off_ta = o; o += Q.cap_a;
+    Q.off_grec = o; o += p2::GREC_BYTES * Q.cap_ng;
+    Q.off_prec = o; o += p2::PREC_BYTES * Q.cap_rec;
+    Q.off_cnt = o; o += r16(2ull * Q.cap_c);
+    Q.off_cstart = o; o += r16(2ull * Q.cap_c);
+    Q.off_plan = o; o += r16(2ull * Q.cap_lines);
+    Q.off_loff = o; o += r16(4ull * (Q.cap_lines + 1));
+    Q.off_toff = o; o += r16(4ull * Q.cap_lines);
+    Q.off_qoff = o; o += r16(8ull * Q.cap_lines);
+    Q.off_slots = o;
+    // parse-time tables and the generic path's scratch share the slots + stage
+    uint32_t t = o;
+    Q.off_gstart = t; t += r16(2ull * (Q.cap_ng + 2));
+    Q.off_pstart = t; t += r16(2ull * (Q.cap_np + 2));
+    Q.off_cp = t; t += r16(4ull * Q.cap_np);
+    Q.off_digest = t; t += r16(4ull * Q.cap_np);
+    const uint32_t need = std::max<uint32_t>(t - o, r16(12ull * ctx->fleet.max_nc + 16));
+    o += R * Q.slot_bytes;
+    Q.off_stage = o;
+    if (R * Q.slot_bytes + Q.stage_bytes < need) Q.stage_bytes = need - R * Q.slot_bytes;
+    o += Q.stage_bytes;
+    Q.slice_bytes = r16(o);
+    if (Q.slice_bytes * 4u <= dyn_max) break;                  // at least 4 documents in flight per SM
+    if (a > 4096) a = a * 3 / 4; else if (g > 1024) g = g * 3 / 4; else return false;
+  }
+  if (Q.slice_bytes * 4u > dyn_max) return false;
+  Q.warps = std::min<uint32_t>(26u, dyn_max / Q.slice_bytes);
+  if (ctx->force_warps) Q.warps = std::max(1u, std::min(Q.warps, ctx->force_warps));
+  *out = Q;
+  return true;
+}
+
+void plan_poll2(kgm_ctx *ctx, const kgm_batch *b, uint64_t max_g, uint64_t max_a) {
+  ctx->poll2_ok = false;
+  if (b->n_docs == 0 || !ctx->p2_any) return;
+  // 4 jobs per line (8 lines per round) unless 8 jobs per line (smaller rounds, smaller slices)
+  // puts a fifth more documents in flight
+  Poll2Params q4{}, q8{};
+  const bool ok4 = poll2_layout(ctx, 2, max_g, max_a, &q4), ok8 = poll2_layout(ctx, 3, max_g, max_a, &q8);
+  if (!ok4 && !ok8) return;
+  bool take8 = !ok4 || (ok8 && q8.warps * 5u >= q4.warps * 6u);
+  if (ctx->force_jobs == 4 && ok4) take8 = false;
+  if (ctx->force_jobs == 8 && ok8) take8 = true;
+  ctx->poll2 = take8 ? q8 : q4;
+  ctx->poll2_ok = true;
+}
+
 // Validates a batch, sizes the device buffers and the workspace guesses for it and points
 // ctx->batch at them.  Nothing is copied.
 int prepare_batch(kgm_ctx *ctx, const kgm_batch *b, uint64_t *gb_out, uint64_t *ab_out) {
@@ -549,6 +644,7 @@ int prepare_batch(kgm_ctx *ctx, const kgm_batch *b, uint64_t *gb_out, uint64_t *
     max_a = std::max(max_a, aoff[d + 1] - aoff[d]);
   }
   plan_fused(ctx, b, max_g, max_a);
+  plan_poll2(ctx, b, max_g, max_a);
   ctx->have_ticks = b->doc_tick != nullptr;
   ctx->max_tick = 0;
   if (b->doc_tick) for (uint32_t d = 0; d < n; ++d) ctx->max_tick = std::max(ctx->max_tick, b->doc_tick[d]);
@@ -860,9 +956,12 @@ int kgm_create(kgm_ctx **out, int device) {
   if (const char *env = getenv("KGM_FUSED_TEAMS")) {
     ctx->force_teams = (uint32_t)std::max(0, std::min(atoi(env), 8));
   }
+  if (const char *env = getenv("KGM_POLL2_JOBS")) ctx->force_jobs = (uint32_t)atoi(env);
+  if (const char *env = getenv("KGM_POLL2_WARPS")) ctx->force_warps = (uint32_t)std::max(0, std::min(atoi(env), 26));
   if (const char *env = getenv("KGM_PIPELINE")) {
     if (!strcmp(env, "staged")) ctx->pipeline = KGM_PIPELINE_STAGED;
     else if (!strcmp(env, "fused-generic")) ctx->pipeline = KGM_PIPELINE_FUSED_GENERIC;
+    else if (!strcmp(env, "fused-v1")) ctx->pipeline = KGM_PIPELINE_FUSED_V1;
   }
   *out = ctx;
   return KGM_OK;
@@ -882,7 +981,8 @@ void kgm_destroy(kgm_ctx *ctx) {
                    &ctx->w_status, &ctx->w_doc_line_off, &ctx->w_doc_byte_off, &ctx->w_totals,
                    &ctx->w_line_off, &ctx->w_out, &ctx->w_flush, &ctx->w_ticket, &ctx->w_scan,
                    &ctx->f_node_fast, &ctx->f_tb_off, &ctx->f_tb_len, &ctx->f_tb_pool, &ctx->f_pid16,
-                   &ctx->f_vis_hash2, &ctx->w_win_samples, &ctx->w_win_groups, &ctx->w_win_temp};
+                   &ctx->f_vis_hash2, &ctx->f_node_fast2, &ctx->f_nslot_off, &ctx->f_tslot_off, &ctx->f_slot_pool,
+                   &ctx->w_win_samples, &ctx->w_win_groups, &ctx->w_win_temp};
   for (DevBuf *b : dev) b->release();
   HostBuf *host[] = {&ctx->h_small, &ctx->h_lines, &ctx->h_line_off, &ctx->h_doc_line_off, &ctx->h_status,
                      &ctx->h_chunk, &ctx->h_docarr, &ctx->h_win_groups};
@@ -1039,10 +1139,53 @@ int kgm_load_fleet(kgm_ctx *ctx, const kgm_fleet *fl) {
     }
   }
 
+  // ---- template slots of k_poll2: one per node, one per gated container.  A node with any raise
+  //      point on the docker side or a pid string longer than 7 bytes is left to the generic path. ----
+  std::vector<uint8_t> node_fast2(std::max(nn, 1u), 0), slot_pool;
+  std::vector<uint32_t> nslot_off(std::max(nn, 1u), 0), tslot_off(std::max(nc, 1u), 0);
+  uint32_t p2_max_nc = 1, p2_max_slot = 64, p2_max_fixed = 0, p2_max_idle = 0, p2_any = 0;
+  for (uint32_t n = 0; n < nn; ++n) {
+    const uint32_t cb = fl->cont_begin[n], ce = fl->cont_begin[n + 1], ncn = ce - cb;
+    bool ok = !fl->node_err_parse[n] && !fl->node_err_join[n] && ncn <= 512 && ctx->node_idle_cap[n] <= 1024;
+    for (uint32_t c = cb; c < ce && ok; ++c) {
+      if (fl->err_inspect[c] || fl->err_emit[c]) ok = false;
+      for (uint32_t k = fl->pid_begin[c]; k < fl->pid_begin[c + 1] && ok; ++k)
+        if (fl->pid.off[k + 1] - fl->pid.off[k] > 7) ok = false;
+    }
+    if (!ok || !node_fast[n]) continue;                // (the compact pid table holds the v1-fast nodes' pids)
+    const size_t mark = slot_pool.size();
+    const std::string host = str_of(fl->node_name, n);
+    size_t start = 0, len = 0;
+    uint32_t max_slot = 0, max_fixed = node_fixed[n] + 1;
+    ok = build_node_slot(host, slot_pool, &start, &len);
+    if (ok) { nslot_off[n] = (uint32_t)(start >> 4); max_slot = (uint32_t)len; }
+    for (uint32_t c = cb; c < ce && ok; ++c) {
+      if (!fl->gated[c]) continue;
+      ok = build_pod_slot(host, str_of(fl->ns, c), str_of(fl->cid, c), str_of(fl->user, c), str_of(fl->pod, c),
+                          slot_pool, &start, &len);
+      if (ok) {
+        tslot_off[c] = (uint32_t)(start >> 4);
+        max_slot = std::max<uint32_t>(max_slot, (uint32_t)len);
+        max_fixed = std::max(max_fixed, cont_fixed[c] + 1);
+      }
+    }
+    if (!ok || max_slot > 4096 || slot_pool.size() >= 0xf0000000ull) { slot_pool.resize(mark); continue; }
+    node_fast2[n] = 1; p2_any = 1;
+    p2_max_nc = std::max(p2_max_nc, ncn);
+    p2_max_slot = std::max(p2_max_slot, max_slot);
+    p2_max_fixed = std::max(p2_max_fixed, max_fixed);
+    p2_max_idle = std::max<uint32_t>(p2_max_idle, (uint32_t)ctx->node_idle_cap[n]);
+  }
+  slot_pool.resize(slot_pool.size() + p2_max_slot + 64, 0);      // every slot can be read at the largest slot's size
+
   ctx->fleet_loaded = false;
   ctx->batch_resident = false;
   ctx->have_result = false;
   int rc;
+  if ((rc = upload(ctx, ctx->f_node_fast2, node_fast2.data(), node_fast2.size()))) return rc;
+  if ((rc = upload(ctx, ctx->f_nslot_off, nslot_off.data(), nslot_off.size()))) return rc;
+  if ((rc = upload(ctx, ctx->f_tslot_off, tslot_off.data(), tslot_off.size()))) return rc;
+  if ((rc = upload(ctx, ctx->f_slot_pool, slot_pool.data(), slot_pool.size()))) return rc;
   if ((rc = upload(ctx, ctx->f_cont_begin, fl->cont_begin, (size_t)nn + 1))) return rc;
   if ((rc = upload(ctx, ctx->f_nerr_parse, fl->node_err_parse, nn))) return rc;
   if ((rc = upload(ctx, ctx->f_nerr_join, fl->node_err_join, nn))) return rc;
@@ -1092,6 +1235,15 @@ int kgm_load_fleet(kgm_ctx *ctx, const kgm_fleet *fl) {
   f.pid16 = ctx->f_pid16.as<fast::PidSlot16>();
   f.pid16_mask = t16 - 1;
   f.vis_hash2 = ctx->f_vis_hash2.as<uint64_t>();
+  f.node_fast2 = ctx->f_node_fast2.as<uint8_t>();
+  f.nslot_off = ctx->f_nslot_off.as<uint32_t>();
+  f.tslot_off = ctx->f_tslot_off.as<uint32_t>();
+  f.slot_pool = ctx->f_slot_pool.as<uint8_t>();
+  ctx->p2_max_nc = p2_max_nc; ctx->p2_max_slot = p2_max_slot; ctx->p2_max_fixed = p2_max_fixed;
+  ctx->p2_max_idle = p2_max_idle; ctx->p2_any = p2_any;
+  ctx->h_node_fast2 = node_fast2;
+  ctx->all_nodes_fast2 = std::all_of(node_fast2.begin(), node_fast2.end(), [](uint8_t v) { return v != 0; });
+  ctx->poll2_ok = false;
   ctx->fast_max_nc = fast_max_nc; ctx->fast_max_tb = fast_max_tb; ctx->fast_max_idle = fast_max_idle;
   ctx->any_fast = any_fast;
   ctx->h_node_fast = node_fast;
@@ -1204,7 +1356,8 @@ int kgm_encode_batch(kgm_ctx *ctx, const kgm_batch *b, int want_host_copy, kgm_r
         ctx->timing.launches = ctx->last_chunks;
         ctx->timing.fused = 1;
         ctx->timing.slow_docs = ctx->slow_docs;
-        ctx->timing.fused_ctas_per_sm = (uint32_t)ctx->fused_ctas_per_sm;
+        ctx->timing.fused_ctas_per_sm = ctx->last_poll2 ? 1u : (uint32_t)ctx->fused_ctas_per_sm;
+        ctx->timing.docs_in_flight_per_sm = ctx->last_poll2 ? ctx->poll2.warps : ctx->fused.teams * ctx->fused_ctas_per_sm;
         cudaGetLastError();
       }
       return rc;
@@ -1362,7 +1515,7 @@ int kgm_debug_chunk_times(kgm_ctx *ctx, float *text_in_ms, float *kernel_done_ms
 }
 
 int kgm_set_pipeline(kgm_ctx *ctx, int mode) {
-  if (!ctx || mode < KGM_PIPELINE_AUTO || mode > KGM_PIPELINE_FUSED_GENERIC) return KGM_E_INVALID;
+  if (!ctx || mode < KGM_PIPELINE_AUTO || mode > KGM_PIPELINE_FUSED_V1) return KGM_E_INVALID;
   ctx->pipeline = mode;
   return KGM_OK;
 }

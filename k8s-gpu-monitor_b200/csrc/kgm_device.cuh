@@ -41,6 +41,11 @@ struct FleetDev {
   const fast::PidSlot16 *pid16;  // pids of up to 7 bytes
   uint32_t pid16_mask;
   const uint64_t *vis_hash2;     // fast::key_hash_bytes of every visible uuid
+  // tables of k_poll2 (kgm_poll2_leaf.cuh): one template slot per node and per gated container
+  const uint8_t *node_fast2;     // 1 = the node's documents may take k_poll2's fast path
+  const uint32_t *nslot_off;     // per node: its slot in slot_pool, in 16-byte units
+  const uint32_t *tslot_off;     // per container: its slot (0 for containers that are not gated)
+  const uint8_t *slot_pool;      // 16-byte aligned slots, padded so that slot_bytes can be read from any of them
 };
 
 enum : int { CTR_GROW = 0, CTR_PROW = 1, CTR_DESC = 2, CTR_OVERFLOW = 3, CTR_SLOW = 4, CTR_COUNT = 8,
@@ -102,8 +107,30 @@ struct FusedParams {
                                     // (chunked end-to-end path), or null
 };
 
+// Launch parameters of k_poll2 (kgm_poll2.cuh): the layout of a warp's shared-memory slice (byte
+// offsets from the slice start, all 16-byte aligned).  The scan / ticket state is FusedParams'.
+struct Poll2Params {
+  uint32_t warps;                // warps (documents in flight) per CTA
+  uint32_t slice_bytes;
+  uint32_t cap_g, cap_a;         // text windows (bytes, incl. slack)
+  uint32_t cap_ng, cap_np;       // rows per document
+  uint32_t cap_rec;              // process rows + idle pseudo-rows
+  uint32_t cap_c;                // containers per node
+  uint32_t cap_lines;            // lines per document
+  uint32_t slot_bytes;           // template slot (multiple of 16)
+  uint32_t slot_magic;           // ceil(2^32 / (slot_bytes / 16)): x / (slot_bytes / 16) == umulhi(x, magic) for x < 2^16
+  uint32_t stage_bytes;          // incl. 64 bytes of slack
+  uint32_t jshift;               // 2: 4 jobs per line, 8 lines per round; 3: 8 jobs per line, 4 lines per round
+  uint32_t off_tg, off_ta, off_grec, off_prec, off_cnt, off_cstart, off_plan, off_loff, off_toff, off_qoff,
+      off_slots, off_stage;
+  uint32_t off_gstart, off_pstart, off_cp, off_digest;   // parse-time tables, inside [off_slots, slice end)
+};
+
 void launch_poll(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P, int blocks,
                  cudaStream_t s);
+void launch_poll2(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P, const Poll2Params &Q,
+                  int blocks, int device, cudaStream_t s);
+int poll2_smem_bytes(const Poll2Params &Q);
 int poll_smem_bytes(const FusedParams &P);
 int debug_stage_clocks(unsigned long long *out64);   // 0 unless built with -DKGM_PROFILE_STAGES
 

@@ -266,7 +266,7 @@ KGM_HD bool finish_gpu_row(const uint32_t *W, GRec &g) {
 // One --query-compute-apps row.  `kw` receives the lstripped gpu_uuid cell (for the
 // dictionary lookup), `klen` its length.  Returns false = irregular.
 KGM_HD bool parse_proc_row(const uint32_t *W, uint32_t s, uint32_t e, PRec &p, uint32_t *kw,
-                           uint32_t *klen, uint64_t *khash) {
+                           uint32_t *klen, uint64_t *khash, uint32_t *koff = nullptr) {
   if (e <= s || e - s > 1000) return false;
   RowShape sh;
   scan_commas<4>(W, s, e, sh);
@@ -329,6 +329,7 @@ KGM_HD bool parse_proc_row(const uint32_t *W, uint32_t s, uint32_t e, PRec &p, u
   while (k < c2 && load1(W, k) == 32u) ++k;
   if (c2 - k > 4u * KEY_WORDS) return false;
   *klen = c2 - k;
+  if (koff) *koff = k;
   load_key(W, k, c2 - k, kw);
   *khash = key_hash_words(kw, c2 - k);
   if (!digit_run(W, c2 + 1, c3, p.mem)) return false;

@@ -90,14 +90,15 @@ struct ScanWords { uint64_t l, b; bool inc; };
 __device__ __forceinline__ ScanWords scan_wait(const unsigned long long *st, uint64_t agg, uint64_t inc,
                                                bool need_inc) {
   const uint64_t VAL = (1ull << 46) - 1ull;
-  for (;;) {
+  // a waiting lane shares its scheduler with warps that have work: back off quickly
+  for (uint32_t ns = 128;; ns = min(ns * 2u, 4096u)) {
     const uint64_t w0 = ld_acquire(st);
     const uint64_t t0 = w0 & ~VAL;
     if (t0 == inc || (!need_inc && t0 == agg)) {
       const uint64_t w1 = ld_relaxed(st + 1);
       if ((w1 & ~VAL) == t0) return ScanWords{w0 & VAL, w1 & VAL, t0 == inc};
     }
-    __nanosleep(40);
+    __nanosleep(ns);
   }
 }
 __device__ __forceinline__ void scan_store(unsigned long long *st, uint64_t tag, uint64_t l, uint64_t b) {

@@ -703,6 +703,7 @@ __global__ void k_flush(uint4 *buf, uint64_t n16) {
 }  // namespace kgm
 
 #include "kgm_fused.cuh"
+#include "kgm_poll2.cuh"
 
 namespace kgm {
 

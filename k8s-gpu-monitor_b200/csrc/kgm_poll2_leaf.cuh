@@ -1,0 +1,345 @@
+// Leaf functions and table layouts of the poll kernel k_poll (kgm_poll2.cuh).
+//
+// Like kgm_common.cuh / kgm_fast.cuh this is per-thread code compiled twice: by nvcc for the
+// kernel (the word array is then the CTA's shared memory) and by g++ for the CPU tests in
+// tests/native/hostcheck.cpp, which compose whole lines with it and compare them with the
+// reference's bytes (gpu.py:136-143, 206-216, 240-250).
+//
+// Vocabulary
+//   run word   one byte run inside the word array: offset << 12 | length (offset < 2^20 bytes,
+//              length < 4096)
+//   record     the run words of one output line's variable cells: 16 words per --query-gpu row
+//              (GREC_*), 8 words per --query-compute-apps row or idle pseudo-row (PREC_*)
+//   slot       the constant pieces of one node's / one container's line template, built once by
+//              kgm_load_fleet: 48-byte header (8 run words relative to the slot start, the
+//              constant-byte prefix at every job boundary, the constant byte count of a line)
+//              followed by the piece bytes
+//   segment    a line is a fixed sequence of segments, each a run taken from the slot ('T'), from
+//              the table of constant strings ('K') or from the line's record ('R')
+//   job        a contiguous range of segments of one line, written by one lane; a line is cut
+//              into 8 jobs at fixed segment indices (or 4, each two of those)
+#pragma once
+#include <stdint.h>
+
+#include "kgm_fast.cuh"
+
+namespace kgm {
+namespace p2 {
+
+using namespace fast;
+
+constexpr uint32_t KIND_NODE = 0, KIND_BUSY = 1, KIND_IDLE = 2;
+
+KGM_HD uint32_t rw(uint32_t off, uint32_t len) { return (off << 12) | len; }
+KGM_HD uint32_t rw_off(uint32_t w) { return w >> 12; }
+KGM_HD uint32_t rw_len(uint32_t w) { return w & 0xfffu; }
+constexpr uint32_t RW_MAX_LEN = 4095;
+
+// ---- records -----------------------------------------------------------------------------------
+constexpr uint32_t GREC_WORDS = 16, GREC_BYTES = 64;
+constexpr uint32_t GREC_UTIL = 0, GREC_MU = 1, GREC_MT = 2, GREC_MF = 3, GREC_FSTR = 4, GREC_SID = 5,
+                   GREC_KEY = 6, GREC_LINE_LEN = 7, GREC_HASH = 8 /* 2 words */, GREC_FSTR_BYTES = 40 /* byte offset */;
+constexpr uint32_t PREC_WORDS = 8, PREC_BYTES = 32;
+constexpr uint32_t PREC_PID = 0, PREC_NAME = 1 /* NAME_RUNS words */, PREC_MEM = 5, PREC_UTIL = 6, PREC_SID = 7;
+static_assert(NAME_RUNS == 4, "PREC_NAME..PREC_MEM");
+
+// ---- constant strings shared by a CTA ------------------------------------------------------------
+// The ConstArea of kgm_fast.cuh (strings + decimal strings), then the table of 'K' run words, the
+// segment tables and the constant part of an idle pseudo-row.
+struct CA2 {
+  static constexpr uint32_t NL = 120;                                   // "\n" (free bytes of ConstArea)
+  static constexpr uint32_t KTAB = (ConstArea::BYTES + 15u) & ~15u;      // 16 run words
+  static constexpr uint32_t SEGTAB = KTAB + 64;                          // 2 x 32 segment descriptors
+  static constexpr uint32_t IDLE_REC = SEGTAB + 64;                      // 8 run words
+  static constexpr uint32_t BYTES = IDLE_REC + 32;
+};
+constexpr uint32_t K_GPU_UTIL = 0, K_MEM_UTIL = 1, K_MEM_USED = 2, K_MEM_TOTAL = 3, K_MEM_FREE = 4,
+                   K_GPU_UTIL_T = 5, K_GPU_ID_V = 6, K_USED_MEMORY = 7, K_NL = 8, K_NONE = 9, K_DASH = 10,
+                   K_ZERO = 11, K_EMPTY = 12;
+
+// ---- segment tables ----------------------------------------------------------------------------
+// descriptor = type << 6 | index;  type 0 = slot run word, 1 = 'K' run word, 2 = record run word
+constexpr uint32_t SEG_T = 0u << 6, SEG_K = 1u << 6, SEG_R = 2u << 6;
+constexpr uint32_t NODE_SEGS = 15, POD_SEGS = 20;
+
+// node_gpu,host=H,gpu_id=<K> gpu_util=<U>,mem_util=<F>,mem_used=<MU>,mem_total=<MT>,node="H",gid=<K>,mem_free=<MF>\n
+KGM_HD constexpr uint32_t seg_node(int k) {
+  return k == 0 ? SEG_T | 0 : k == 1 ? SEG_R | GREC_SID : k == 2 ? SEG_K | K_GPU_UTIL : k == 3 ? SEG_R | GREC_UTIL
+       : k == 4 ? SEG_K | K_MEM_UTIL : k == 5 ? SEG_R | GREC_FSTR : k == 6 ? SEG_K | K_MEM_USED
+       : k == 7 ? SEG_R | GREC_MU : k == 8 ? SEG_K | K_MEM_TOTAL : k == 9 ? SEG_R | GREC_MT : k == 10 ? SEG_T | 1
+       : k == 11 ? SEG_R | GREC_SID : k == 12 ? SEG_K | K_MEM_FREE : k == 13 ? SEG_R | GREC_MF : SEG_K | K_NL;
+}
+// pod_gpu,host=H,namespace=NS,gpu_id=<G>,containerid=C,pid_t=<P>,gpu_util_t=<U>,user_name_t=UN procressname="<PN>",
+// podname="POD",pid="<P>",gpu_id_v="<G>",node="H",user_name="UN",gpu_util=<U>,used_memory=<UM>\n
+KGM_HD constexpr uint32_t seg_pod(int k) {
+  return k == 0 ? SEG_T | 0 : k == 1 ? SEG_R | PREC_SID : k == 2 ? SEG_T | 1 : k == 3 ? SEG_R | PREC_PID
+       : k == 4 ? SEG_K | K_GPU_UTIL_T : k == 5 ? SEG_R | PREC_UTIL : k == 6 ? SEG_T | 2
+       : k == 7 ? SEG_R | (PREC_NAME + 0) : k == 8 ? SEG_R | (PREC_NAME + 1) : k == 9 ? SEG_R | (PREC_NAME + 2)
+       : k == 10 ? SEG_R | (PREC_NAME + 3) : k == 11 ? SEG_T | 3 : k == 12 ? SEG_R | PREC_PID
+       : k == 13 ? SEG_K | K_GPU_ID_V : k == 14 ? SEG_R | PREC_SID : k == 15 ? SEG_T | 4
+       : k == 16 ? SEG_R | PREC_UTIL : k == 17 ? SEG_K | K_USED_MEMORY : k == 18 ? SEG_R | PREC_MEM : SEG_K | K_NL;
+}
+// job boundaries: job q of 8 covers segments [jb8(q), jb8(q+1)); with 4 jobs per line job q covers
+// the jobs 2q and 2q+1 of 8
+// (equal segment counts per job of 4: the lanes of a round then meet pieces of similar length at
+// the same step -- step t of a pod line's four jobs copies segments t, 5+t, 10+t, 15+t)
+KGM_HD constexpr uint32_t jb8_node(int q) {
+  return q == 0 ? 0 : q == 1 ? 2 : q == 2 ? 4 : q == 3 ? 6 : q == 4 ? 8 : q == 5 ? 10 : q == 6 ? 12 : q == 7 ? 14 : 15;
+}
+KGM_HD constexpr uint32_t jb8_pod(int q) {
+  return q == 0 ? 0 : q == 1 ? 3 : q == 2 ? 5 : q == 3 ? 8 : q == 4 ? 10 : q == 5 ? 13 : q == 6 ? 15 : q == 7 ? 18 : 20;
+}
+KGM_HD constexpr uint64_t jb8_pack(bool pod) {                           // 9 x 5 bits
+  uint64_t v = 0;
+  for (int q = 0; q <= 8; ++q) v |= (uint64_t)(pod ? jb8_pod(q) : jb8_node(q)) << (5 * q);
+  return v;
+}
+
+// The constant area is filled in three independent parts (the kernel gives them to different
+// threads; the area must be zeroed first).  `abs0` = its byte offset in the word array that
+// run words refer to.
+KGM_HD void fill_ca2_strings(uint8_t *c) {
+  fill_const_strings(c);
+  c[CA2::NL] = 10u;
+}
+KGM_HD void fill_ca2_tables(uint8_t *c, uint32_t abs0) {
+  uint32_t *kt = reinterpret_cast<uint32_t *>(c + CA2::KTAB);
+  for (int i = 0; i < 16; ++i) kt[i] = rw(abs0, 0);
+  kt[K_GPU_UTIL] = rw(abs0 + ConstArea::GPU_UTIL, 10);
+  kt[K_MEM_UTIL] = rw(abs0 + ConstArea::MEM_UTIL, 10);
+  kt[K_MEM_USED] = rw(abs0 + ConstArea::MEM_USED, 10);
+  kt[K_MEM_TOTAL] = rw(abs0 + ConstArea::MEM_TOTAL, 11);
+  kt[K_MEM_FREE] = rw(abs0 + ConstArea::MEM_FREE, 10);
+  kt[K_GPU_UTIL_T] = rw(abs0 + ConstArea::GPU_UTIL_T, 12);
+  kt[K_GPU_ID_V] = rw(abs0 + ConstArea::GPU_ID_V, 12);
+  kt[K_USED_MEMORY] = rw(abs0 + ConstArea::USED_MEMORY, 13);
+  kt[K_NL] = rw(abs0 + CA2::NL, 1);
+  kt[K_NONE] = rw(abs0 + ConstArea::NONE, 4);
+  kt[K_DASH] = rw(abs0 + ConstArea::DASH, 1);
+  kt[K_ZERO] = rw(abs0 + ConstArea::ZERO, 1);
+  // idle pseudo-row (gpu.py:234-239): pid "-", procressname "-", used_memory 0, gpu_util 0
+  uint32_t *ir = reinterpret_cast<uint32_t *>(c + CA2::IDLE_REC);
+  ir[PREC_PID] = kt[K_DASH];
+  ir[PREC_NAME] = kt[K_DASH];
+  ir[PREC_NAME + 1] = ir[PREC_NAME + 2] = ir[PREC_NAME + 3] = kt[K_EMPTY];
+  ir[PREC_MEM] = kt[K_ZERO];
+  ir[PREC_UTIL] = kt[K_ZERO];
+  ir[PREC_SID] = kt[K_NONE];
+}
+KGM_HD void fill_ca2_segtab(uint8_t *c, int k) {                         // k in 0..31
+  uint8_t *st = c + CA2::SEGTAB;
+  uint32_t a = SEG_K | K_EMPTY, b = SEG_K | K_EMPTY;
+  for (int i = 0; i < (int)POD_SEGS; ++i) {
+    if (i == k && i < (int)NODE_SEGS) a = seg_node(i);
+    if (i == k) b = seg_pod(i);
+  }
+  st[k] = (uint8_t)a;
+  st[32 + k] = (uint8_t)b;
+}
+KGM_HD void fill_ca2(uint8_t *c, uint32_t abs0) {                       // the whole area, one thread (host)
+  for (uint32_t i = 0; i < CA2::BYTES; ++i) c[i] = 0;
+  fill_ca2_strings(c);
+  for (uint32_t v = 0; v <= MAX_FAST_SID; ++v) fill_const_decimal(c, v);
+  fill_ca2_tables(c, abs0);
+  for (int k = 0; k < 32; ++k) fill_ca2_segtab(c, k);
+}
+
+KGM_HD uint32_t sid_run(uint32_t abs0, uint32_t sid) {                   // '%s' % shortunitids.get(uuid)
+  if (sid == NONE32) return rw(abs0 + ConstArea::NONE, 4);
+  return rw(abs0 + ConstArea::DEC + 4u * sid, dec_len(sid));
+}
+
+// ---- slots -------------------------------------------------------------------------------------
+constexpr uint32_t SLOT_HEADER = 48;
+constexpr uint32_t SLOT_CPRE = 32;           // 7 x u16: constant bytes in front of job q+1 of 8
+constexpr uint32_t SLOT_FIXED = 46;          // u16: constant bytes of a line (incl. '\n')
+
+// lengths of the 'K' strings (the host needs them for the slots' constant-byte prefixes)
+KGM_HD constexpr uint32_t k_len(uint32_t idx) {
+  return idx == K_MEM_TOTAL ? 11u : idx == K_GPU_UTIL_T || idx == K_GPU_ID_V ? 12u : idx == K_USED_MEMORY ? 13u
+       : idx == K_NL || idx == K_DASH || idx == K_ZERO ? 1u : idx == K_NONE ? 4u : idx == K_EMPTY ? 0u : 10u;
+}
+
+// ---- measuring a line: its variable bytes in front of every job boundary ------------------------
+// 7 x 9 bits (a line whose variable cells exceed 511 bytes is left to the generic path).  `r`
+// = the record's run words.  *total receives all variable bytes of the line.
+template <bool POD>
+KGM_HD uint64_t measure_line(const uint32_t *r, uint32_t *total) {
+  uint32_t acc = 0;
+  uint64_t packed = 0;
+  constexpr int NS = POD ? (int)POD_SEGS : (int)NODE_SEGS;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int k = 0; k < NS; ++k) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int q = 1; q < 8; ++q)
+      if ((POD ? jb8_pod(q) : jb8_node(q)) == (uint32_t)k) packed |= (uint64_t)acc << (9 * (q - 1));
+    const uint32_t e = POD ? seg_pod(k) : seg_node(k);
+    if ((e >> 6) == 2u) acc += rw_len(r[e & 63u]);
+  }
+  *total = acc;
+  return packed;
+}
+
+// ---- composing --------------------------------------------------------------------------------
+// Writes the segments of job `q8 .. q8 + nq8` (of 8) of one line into the word array B.
+//   ca      byte offset of the constant area (CA2) in B
+//   tmpl    byte offset of the line's slot in B
+//   rec     byte offset of the line's record in B
+//   dst     byte offset of the line's first byte in B
+//   qoff    measure_line() of the line
+// Only bytes of the job's own segments are written (byte stores at segment ends), so the jobs of
+// a line, and neighbouring lines, can be written by different lanes.
+KGM_HD void compose_job(uint32_t *B, uint32_t ca, uint32_t pod, uint32_t q8, uint32_t nq8, uint32_t tmpl,
+                        uint32_t rec, uint32_t dst, uint64_t qoff) {
+  const uint8_t *Bb = reinterpret_cast<const uint8_t *>(B);
+  const uint64_t pack = pod ? jb8_pack(true) : jb8_pack(false);
+  const uint32_t k0 = (uint32_t)(pack >> (5u * q8)) & 31u, k1 = (uint32_t)(pack >> (5u * (q8 + nq8))) & 31u;
+  uint32_t at = dst;
+  if (q8) {
+    at += *reinterpret_cast<const uint16_t *>(Bb + tmpl + SLOT_CPRE + 2u * (q8 - 1u));
+    at += (uint32_t)(qoff >> (9u * (q8 - 1u))) & 511u;
+  }
+  const uint8_t *st = Bb + ca + CA2::SEGTAB + (pod ? 32u : 0u);
+  for (uint32_t k = k0; k < k1; ++k) {
+    const uint32_t e = st[k], type = e >> 6;
+    const uint32_t base = type == 0u ? tmpl : type == 1u ? ca + CA2::KTAB : rec;
+    const uint32_t w = B[(base >> 2) + (e & 63u)];
+    const uint32_t len = rw_len(w);
+    if (len) copy_run(B, at, rw_off(w) + (type == 0u ? tmpl : 0u), len);
+    at += len;
+  }
+}
+
+// ---- parsing: the row parsers of kgm_fast.cuh, returning runs relative to the text window -------
+struct G2 {                                         // one --query-gpu row (gpu.py:104-109)
+  Run key, util, mt, mu, mf;
+  uint64_t hash;                                    // of lstrip(cell 0)
+  uint64_t total, used;                             // int(digits) of memory.total / memory.used
+};
+
+// int(digits) of a run of at most 18 digits, two words at a time
+KGM_HD uint64_t run_value2(const uint32_t *W, Run r) {
+  uint64_t v = 0;
+  uint32_t o = r.off, n = r.len;
+  while (n >= 4) {
+    const uint32_t w = load4(W, o) - 0x30303030u;                      // 4 digits, first one in the low byte
+    const uint32_t t = (w * 10u + (w >> 8)) & 0x00ff00ffu;              // pairs: d0d1 in bits 0..7, d2d3 in 16..23
+    v = v * 10000u + ((t & 0xffu) * 100u + (t >> 16));
+    o += 4; n -= 4;
+  }
+  for (; n; --n, ++o) v = v * 10u + (load1(W, o) - 48u);
+  return v;
+}
+
+// Same accept / decline rules as fast::parse_gpu_row (kgm_fast.cuh); false = irregular row.
+KGM_HD bool parse_gpu_row2(const uint32_t *W, uint32_t s, uint32_t e, G2 &g) {
+  if (e <= s || e - s > 1000) return false;
+  RowShape sh;
+  scan_commas<6>(W, s, e, sh);
+  if (sh.irregular || sh.ncommas < 5) return false;               // fewer than 6 cells: KeyError
+  const uint32_t c0 = sh.comma[0], c1 = sh.comma[1], c2 = sh.comma[2], c3 = sh.comma[3], c4 = sh.comma[4];
+  const uint32_t c5 = sh.ncommas >= 6 ? sh.comma[5] : e;          // zip() drops extra cells (gpu.py:49)
+  uint32_t k = s;
+  while (k < c0 && load1(W, k) == 32u) ++k;                       // lstrip (gpu.py:108)
+  if (c0 - k > 4u * KEY_WORDS) return false;
+  g.key.off = (uint16_t)k; g.key.len = (uint16_t)(c0 - k);
+  {
+    uint32_t kw[KEY_WORDS];
+    load_key(W, k, c0 - k, kw);
+    g.hash = key_hash_words(kw, c0 - k);
+  }
+  if (!digit_run(W, c0 + 1, c1, g.util)) return false;
+  if (!digit_run(W, c2 + 1, c3, g.mt)) return false;
+  if (!digit_run(W, c3 + 1, c4, g.mu)) return false;
+  if (!digit_run(W, c4 + 1, c5, g.mf)) return false;
+  if (g.mt.len == 0 || g.mu.len == 0) return false;               // ValueError gpu.py:133-134
+  if (g.mt.len > 18 || g.mu.len > 18) return false;
+  g.total = run_value2(W, g.mt);
+  g.used = run_value2(W, g.mu);
+  return g.total != 0;                                            // ZeroDivisionError gpu.py:135
+}
+
+struct P2 {                                         // one --query-compute-apps row (gpu.py:111-116)
+  uint64_t pidkey;                                  // pid cell bytes (<= 7) | len << 56; ~0 if longer
+  Run pid, name[NAME_RUNS], mem, key;
+  uint64_t khash;                                   // of lstrip(cell 2)
+};
+
+KGM_HD bool parse_proc_row2(const uint32_t *W, uint32_t s, uint32_t e, P2 &p) {
+  PRec r;
+  uint32_t kw[KEY_WORDS], klen = 0;
+  uint64_t kh = 0;
+  uint32_t koff = 0;
+  if (!parse_proc_row(W, s, e, r, kw, &klen, &kh, &koff)) return false;
+  p.pidkey = r.pidkey;
+  p.pid = r.pid;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int i = 0; i < NAME_RUNS; ++i) p.name[i] = r.name[i];
+  p.mem = r.mem;
+  p.key.off = (uint16_t)koff; p.key.len = (uint16_t)klen;
+  p.khash = kh;
+  return true;
+}
+
+// The record of a gpu row: run words with absolute offsets.  `tg` = byte offset of the text window
+// the runs of `g` refer to, `rec` = byte offset of the record itself (its bytes 40..63 receive
+// repr(mem_util), gpu.py:135,139), `sid` = the row's short id.  Returns the variable bytes of
+// its node_gpu line.
+KGM_HD void store_grec(uint32_t *B, uint32_t tg, uint32_t rec, const G2 &g, uint32_t sid) {
+  uint32_t *r = B + (rec >> 2);
+  const uint32_t fs = rec + GREC_FSTR_BYTES;
+  const uint32_t flen = (uint32_t)float_repr(mem_util(g.used, g.total), reinterpret_cast<uint8_t *>(B) + fs);
+  r[GREC_UTIL] = rw(tg + g.util.off, g.util.len);
+  r[GREC_MU] = rw(tg + g.mu.off, g.mu.len);
+  r[GREC_MT] = rw(tg + g.mt.off, g.mt.len);
+  r[GREC_MF] = rw(tg + g.mf.off, g.mf.len);
+  r[GREC_FSTR] = rw(fs, flen);
+  r[GREC_SID] = sid_run(0u, sid);
+  r[GREC_KEY] = rw(tg + g.key.off, g.key.len);
+  r[GREC_LINE_LEN] = 0;
+  r[GREC_HASH] = (uint32_t)g.hash;
+  r[GREC_HASH + 1] = (uint32_t)(g.hash >> 32);
+}
+// The record of a process row; `grec` = the record of its gpu (utilization and short id are the
+// gpu's, gpu.py:202,205).
+KGM_HD void store_prec(uint32_t *B, uint32_t ta, uint32_t rec, const P2 &p, const uint32_t *grec) {
+  uint32_t *q = B + (rec >> 2);
+  q[PREC_PID] = rw(ta + p.pid.off, p.pid.len);
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int i = 0; i < NAME_RUNS; ++i) q[PREC_NAME + i] = rw(ta + p.name[i].off, p.name[i].len);
+  q[PREC_MEM] = rw(ta + p.mem.off, p.mem.len);
+  q[PREC_UTIL] = grec[GREC_UTIL];
+  q[PREC_SID] = grec[GREC_SID];
+}
+// The pseudo-row of an idle line (gpu.py:225-239): constants, and the short id or None.
+KGM_HD void store_idle_rec(uint32_t *B, uint32_t ca, uint32_t rec, uint32_t sid) {
+  uint32_t *q = B + (rec >> 2);
+  const uint32_t *proto = B + ((ca + CA2::IDLE_REC) >> 2);
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int i = 0; i < (int)PREC_WORDS; ++i) q[i] = proto[i];
+  q[PREC_SID] = sid_run(ca, sid);
+}
+
+// bytes [a, a+n) of word array A == bytes [b, b+n) of word array B  (n <= 4 * KEY_WORDS)
+KGM_HD bool keys_equal(const uint32_t *A, uint32_t a, const uint32_t *Bw, uint32_t b, uint32_t n) {
+  bool eq = true;
+  for (uint32_t i = 0; i < n; i += 4) {
+    uint32_t x = load4(A, a + i), y = load4(Bw, b + i);
+    if (i + 4 > n) { const uint32_t m = low_mask(n - i); x &= m; y &= m; }
+    eq &= x == y;
+  }
+  return eq;
+}
+
+}  // namespace p2
+}  // namespace kgm

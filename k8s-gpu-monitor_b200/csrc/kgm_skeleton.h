@@ -9,6 +9,7 @@
 
 #include "kgm_common.cuh"
 #include "kgm_fast.cuh"
+#include "kgm_poll2_leaf.cuh"
 
 namespace kgm {
 
@@ -114,6 +115,62 @@ inline bool build_template_block(const std::string &host, uint32_t node_fixed,
   out.insert(out.end(), dp, dp + sizeof(fast::TbCont) * (size_t)ncn);
   out.insert(out.end(), pieces.begin(), pieces.end());
   return true;
+}
+
+// ---- template slots of k_poll2 (kgm_poll2_leaf.cuh) -------------------------------------------
+// One slot per node (the two pieces of its node_gpu lines) and per gated container (the five
+// pieces of its pod_gpu lines): header | piece bytes, 16-byte aligned and padded.
+//   header  8 run words relative to the slot start (piece i), 7 x u16 constant bytes in front of
+//           job 1..7 (of 8), u16 constant bytes of a whole line incl. its '\n'
+// Appends the slot to `pool` and returns true; false (pool untouched) if a piece is too long.
+inline bool build_slot(bool pod, const std::string *pieces, int npieces, std::vector<uint8_t> &pool,
+                       size_t *start_out, size_t *len_out) {
+  using namespace p2;
+  uint32_t W[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  uint32_t at = SLOT_HEADER;
+  for (int i = 0; i < npieces; ++i) {
+    if (pieces[i].size() > 2000) return false;
+    W[i] = rw(at, (uint32_t)pieces[i].size());
+    at += (uint32_t)pieces[i].size();
+  }
+  if (at > 8192) return false;
+  uint16_t tail[8];
+  uint32_t cst = 0;
+  const int ns = pod ? (int)POD_SEGS : (int)NODE_SEGS;
+  for (int k = 0; k <= ns; ++k) {
+    for (int q = 1; q < 8; ++q)
+      if ((pod ? jb8_pod(q) : jb8_node(q)) == (uint32_t)k) tail[q - 1] = (uint16_t)cst;
+    if (k == ns) break;
+    const uint32_t e = pod ? seg_pod(k) : seg_node(k);
+    if ((e >> 6) == 0u) cst += rw_len(W[e & 63u]);
+    else if ((e >> 6) == 1u) cst += k_len(e & 63u);
+  }
+  tail[7] = (uint16_t)cst;
+  while (pool.size() & 15) pool.push_back(0);
+  *start_out = pool.size();
+  const uint8_t *wp = reinterpret_cast<const uint8_t *>(W), *tp = reinterpret_cast<const uint8_t *>(tail);
+  pool.insert(pool.end(), wp, wp + 32);
+  pool.insert(pool.end(), tp, tp + 16);
+  for (int i = 0; i < npieces; ++i) pool.insert(pool.end(), pieces[i].begin(), pieces[i].end());
+  while (pool.size() & 15) pool.push_back(0);
+  *len_out = pool.size() - *start_out;
+  return true;
+}
+
+inline bool build_node_slot(const std::string &host, std::vector<uint8_t> &pool, size_t *start, size_t *len) {
+  const std::string pc[2] = {"node_gpu,host=" + host + ",gpu_id=", ",node=\"" + host + "\",gid="};
+  return build_slot(false, pc, 2, pool, start, len);
+}
+
+inline bool build_pod_slot(const std::string &host, const std::string &ns, const std::string &cid,
+                           const std::string &user, const std::string &pod, std::vector<uint8_t> &pool,
+                           size_t *start, size_t *len) {
+  const std::string pc[5] = {"pod_gpu,host=" + host + ",namespace=" + ns + ",gpu_id=",
+                             ",containerid=" + cid + ",pid_t=",
+                             ",user_name_t=" + user + " procressname=\"",
+                             "\",podname=\"" + pod + "\",pid=\"",
+                             "\",node=\"" + host + "\",user_name=\"" + user + "\",gpu_util="};
+  return build_slot(true, pc, 5, pool, start, len);
 }
 
 }  // namespace kgm

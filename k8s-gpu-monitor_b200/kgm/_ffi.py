@@ -86,7 +86,7 @@ class KgmTiming(C.Structure):
         ("h2d_ms", C.c_float), ("tokenize_ms", C.c_float), ("join_ms", C.c_float),
         ("scan_ms", C.c_float), ("encode_ms", C.c_float), ("d2h_ms", C.c_float),
         ("total_ms", C.c_float), ("launches", C.c_uint32), ("fused", C.c_uint32),
-        ("slow_docs", C.c_uint32), ("fused_ctas_per_sm", C.c_uint32),
+        ("slow_docs", C.c_uint32), ("fused_ctas_per_sm", C.c_uint32), ("docs_in_flight_per_sm", C.c_uint32),
     ]
 
 
@@ -122,8 +122,8 @@ SIGNATURES = {
                                            C.c_void_p, C.c_void_p]),
 }
 NOALLOC_MAX_ROWS = 16384
-ABI_VERSION = 2
-PIPELINE_AUTO, PIPELINE_STAGED, PIPELINE_FUSED_GENERIC = 0, 1, 2
+ABI_VERSION = 3
+PIPELINE_AUTO, PIPELINE_STAGED, PIPELINE_FUSED_GENERIC, PIPELINE_FUSED_V1 = 0, 1, 2, 3
 
 _lib = None
 

@@ -145,5 +145,43 @@ def fast_proc_row(row: bytes, shift=0):
                 hash=u64[0], pidkey=u64[1])
 
 
+# ---- k_poll2: lines written as independent jobs -----------------------------------------------
+def p2_node_line(host, row: bytes, sid, shift=0, align=0, jobs=4):
+    out = (C.c_ubyte * 20000)()
+    planned = C.c_uint32()
+    n = lib().hc_p2_node_line(host.encode(), row + b"\0" * 16, len(row), sid, shift, align, jobs, out,
+                              C.byref(planned))
+    line, guards = _line_or_none(n, out)
+    return line, planned.value, guards
+
+
+def p2_busy_line(host, ns, cid, user, pod, prow: bytes, grow: bytes, sid, shift=0, align=0, jobs=4):
+    out = (C.c_ubyte * 20000)()
+    planned = C.c_uint32()
+    n = lib().hc_p2_busy_line(host.encode(), ns.encode(), cid.encode(), user.encode(), pod.encode(),
+                              prow + b"\0" * 16, len(prow), grow + b"\0" * 16, len(grow), sid, shift,
+                              align, jobs, out, C.byref(planned))
+    line, guards = _line_or_none(n, out)
+    return line, planned.value, guards
+
+
+def p2_idle_line(host, ns, cid, user, pod, sid, align=0, jobs=4):
+    out = (C.c_ubyte * 20000)()
+    planned = C.c_uint32()
+    n = lib().hc_p2_idle_line(host.encode(), ns.encode(), cid.encode(), user.encode(), pod.encode(),
+                              0xFFFFFFFF if sid is None else sid, align, jobs, out, C.byref(planned))
+    line, guards = _line_or_none(n, out)
+    return line, planned.value, guards
+
+
+def p2_gpu_row(row: bytes, shift=0):
+    out = (C.c_uint32 * 16)()
+    u64 = (C.c_uint64 * 3)()
+    if not lib().hc_p2_gpu_row(row + b"\0" * 16, len(row), shift, out, u64):
+        return None
+    f = lambda i: row[out[2 * i]:out[2 * i] + out[2 * i + 1]]
+    return dict(key=f(0), util=f(1), mt=f(2), mu=f(3), mf=f(4), hash=u64[0], total=u64[1], used=u64[2])
+
+
 def key_hash_bytes(b: bytes) -> int:
     return lib().hc_key_hash_bytes(b, len(b))

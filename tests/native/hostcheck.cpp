@@ -244,6 +244,109 @@ int hc_fast_proc_row(const uint8_t *row, uint32_t row_len, uint32_t shift, uint3
   return 1;
 }
 
+// ---- k_poll2 (kgm_poll2_leaf.cuh): a line written as 4 or 8 independent jobs, laid out like a
+//      warp's slice: constant area | gpu text window | apps text window | slot | records | stage
+struct P2Mem {
+  std::vector<uint32_t> words;
+  uint32_t tg, ta, slot, grec, prec, stage;
+  uint8_t *bytes() { return reinterpret_cast<uint8_t *>(words.data()); }
+};
+
+static P2Mem p2_make(const uint8_t *gtext, uint32_t glen, uint32_t gshift, const uint8_t *atext, uint32_t alen,
+                     uint32_t ashift, const std::vector<uint8_t> &pool, size_t slot_start, size_t slot_len) {
+  P2Mem m;
+  auto r16 = [](uint32_t v) { return (v + 15u) & ~15u; };
+  m.tg = r16(p2::CA2::BYTES);
+  m.ta = m.tg + r16(gshift + glen) + 48;
+  m.slot = m.ta + r16(ashift + alen) + 48;
+  m.grec = m.slot + r16((uint32_t)slot_len) + 16;
+  m.prec = m.grec + p2::GREC_BYTES;
+  m.stage = m.prec + p2::PREC_BYTES + 16;
+  m.words.assign((m.stage + 3 * MAX_LINE_BYTES) / 4, 0x5a5a5a5au);
+  p2::fill_ca2(m.bytes(), 0u);
+  memcpy(m.bytes() + m.tg + gshift, gtext, glen);
+  memcpy(m.bytes() + m.ta + ashift, atext, alen);
+  memcpy(m.bytes() + m.slot, pool.data() + slot_start, slot_len);
+  return m;
+}
+
+// all jobs of one line, last job first (they must not depend on each other)
+static uint32_t p2_write(P2Mem &m, uint32_t pod, uint32_t jobs, uint32_t rec, uint32_t dst, uint64_t qoff,
+                         uint32_t var) {
+  const uint32_t step = 8u / jobs;
+  for (uint32_t q = jobs; q-- > 0;) p2::compose_job(m.words.data(), 0u, pod, q * step, step, m.slot, rec, dst, qoff);
+  return *reinterpret_cast<const uint16_t *>(m.bytes() + m.slot + p2::SLOT_FIXED) + var;
+}
+
+int hc_p2_node_line(const char *host, const uint8_t *row, uint32_t row_len, uint32_t sid, uint32_t shift,
+                    uint32_t align, uint32_t jobs, uint8_t *out, uint32_t *planned) {
+  std::vector<uint8_t> pool;
+  size_t st = 0, ln = 0;
+  if (!build_node_slot(host, pool, &st, &ln)) return -2;
+  P2Mem m = p2_make(row, row_len, shift, row, 0, 0, pool, st, ln);
+  p2::G2 g;
+  if (!p2::parse_gpu_row2(m.words.data() + m.tg / 4, shift, shift + row_len, g)) return -1;
+  p2::store_grec(m.words.data(), m.tg, m.grec, g, sid);
+  uint32_t var;
+  const uint64_t qoff = p2::measure_line<false>(m.words.data() + m.grec / 4, &var);
+  if (var > 511) return -1;
+  const uint32_t n = p2_write(m, 0u, jobs, m.grec, m.stage + 64 + align, qoff, var);
+  *planned = n;
+  memcpy(out, m.bytes() + m.stage + 64 + align - 8, n + 16);      // 8 guard bytes either side
+  return (int)n;
+}
+
+int hc_p2_busy_line(const char *host, const char *ns, const char *cid, const char *user, const char *pod,
+                    const uint8_t *prow, uint32_t prow_len, const uint8_t *grow, uint32_t grow_len, uint32_t sid,
+                    uint32_t shift, uint32_t align, uint32_t jobs, uint8_t *out, uint32_t *planned) {
+  std::vector<uint8_t> pool;
+  size_t st = 0, ln = 0;
+  if (!build_pod_slot(host, ns, cid, user, pod, pool, &st, &ln)) return -2;
+  const uint32_t ashift = (shift * 7 + 3) & 15;
+  P2Mem m = p2_make(grow, grow_len, shift, prow, prow_len, ashift, pool, st, ln);
+  p2::G2 g;
+  if (!p2::parse_gpu_row2(m.words.data() + m.tg / 4, shift, shift + grow_len, g)) return -1;
+  p2::store_grec(m.words.data(), m.tg, m.grec, g, sid);
+  p2::P2 p;
+  if (!p2::parse_proc_row2(m.words.data() + m.ta / 4, ashift, ashift + prow_len, p)) return -1;
+  p2::store_prec(m.words.data(), m.ta, m.prec, p, m.words.data() + m.grec / 4);
+  uint32_t var;
+  const uint64_t qoff = p2::measure_line<true>(m.words.data() + m.prec / 4, &var);
+  if (var > 511) return -1;
+  const uint32_t n = p2_write(m, 1u, jobs, m.prec, m.stage + 64 + align, qoff, var);
+  *planned = n;
+  memcpy(out, m.bytes() + m.stage + 64 + align - 8, n + 16);
+  return (int)n;
+}
+
+int hc_p2_idle_line(const char *host, const char *ns, const char *cid, const char *user, const char *pod,
+                    uint32_t sid, uint32_t align, uint32_t jobs, uint8_t *out, uint32_t *planned) {
+  std::vector<uint8_t> pool;
+  size_t st = 0, ln = 0;
+  if (!build_pod_slot(host, ns, cid, user, pod, pool, &st, &ln)) return -2;
+  const uint8_t dummy[4] = {0, 0, 0, 0};
+  P2Mem m = p2_make(dummy, 0, 0, dummy, 0, 0, pool, st, ln);
+  p2::store_idle_rec(m.words.data(), 0u, m.prec, sid);
+  uint32_t var;
+  const uint64_t qoff = p2::measure_line<true>(m.words.data() + m.prec / 4, &var);
+  const uint32_t n = p2_write(m, 1u, jobs, m.prec, m.stage + 64 + align, qoff, var);
+  *planned = n;
+  memcpy(out, m.bytes() + m.stage + 64 + align - 8, n + 16);
+  return (int)n;
+}
+
+// the fields parse_gpu_row2 extracts: out = key off/len, util, mt, mu, mf off/len; u64 = hash, total, used
+int hc_p2_gpu_row(const uint8_t *row, uint32_t row_len, uint32_t shift, uint32_t *out, uint64_t *u64out) {
+  std::vector<uint8_t> pool(64, 0);
+  P2Mem m = p2_make(row, row_len, shift, row, 0, 0, pool, 0, 16);
+  p2::G2 g;
+  if (!p2::parse_gpu_row2(m.words.data() + m.tg / 4, shift, shift + row_len, g)) return 0;
+  const fast::Run runs[5] = {g.key, g.util, g.mt, g.mu, g.mf};
+  for (int i = 0; i < 5; ++i) { out[2 * i] = runs[i].off - shift; out[2 * i + 1] = runs[i].len; }
+  u64out[0] = g.hash; u64out[1] = g.total; u64out[2] = g.used;
+  return 1;
+}
+
 uint64_t hc_key_hash_bytes(const uint8_t *p, uint32_t n) { return fast::key_hash_bytes(p, n); }
 
 uint64_t hc_hash_bytes(const uint8_t *p, uint32_t n) {

@@ -26,7 +26,7 @@ def test_library_builds_and_exports_the_declared_abi():
 
 def test_version_strings_and_struct_layout_without_a_gpu():
     lib = _ffi.load()
-    assert lib.kgm_abi_version() == _ffi.ABI_VERSION == 2
+    assert lib.kgm_abi_version() == _ffi.ABI_VERSION == 3
     assert lib.kgm_strerror(0) == b"ok"
     assert lib.kgm_strerror(_ffi.DOC_KEY_ERROR) == b"KeyError"
     assert lib.kgm_strerror(_ffi.DOC_CSV_ERROR) == b"Error"
@@ -36,5 +36,5 @@ def test_version_strings_and_struct_layout_without_a_gpu():
     assert C.sizeof(_ffi.KgmStrings) == 16
     assert C.sizeof(_ffi.KgmBatch) == 56
     assert C.sizeof(_ffi.KgmResult) == 56
-    assert C.sizeof(_ffi.KgmTiming) == 44
+    assert C.sizeof(_ffi.KgmTiming) == 48
     assert C.sizeof(_ffi.KgmFleet) == 8 + 16 + 8 * 3 + 8 + 8 * 3 + 16 * 4 + 8 + 16 + 8 + 16

@@ -287,3 +287,70 @@ def test_fast_lines_are_the_generic_lines_at_every_alignment():
             assert got == want and planned == len(want) and guards
             checked += 1
     assert checked > 1200
+
+
+# ---- k_poll2 (kgm_poll2_leaf.cuh): lines written as 4 or 8 independent jobs -------------------
+def test_p2_gpu_row_values_and_fields():
+    """parse_gpu_row2: same fields as the v1 fast parser, plus int(digits) of the memory cells
+    computed four digits at a time."""
+    rng = random.Random(29)
+    base = [r for r in ROW_POOL if r.startswith("GPU")][:200]
+    rows = base + [_mutate(rng, rng.choice(base)) for _ in range(3000)]
+    rows += ["GPU-a, 1 %%, 2 %%, %d MiB, %d MiB, 3 MiB" % (t, u) for t, u in
+             [(1, 0), (9, 9), (12, 3), (123, 45), (1234, 999), (12345, 1234), (183359, 99999),
+              (10 ** 17 + 7, 10 ** 17 - 1), (99999999, 12345678), (100000001, 1)]]
+    accepted = 0
+    for row in rows:
+        if not row.isascii():
+            continue
+        shift = rng.randrange(16)
+        got, v1 = hc.p2_gpu_row(row.encode(), shift), hc.fast_gpu_row(row.encode(), shift)
+        assert (got is None) == (v1 is None), row
+        if got is None:
+            continue
+        accepted += 1
+        for k in ("key", "util", "mt", "mu", "mf", "hash"):
+            assert got[k] == v1[k], (row, k)
+        assert got["total"] == int(got["mt"]) and got["used"] == int(got["mu"]), row
+    assert accepted > 1200
+
+
+@pytest.mark.parametrize("jobs", [4, 8])
+def test_p2_lines_are_the_generic_lines_at_every_alignment(jobs):
+    """node / busy / idle lines written job by job (last job first) == the byte-wise composer
+    (pinned to the oracle above), at every stage alignment and text shift, with the planned
+    length equal to the written one and no byte touched outside the line."""
+    rng = random.Random(31 + jobs)
+    grows = [r for r in ROW_POOL if r.startswith("GPU")][:60]
+    prows = [r for r in ROW_POOL if not r.startswith("GPU") and r.count(",") == 3][:60]
+    prows += ["34443, python3 train.py --lr 1, %s, 419 MiB" % "GPU-aaaa", "7, a  b, GPU-x, 1 MiB",
+              "123456, /a/very/long/path/to/some/binary/that/goes/on/and/on/python3.11, GPU-x, 40000 MiB"]
+    hosts = ["node-a", "k8s-node-gpu-00012", "n", "None"]
+    checked = 0
+    for _ in range(400):
+        host = rng.choice(hosts)
+        grow, prow = rng.choice(grows), rng.choice(prows)
+        sid = rng.choice([0, 1, 7, 9, 10, 15, 99, 100, 255])
+        shift, align = rng.randrange(16), rng.randrange(16)
+        want, planned_w, n_w = hc.node_line(host, grow.encode(), sid)
+        got, planned, guards = hc.p2_node_line(host, grow.encode(), sid, shift, align, jobs)
+        if got is not None:
+            assert want is not None and got == want and planned == len(want) == planned_w and guards, grow
+            checked += 1
+        else:
+            assert want is None or not hc.fast_gpu_row(grow.encode())
+        ns, cid, user, pod = rng.choice([("ns2", "76a082ecc41d", "q", "jupyter-q-0"),
+                                         ("10007089-name", "16ee8a182726", "alice-bob",
+                                          "turing-gpu-notebook-alice-bob-5d9f-xk2p"), ("-", "c", "-", "-")])
+        want, planned_w, n_w = hc.busy_line(host, ns, cid, user, pod, prow.encode(), grow.encode(), sid)
+        got, planned, guards = hc.p2_busy_line(host, ns, cid, user, pod, prow.encode(), grow.encode(), sid,
+                                               shift, align, jobs)
+        if got is not None:
+            assert want is not None and got == want and planned == len(want) and guards, (prow, grow)
+            checked += 1
+        for s in (sid, None):
+            want, planned_w = hc.idle_line(host, ns, cid, user, pod, s)
+            got, planned, guards = hc.p2_idle_line(host, ns, cid, user, pod, s, align, jobs)
+            assert got == want and planned == len(want) and guards
+            checked += 1
+    assert checked > 1200

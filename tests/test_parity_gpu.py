@@ -23,7 +23,7 @@ UNSUPPORTED_OK = {"err_quoted_first_cell": _ffi.DOC_UNSUPPORTED_QUOTE}
 
 
 PIPELINES = {"fused": _ffi.PIPELINE_AUTO, "staged": _ffi.PIPELINE_STAGED,
-             "fused-generic": _ffi.PIPELINE_FUSED_GENERIC}
+             "fused-generic": _ffi.PIPELINE_FUSED_GENERIC, "fused-v1": _ffi.PIPELINE_FUSED_V1}
 
 
 @pytest.fixture(scope="module", params=list(PIPELINES))
@@ -205,7 +205,7 @@ def test_full_config2_properties_and_sampled_parity(mon):
     else:
         # the clean fleet batch goes through the fast path entirely (or not at all when it is off)
         assert t["launches"] == 1 and t["fused"] == 1
-        assert t["slow_docs"] == (0 if mon.pipeline_name == "fused" else rp.n_docs)
+        assert t["slow_docs"] == (0 if mon.pipeline_name in ("fused", "fused-v1") else rp.n_docs)
         assert t["fused_ctas_per_sm"] in (1, 2)                     # 1 x 7 or 2 x 3/4 teams per SM
 
 

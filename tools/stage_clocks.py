@@ -6,6 +6,8 @@ sys.path[:0] = [ROOT, os.path.join(ROOT, "k8s-gpu-monitor_b200"), os.path.join(R
 from kgm import _ffi, monitor, replay
 from fleet_util import entry_of_snap
 rp = replay.make_replay(seed=0, **replay.CONFIGS["config2"])
+names2 = {1: "windows+rows", 2: "gpu rows", 3: "process rows", 4: "containers+lines", 5: "publish", 6: "slot wait",
+          7: "compose", 8: "look-back+wait", 9: "copy-out"}
 names = {1: "A work", 2: "A wait", 3: "B work", 4: "B wait", 5: "C work", 6: "C wait", 7: "busy entries+wait",
          8: "D lengths", 9: "segments+compose", 10: "look-back+wait", 11: "line_off+copy-out", 12: "last barrier"}
 with monitor.Monitor(0) as mon:
@@ -19,6 +21,14 @@ with monitor.Monitor(0) as mon:
     n = _ffi.load().kgm_debug_stage_clocks(buf)
     print("values", n, "kernel ms", mon.timing()["encode_ms"])
     docs = rp.n_docs * reps
+    if mon.timing()["docs_in_flight_per_sm"] and os.environ.get("KGM_PIPELINE") != "fused-v1":
+        tot = 0
+        for st in range(1, 10):
+            v = buf[st] / docs
+            tot += v
+            print("%-22s %8.0f clk/doc" % (names2[st], v))
+        print("total %8.0f clk/doc  (%d documents in flight per SM)" % (tot, mon.timing()["docs_in_flight_per_sm"]))
+        sys.exit(0)
     for half in (0, 1):
         tot = 0
         for st in range(1, 13):
