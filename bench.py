@@ -255,7 +255,7 @@ def run_kgm_arm(args):
     for v in range(rotate):
         rp, entries = build_workload(args.config, rank * rotate + v)
         mon = monitor.Monitor(local_rank)
-        mon.set_pipeline({"fused": 0, "staged": 1, "fused-generic": 2}[args.pipeline])
+        mon.set_pipeline({"fused": 0, "staged": 1, "fused-generic": 2, "fused-v1": 3, "fused-v2": 4}[args.pipeline])
         mon.load_fleet(entries)
         batch = mon.make_batch(rp.gpu_texts, rp.apps_texts, rp.doc_node, rp.doc_tick, pinned=True)
         mon.upload(batch)
@@ -569,7 +569,7 @@ def main():
     ap.add_argument("--impl", default="kgm", choices=["kgm", "reference"])
     ap.add_argument("--config", default="config2", choices=["config1", "config2", "config3"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--pipeline", default="fused", choices=["fused", "staged", "fused-generic"])
+    ap.add_argument("--pipeline", default="fused", choices=["fused", "staged", "fused-generic", "fused-v1", "fused-v2"])
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

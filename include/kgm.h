@@ -242,8 +242,9 @@ int  kgm_debug_stage_clocks(uint64_t *out64);
 int  kgm_debug_chunk_times(kgm_ctx *ctx, float *text_in_ms, float *kernel_done_ms, uint32_t cap);
 
 /* Which kernels run a batch (no counterpart in the reference; results are identical):
- *   AUTO           one fused single-pass kernel when the batch fits its shared-memory slices,
- *                  the staged kernels otherwise (default)
+ *   AUTO           one fused single-pass kernel when the batch fits its shared-memory slices
+ *                  (k_poll for batches of a few waves, k_poll2 for large ones), the staged
+ *                  kernels otherwise (default)
  *   STAGED         always tokenize -> join -> scan -> encode as four kernels
  *   FUSED_GENERIC  the fused kernel with its fast path switched off: every document takes
  *                  the generic per-byte path inside it (testing)
@@ -251,7 +252,8 @@ int  kgm_debug_chunk_times(kgm_ctx *ctx, float *text_in_ms, float *kernel_done_m
 #define KGM_PIPELINE_AUTO          0
 #define KGM_PIPELINE_STAGED        1
 #define KGM_PIPELINE_FUSED_GENERIC 2
-#define KGM_PIPELINE_FUSED_V1      3   /* the round-1 fused kernel (two-warp teams), kept for comparison */
+#define KGM_PIPELINE_FUSED_V1      3   /* always the team kernel k_poll (two warps per document)            */
+#define KGM_PIPELINE_FUSED_V2      4   /* always the warp kernel k_poll2 (one warp per document)            */
 int  kgm_set_pipeline(kgm_ctx *ctx, int mode);
 
 /* Writes `bytes` of device scratch on the context's stream so that the L2 holds none of

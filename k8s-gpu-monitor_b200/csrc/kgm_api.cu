@@ -126,7 +126,7 @@ struct kgm_ctx {
   uint32_t p2_max_nc = 1, p2_max_slot = 64, p2_max_fixed = 0, p2_max_idle = 0, p2_any = 0;
   std::vector<uint8_t> h_node_fast2;
   bool all_nodes_fast2 = false;
-  uint32_t force_jobs = 0;                 // KGM_POLL2_JOBS=4|8: jobs per line (experiments)
+  uint32_t force_lines = 0;                // KGM_POLL2_LINES=4..32: lines per round the stage is sized for (experiments)
   uint32_t force_warps = 0;                // KGM_POLL2_WARPS: documents in flight per SM (experiments)
   uint32_t force_teams = 0;                // KGM_FUSED_TEAMS=4..8: documents in flight per SM (experiments)
   int reserve_ctas = 0;                    // KGM_RESERVE_CTAS: CTA slots k_poll leaves free (for NCCL kernels)
@@ -245,8 +245,14 @@ int ensure_workspace(kgm_ctx *ctx) {
 }
 
 // The batch goes through the fused kernel unless it was switched off or does not fit.
+// Two fused kernels: k_poll (two-warp teams, 7 - 8 documents in flight per SM, whole document
+// staged) finishes a batch of a few waves sooner; k_poll2 (one warp per document, 12 - 18 in
+// flight) has the higher throughput once a launch runs many waves (measured crossover between
+// the configs[1] batch, 3840 documents, and the configs[2] batch, 40 000: profiles/README.md).
 bool use_poll2(const kgm_ctx *ctx) {
-  return ctx->pipeline != KGM_PIPELINE_STAGED && ctx->pipeline != KGM_PIPELINE_FUSED_V1 && ctx->poll2_ok;
+  if (ctx->pipeline == KGM_PIPELINE_STAGED || ctx->pipeline == KGM_PIPELINE_FUSED_V1 || !ctx->poll2_ok) return false;
+  if (ctx->pipeline == KGM_PIPELINE_FUSED_V2 || !ctx->fused_ok) return true;
+  return ctx->batch.n_docs >= (uint32_t)ctx->sms * 64u;
 }
 bool use_fused(const kgm_ctx *ctx) {
   return use_poll2(ctx) || (ctx->pipeline != KGM_PIPELINE_STAGED && ctx->fused_ok);
@@ -284,7 +290,7 @@ int launch_pipeline(kgm_ctx *ctx) {
     ctx->ticket_next += (unsigned long long)n + (unsigned long long)blocks * wpb;
     if (!ctx->chunk_launch) CU(cudaEventRecord(ctx->ev[EV_SCAN], ctx->stream));
     if (v2) launch_poll2(ctx->batch, ctx->fleet, ctx->work, P, ctx->poll2, blocks, ctx->device, ctx->stream);
-    else launch_poll(ctx->batch, ctx->fleet, ctx->work, P, blocks, ctx->stream);
+    else launch_poll(ctx->batch, ctx->fleet, ctx->work, P, blocks, ctx->device, ctx->stream);
     ctx->last_poll2 = v2;
     if (!ctx->chunk_launch) CU(cudaEventRecord(ctx->ev[EV_ENC], ctx->stream));
     CU(cudaGetLastError());
@@ -304,7 +310,7 @@ int launch_pipeline(kgm_ctx *ctx) {
   CU(cudaEventRecord(ctx->ev[EV_JOIN], ctx->stream));
   launch_scan(ctx->batch, ctx->work, ctx->stream);
   CU(cudaEventRecord(ctx->ev[EV_SCAN], ctx->stream));
-  launch_encode(ctx->batch, ctx->fleet, ctx->work, ctx->sms, ctx->stream);
+  launch_encode(ctx->batch, ctx->fleet, ctx->work, ctx->sms, ctx->device, ctx->stream);
   CU(cudaEventRecord(ctx->ev[EV_ENC], ctx->stream));
   CU(cudaGetLastError());
   return KGM_OK;
@@ -553,7 +559,7 @@ void plan_fused(kgm_ctx *ctx, const kgm_batch *b, uint64_t max_g, uint64_t max_a
 // slots and the stage of a round, which double as the parse-time tables (row starts, join
 // words) and as the generic path's scratch.  Text windows are clamped so that at least a few
 // documents stay in flight per SM; a document that does not fit takes the generic path.
-bool poll2_layout(kgm_ctx *ctx, uint32_t jshift, uint64_t max_g, uint64_t max_a, Poll2Params *out) {
+bool poll2_layout(kgm_ctx *ctx, uint32_t lines, uint64_t max_g, uint64_t max_a, Poll2Params *out) {
   auto r16 = [](uint64_t v) { return (uint32_t)((v + 15) & ~15ull); };
   const uint32_t ca = (p2::CA2::BYTES + 15u) & ~15u;
   const uint32_t dyn_max = 232448u - ca;
@@ -561,8 +567,6 @@ bool poll2_layout(kgm_ctx *ctx, uint32_t jshift, uint64_t max_g, uint64_t max_a,
   Poll2Params Q{};
   for (int round = 0; round < 8; ++round) {
     Q = Poll2Params{};
-    Q.jshift = jshift;
-    const uint32_t R = 32u >> jshift;
     Q.cap_g = r16(g + 30) + 48;
     Q.cap_a = r16(a + 30) + 48;
     // rows of the two texts are rarely shorter than 80 / 72 bytes (uuid 40 + five cells; pid, name,
@@ -573,10 +577,8 @@ bool poll2_layout(kgm_ctx *ctx, uint32_t jshift, uint64_t max_g, uint64_t max_a,
     Q.cap_rec = Q.cap_np + cap_idle;
     Q.cap_c = std::min(512u, std::max(1u, ctx->p2_max_nc));
     Q.cap_lines = Q.cap_ng + Q.cap_np + cap_idle;
-    Q.slot_bytes = r16(std::max(ctx->p2_max_slot, 64u));
-    Q.slot_magic = (uint32_t)(((1ull << 32) + (Q.slot_bytes >> 4) - 1) / (Q.slot_bytes >> 4));
     const uint32_t est_line = ctx->p2_max_fixed + 80u;         // constant bytes + typical variable cells
-    Q.stage_bytes = r16((uint64_t)R * est_line + 64);
+    Q.stage_bytes = r16((uint64_t)lines * est_line + 64);
     uint32_t o = 0;
     Q.off_tg = o; o += Q.cap_g;
     Q.off_ta = o; o += Q.cap_a;
@@ -587,25 +589,22 @@ bool poll2_layout(kgm_ctx *ctx, uint32_t jshift, uint64_t max_g, uint64_t max_a,
     Q.off_plan = o; o += r16(2ull * Q.cap_lines);
     Q.off_loff = o; o += r16(4ull * (Q.cap_lines + 1));
     Q.off_toff = o; o += r16(4ull * Q.cap_lines);
-    Q.off_qoff = o; o += r16(8ull * Q.cap_lines);
-    Q.off_slots = o;
-    // parse-time tables and the generic path's scratch share the slots + stage
+    Q.off_stage = o;
+    // parse-time tables and the generic path's scratch share the stage
     uint32_t t = o;
     Q.off_gstart = t; t += r16(2ull * (Q.cap_ng + 2));
     Q.off_pstart = t; t += r16(2ull * (Q.cap_np + 2));
     Q.off_cp = t; t += r16(4ull * Q.cap_np);
     Q.off_digest = t; t += r16(4ull * Q.cap_np);
     const uint32_t need = std::max<uint32_t>(t - o, r16(12ull * ctx->fleet.max_nc + 16));
-    o += R * Q.slot_bytes;
-    Q.off_stage = o;
-    if (R * Q.slot_bytes + Q.stage_bytes < need) Q.stage_bytes = need - R * Q.slot_bytes;
+    Q.stage_bytes = std::max(Q.stage_bytes, need);
     o += Q.stage_bytes;
     Q.slice_bytes = r16(o);
     if (Q.slice_bytes * 4u <= dyn_max) break;                  // at least 4 documents in flight per SM
     if (a > 4096) a = a * 3 / 4; else if (g > 1024) g = g * 3 / 4; else return false;
   }
   if (Q.slice_bytes * 4u > dyn_max) return false;
-  Q.warps = std::min<uint32_t>(26u, dyn_max / Q.slice_bytes);
+  Q.warps = std::min<uint32_t>(20u, dyn_max / Q.slice_bytes);
   if (ctx->force_warps) Q.warps = std::max(1u, std::min(Q.warps, ctx->force_warps));
   *out = Q;
   return true;
@@ -614,15 +613,11 @@ bool poll2_layout(kgm_ctx *ctx, uint32_t jshift, uint64_t max_g, uint64_t max_a,
 void plan_poll2(kgm_ctx *ctx, const kgm_batch *b, uint64_t max_g, uint64_t max_a) {
   ctx->poll2_ok = false;
   if (b->n_docs == 0 || !ctx->p2_any) return;
-  // 4 jobs per line (8 lines per round) unless 8 jobs per line (smaller rounds, smaller slices)
-  // puts a fifth more documents in flight
-  Poll2Params q4{}, q8{};
-  const bool ok4 = poll2_layout(ctx, 2, max_g, max_a, &q4), ok8 = poll2_layout(ctx, 3, max_g, max_a, &q8);
-  if (!ok4 && !ok8) return;
-  bool take8 = !ok4 || (ok8 && q8.warps * 5u >= q4.warps * 6u);
-  if (ctx->force_jobs == 4 && ok4) take8 = false;
-  if (ctx->force_jobs == 8 && ok8) take8 = true;
-  ctx->poll2 = take8 ? q8 : q4;
+  // lines per round: the stage holds that many typical lines (one lane writes one line)
+  const uint32_t lines = ctx->force_lines ? ctx->force_lines : 16u;
+  Poll2Params q{};
+  if (!poll2_layout(ctx, lines, max_g, max_a, &q)) return;
+  ctx->poll2 = q;
   ctx->poll2_ok = true;
 }
 
@@ -956,12 +951,13 @@ int kgm_create(kgm_ctx **out, int device) {
   if (const char *env = getenv("KGM_FUSED_TEAMS")) {
     ctx->force_teams = (uint32_t)std::max(0, std::min(atoi(env), 8));
   }
-  if (const char *env = getenv("KGM_POLL2_JOBS")) ctx->force_jobs = (uint32_t)atoi(env);
-  if (const char *env = getenv("KGM_POLL2_WARPS")) ctx->force_warps = (uint32_t)std::max(0, std::min(atoi(env), 26));
+  if (const char *env = getenv("KGM_POLL2_LINES")) ctx->force_lines = (uint32_t)std::max(4, std::min(atoi(env), 32));
+  if (const char *env = getenv("KGM_POLL2_WARPS")) ctx->force_warps = (uint32_t)std::max(0, std::min(atoi(env), 20));
   if (const char *env = getenv("KGM_PIPELINE")) {
     if (!strcmp(env, "staged")) ctx->pipeline = KGM_PIPELINE_STAGED;
     else if (!strcmp(env, "fused-generic")) ctx->pipeline = KGM_PIPELINE_FUSED_GENERIC;
     else if (!strcmp(env, "fused-v1")) ctx->pipeline = KGM_PIPELINE_FUSED_V1;
+    else if (!strcmp(env, "fused-v2")) ctx->pipeline = KGM_PIPELINE_FUSED_V2;
   }
   *out = ctx;
   return KGM_OK;
@@ -1515,7 +1511,7 @@ int kgm_debug_chunk_times(kgm_ctx *ctx, float *text_in_ms, float *kernel_done_ms
 }
 
 int kgm_set_pipeline(kgm_ctx *ctx, int mode) {
-  if (!ctx || mode < KGM_PIPELINE_AUTO || mode > KGM_PIPELINE_FUSED_V1) return KGM_E_INVALID;
+  if (!ctx || mode < KGM_PIPELINE_AUTO || mode > KGM_PIPELINE_FUSED_V2) return KGM_E_INVALID;
   ctx->pipeline = mode;
   return KGM_OK;
 }

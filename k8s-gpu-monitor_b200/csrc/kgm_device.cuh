@@ -117,17 +117,13 @@ struct Poll2Params {
   uint32_t cap_rec;              // process rows + idle pseudo-rows
   uint32_t cap_c;                // containers per node
   uint32_t cap_lines;            // lines per document
-  uint32_t slot_bytes;           // template slot (multiple of 16)
-  uint32_t slot_magic;           // ceil(2^32 / (slot_bytes / 16)): x / (slot_bytes / 16) == umulhi(x, magic) for x < 2^16
   uint32_t stage_bytes;          // incl. 64 bytes of slack
-  uint32_t jshift;               // 2: 4 jobs per line, 8 lines per round; 3: 8 jobs per line, 4 lines per round
-  uint32_t off_tg, off_ta, off_grec, off_prec, off_cnt, off_cstart, off_plan, off_loff, off_toff, off_qoff,
-      off_slots, off_stage;
-  uint32_t off_gstart, off_pstart, off_cp, off_digest;   // parse-time tables, inside [off_slots, slice end)
+  uint32_t off_tg, off_ta, off_grec, off_prec, off_cnt, off_cstart, off_plan, off_loff, off_toff, off_stage;
+  uint32_t off_gstart, off_pstart, off_cp, off_digest;   // parse-time tables, inside the stage
 };
 
 void launch_poll(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P, int blocks,
-                 cudaStream_t s);
+                 int device, cudaStream_t s);
 void launch_poll2(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P, const Poll2Params &Q,
                   int blocks, int device, cudaStream_t s);
 int poll2_smem_bytes(const Poll2Params &Q);
@@ -137,7 +133,7 @@ int debug_stage_clocks(unsigned long long *out64);   // 0 unless built with -DKG
 void launch_tokenize(const BatchDev &b, const WorkDev &w, int sms, cudaStream_t s);
 void launch_join(const BatchDev &b, const FleetDev &f, const WorkDev &w, int sms, cudaStream_t s);
 void launch_scan(const BatchDev &b, const WorkDev &w, cudaStream_t s);
-void launch_encode(const BatchDev &b, const FleetDev &f, const WorkDev &w, int sms, cudaStream_t s);
+void launch_encode(const BatchDev &b, const FleetDev &f, const WorkDev &w, int sms, int device, cudaStream_t s);
 void launch_flush(uint8_t *buf, uint64_t bytes, int sms, cudaStream_t s);
 int encode_smem_bytes();
 

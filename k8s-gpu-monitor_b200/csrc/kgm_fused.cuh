@@ -91,7 +91,7 @@ __device__ __forceinline__ ScanWords scan_wait(const unsigned long long *st, uin
                                                bool need_inc) {
   const uint64_t VAL = (1ull << 46) - 1ull;
   // a waiting lane shares its scheduler with warps that have work: back off quickly
-  for (uint32_t ns = 128;; ns = min(ns * 2u, 4096u)) {
+  for (uint32_t ns = 20;; ns = min(ns + 20u, 200u)) {
     const uint64_t w0 = ld_acquire(st);
     const uint64_t t0 = w0 & ~VAL;
     if (t0 == inc || (!need_inc && t0 == agg)) {
@@ -782,13 +782,14 @@ int debug_stage_clocks(unsigned long long *out64) {
 int poll_smem_bytes(const FusedParams &P) { return (int)(CONST_PAD + P.teams * P.warp_bytes); }
 
 void launch_poll(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P, int blocks,
-                 cudaStream_t s) {
-  static int attr_bytes = -1;                        // (one attribute for all contexts of the process)
-  if (poll_smem_bytes(P) > attr_bytes) {
-    cudaFuncSetAttribute(k_poll, cudaFuncAttributeMaxDynamicSharedMemorySize, poll_smem_bytes(P));
-    attr_bytes = poll_smem_bytes(P);
+                 int device, cudaStream_t s) {
+  static int attr_bytes[64];                         // the shared-memory opt-in is per device
+  const int need = poll_smem_bytes(P);
+  if (device < 0 || device >= 64 || need > attr_bytes[device]) {
+    cudaFuncSetAttribute(k_poll, cudaFuncAttributeMaxDynamicSharedMemorySize, need);
+    if (device >= 0 && device < 64) attr_bytes[device] = need;
   }
-  k_poll<<<blocks, 64 * P.teams, poll_smem_bytes(P), s>>>(b, f, w, P);
+  k_poll<<<blocks, 64 * P.teams, need, s>>>(b, f, w, P);
 }
 
 }  // namespace kgm

@@ -730,11 +730,11 @@ void launch_scan(const BatchDev &b, const WorkDev &w, cudaStream_t s) {
 
 int encode_smem_bytes() { return (int)STAGE_BYTES + 16; }
 
-void launch_encode(const BatchDev &b, const FleetDev &f, const WorkDev &w, int sms, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
+void launch_encode(const BatchDev &b, const FleetDev &f, const WorkDev &w, int sms, int device, cudaStream_t s) {
+  static bool attr_set[64];                          // the shared-memory opt-in is per device
+  if (device < 0 || device >= 64 || !attr_set[device]) {
     cudaFuncSetAttribute(k_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, encode_smem_bytes());
-    attr_set = true;
+    if (device >= 0 && device < 64) attr_set[device] = true;
   }
   k_encode<<<sms * 4, ENC_THREADS, encode_smem_bytes(), s>>>(b, f, w);
 }

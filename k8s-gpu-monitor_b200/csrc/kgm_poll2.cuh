@@ -3,19 +3,20 @@
 // uses).
 //
 // Documents are handed out in batch order by a ticket counter.  A regular document lives in its
-// warp's slice of shared memory (about 10 KB, so that 20 - 26 documents are in flight per SM):
+// warp's slice of shared memory (12 - 18 KB, 12 - 18 documents in flight per SM):
 //   text windows  <- cp.async of the two nvidia-smi texts (16-byte units)     (gpu.py:104-116)
 //   rows          <- SWAR line-feed scan; one lane per row: cells, digit runs, keys, repr(mem_util)
 //   join          <- uuid -> short id against the gpu rows, pid -> container probe of the
 //                    HBM-resident table, container-major placement          (gpu.py:119-128,151,172-178)
 //   records       <- per row the run words of its variable cells; per line: record, template
-//                    slot, length, variable bytes in front of every job boundary
+//                    slot, length
 //   device-wide exclusive scan over documents by decoupled look-back (kgm_fused.cuh)
-//   rounds        <- 4 or 8 lines at a time: their template slots arrive by cp.async (the next
-//                    round's while this one is copied out), every line is written by 8 or 4
-//                    lanes (jobs = fixed ranges of its segments) into the stage, the warp streams
-//                    the stage out with aligned 16-byte stores, realigned to the document's
-//                    position in the output                                 (gpu.py:136-143,206-216,240-250)
+//   rounds        <- up to 32 lines at a time, one lane per line: every lane streams its line's
+//                    segments (template pieces straight from the slot pool in global memory with
+//                    16-byte loads, cells from the text windows) through a pending word into the
+//                    stage, so all lanes run the same segment sequence; the warp then streams the
+//                    stage out with aligned 16-byte stores, realigned to the document's position
+//                    in the output                                          (gpu.py:136-143,206-216,240-250)
 // A document the fast path declines (any raise point of the reference, unusual bytes, duplicate
 // keys, sizes beyond the slice) is re-done from scratch by the generic per-byte code, out of
 // line, and joins the same look-back chain: same bytes either way.
@@ -28,7 +29,7 @@ namespace {
 
 using namespace p2;
 
-constexpr int P2_MAX_THREADS = 832;                  // 26 warps x 78 registers
+constexpr int P2_MAX_THREADS = 640;                  // 20 warps x 102 registers
 
 __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void *g) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(g) : "memory");
@@ -36,7 +37,7 @@ __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void *g) {
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 struct P2Slice {                                     // byte offsets from the CTA's shared memory base
-  uint32_t tg, ta, grec, prec, cnt, cstart, plan, loff, toff, qoff, slots, stage, gstart, pstart, cp, digest;
+  uint32_t tg, ta, grec, prec, cnt, cstart, plan, loff, toff, stage, gstart, pstart, cp, digest;
 };
 
 // The 16-byte aligned window covering text[lo, hi) -> shared memory, asynchronously.
@@ -207,15 +208,11 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
   // ---- per line: record, slot, length, variable bytes in front of the job boundaries ----
   uint16_t *plan = reinterpret_cast<uint16_t *>(Sb + sl.plan);
   uint32_t *loff = S + (sl.loff >> 2), *toff = S + (sl.toff >> 2);
-  uint64_t *qoff = reinterpret_cast<uint64_t *>(Sb + sl.qoff);
   bool too_long = false;
   if (l < ng) {                                      // node lines (gpu.py:132-146)
-    uint32_t var;
-    qoff[l] = measure_line<false>(grec + GREC_WORDS * l, &var);
     plan[l] = (uint16_t)((KIND_NODE << 14) | l);
     toff[l] = f.nslot_off[n];
-    loff[l] = f.node_fixed[n] + 1u + var;
-    too_long |= var > 511u;
+    loff[l] = f.node_fixed[n] + 1u + line_var_bytes<false>(grec + GREC_WORDS * l);
   }
   for (uint32_t c = l; c < nc; c += 32) {            // idle containers: one line per visible uuid (gpu.py:221-250)
     const uint32_t cw = cnt[c];
@@ -236,24 +233,18 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
       }
       const uint32_t ir = np + (cw & 0x7fffu) + v, idx = ng + cstart[c] + v;
       store_idle_rec(S, 0u, sl.prec + PREC_BYTES * ir, sid);
-      const uint32_t *q = prec + PREC_WORDS * ir;
-      uint32_t var;
-      qoff[idx] = measure_line<true>(q, &var);
       plan[idx] = (uint16_t)((KIND_IDLE << 14) | ir);
       toff[idx] = f.tslot_off[gc];
-      loff[idx] = f.cont_fixed[gc] + 1u + var;
+      loff[idx] = f.cont_fixed[gc] + 1u + line_var_bytes<true>(prec + PREC_WORDS * ir);
     }
   }
   for (uint32_t r = l; r < np; r += 32) {            // busy lines (gpu.py:190-219)
     const uint32_t c = (cp[r] >> 16) & 0x7fffu;
     if (c == CP_NONE) continue;
     const uint32_t gc = cb + c, idx = ng + cstart[c] + (cp[r] & 0xffffu);
-    uint32_t var;
-    qoff[idx] = measure_line<true>(prec + PREC_WORDS * r, &var);
     plan[idx] = (uint16_t)((KIND_BUSY << 14) | r);
     toff[idx] = f.tslot_off[gc];
-    loff[idx] = f.cont_fixed[gc] + 1u + var;
-    too_long |= var > 511u;
+    loff[idx] = f.cont_fixed[gc] + 1u + line_var_bytes<true>(prec + PREC_WORDS * r);
   }
   __syncwarp();
   // lengths -> offsets inside the document
@@ -275,35 +266,27 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
   scan_publish(P, d, b.n_docs, nl, nb);
   STAGE_MARK(5);                                     // publish (block aggregators: + their look-back)
 
-  const uint32_t jshift = Q.jshift, R = 32u >> jshift, CH = Q.slot_bytes >> 4;
-  auto issue_slots = [&](uint32_t from) {            // slots of the lines [from, from + R)
-    const uint32_t cntl = min(R, nl - from), total = cntl * CH;
-    for (uint32_t x = l; x < total; x += 32) {
-      const uint32_t s = __umulhi(x, Q.slot_magic), c = x - s * CH;      // x / CH
-      cp_async16(s0 + sl.slots + s * Q.slot_bytes + 16u * c, f.slot_pool + 16ull * toff[from + s] + 16u * c);
-    }
-  };
   uint64_t line0 = 0, byte0 = 0;
   bool resolved = false, fits_out = true;
-  if (nl) issue_slots(0);
   uint32_t i0 = 0;
   do {
-    uint32_t i1 = min(nl, i0 + R), r_lo = 0;
+    // a round: up to 32 lines of one kind (the node lines come first) whose bytes fit the stage
+    uint32_t i1 = min(i0 < ng ? ng : nl, i0 + 32u), r_lo = 0;
     if (nl) {
       r_lo = loff[i0];
       while (i1 > i0 + 1 && loff[i1] - r_lo + 64u > Q.stage_bytes) --i1;
-      cp_async_wait_all();
-      __syncwarp();
-      STAGE_MARK(6);                                 // waiting for the round's slots
-      const uint32_t s = l >> jshift, i = i0 + s;
+      STAGE_MARK(6);
+      const uint32_t i = i0 + l;
+      LineWriter lw;
+      lw.fill = 0;
       if (i < i1) {
         const uint32_t pl = plan[i], pod = (pl >> 14) != KIND_NODE ? 1u : 0u, ref = pl & 0x3fffu;
-        compose_job(S, 0u, pod, (l & ((1u << jshift) - 1u)) << (3u - jshift), 1u << (3u - jshift),
-                    sl.slots + s * Q.slot_bytes, pod ? sl.prec + PREC_BYTES * ref : sl.grec + GREC_BYTES * ref,
-                    sl.stage + (loff[i] - r_lo), qoff[i]);
+        lw = compose_line(S, 0u, pod, f.slot_pool + 16ull * toff[i],
+                          pod ? sl.prec + PREC_BYTES * ref : sl.grec + GREC_BYTES * ref, sl.stage + (loff[i] - r_lo));
       }
       __syncwarp();
-      if (i1 < nl) issue_slots(i1);                  // arrives while this round is copied out
+      if (i < i1) lw_finish(lw, i + 1 < i1);
+      __syncwarp();
       STAGE_MARK(7);                                 // compose
     }
     if (!resolved) {
@@ -357,8 +340,6 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
     __syncwarp();                                    // the stage may be overwritten
     STAGE_MARK(9);                                   // copy-out
   } while (i0 < nl);
-  cp_async_wait_all();                               // (a break above may leave copies in flight)
-  __syncwarp();
   return true;
 }
 
@@ -417,7 +398,7 @@ k_poll2(BatchDev b, FleetDev f, WorkDev w, FusedParams P, Poll2Params Q) {
   P2Slice sl;
   sl.tg = base + Q.off_tg; sl.ta = base + Q.off_ta; sl.grec = base + Q.off_grec; sl.prec = base + Q.off_prec;
   sl.cnt = base + Q.off_cnt; sl.cstart = base + Q.off_cstart; sl.plan = base + Q.off_plan; sl.loff = base + Q.off_loff;
-  sl.toff = base + Q.off_toff; sl.qoff = base + Q.off_qoff; sl.slots = base + Q.off_slots; sl.stage = base + Q.off_stage;
+  sl.toff = base + Q.off_toff; sl.stage = base + Q.off_stage;
   sl.gstart = base + Q.off_gstart; sl.pstart = base + Q.off_pstart; sl.cp = base + Q.off_cp; sl.digest = base + Q.off_digest;
   const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(S);
 
@@ -430,7 +411,7 @@ k_poll2(BatchDev b, FleetDev f, WorkDev w, FusedParams P, Poll2Params Q) {
     if (P.allow_fast && p2_fast_doc(d, b, f, w, P, Q, S, s0, sl)) continue;
     cp_async_wait_all();
     __syncwarp();
-    p2_slow_doc(d, b, f, w, P, S + (sl.slots >> 2));
+    p2_slow_doc(d, b, f, w, P, S + (sl.stage >> 2));
   }
 }
 

@@ -11,13 +11,13 @@
 //   record     the run words of one output line's variable cells: 16 words per --query-gpu row
 //              (GREC_*), 8 words per --query-compute-apps row or idle pseudo-row (PREC_*)
 //   slot       the constant pieces of one node's / one container's line template, built once by
-//              kgm_load_fleet: 48-byte header (8 run words relative to the slot start, the
-//              constant-byte prefix at every job boundary, the constant byte count of a line)
-//              followed by the piece bytes
+//              kgm_load_fleet and read from global memory: 48-byte header (8 run words relative
+//              to the slot start, the constant byte count of a line), then the piece bytes, every
+//              piece starting on a 16-byte boundary
 //   segment    a line is a fixed sequence of segments, each a run taken from the slot ('T'), from
 //              the table of constant strings ('K') or from the line's record ('R')
-//   job        a contiguous range of segments of one line, written by one lane; a line is cut
-//              into 8 jobs at fixed segment indices (or 4, each two of those)
+//   line writer  one lane writes one line: it streams the segments' bytes through a pending word
+//              and stores aligned words only, so all lanes of a warp run the same segment sequence
 #pragma once
 #include <stdint.h>
 
@@ -27,6 +27,10 @@ namespace kgm {
 namespace p2 {
 
 using namespace fast;
+
+#if !defined(__CUDACC__)
+struct alignas(16) uint4 { uint32_t x, y, z, w; };   // (host build of the leaf functions)
+#endif
 
 constexpr uint32_t KIND_NODE = 0, KIND_BUSY = 1, KIND_IDLE = 2;
 
@@ -79,22 +83,6 @@ KGM_HD constexpr uint32_t seg_pod(int k) {
        : k == 13 ? SEG_K | K_GPU_ID_V : k == 14 ? SEG_R | PREC_SID : k == 15 ? SEG_T | 4
        : k == 16 ? SEG_R | PREC_UTIL : k == 17 ? SEG_K | K_USED_MEMORY : k == 18 ? SEG_R | PREC_MEM : SEG_K | K_NL;
 }
-// job boundaries: job q of 8 covers segments [jb8(q), jb8(q+1)); with 4 jobs per line job q covers
-// the jobs 2q and 2q+1 of 8
-// (equal segment counts per job of 4: the lanes of a round then meet pieces of similar length at
-// the same step -- step t of a pod line's four jobs copies segments t, 5+t, 10+t, 15+t)
-KGM_HD constexpr uint32_t jb8_node(int q) {
-  return q == 0 ? 0 : q == 1 ? 2 : q == 2 ? 4 : q == 3 ? 6 : q == 4 ? 8 : q == 5 ? 10 : q == 6 ? 12 : q == 7 ? 14 : 15;
-}
-KGM_HD constexpr uint32_t jb8_pod(int q) {
-  return q == 0 ? 0 : q == 1 ? 3 : q == 2 ? 5 : q == 3 ? 8 : q == 4 ? 10 : q == 5 ? 13 : q == 6 ? 15 : q == 7 ? 18 : 20;
-}
-KGM_HD constexpr uint64_t jb8_pack(bool pod) {                           // 9 x 5 bits
-  uint64_t v = 0;
-  for (int q = 0; q <= 8; ++q) v |= (uint64_t)(pod ? jb8_pod(q) : jb8_node(q)) << (5 * q);
-  return v;
-}
-
 // The constant area is filled in three independent parts (the kernel gives them to different
 // threads; the area must be zeroed first).  `abs0` = its byte offset in the word array that
 // run words refer to.
@@ -151,7 +139,6 @@ KGM_HD uint32_t sid_run(uint32_t abs0, uint32_t sid) {                   // '%s'
 
 // ---- slots -------------------------------------------------------------------------------------
 constexpr uint32_t SLOT_HEADER = 48;
-constexpr uint32_t SLOT_CPRE = 32;           // 7 x u16: constant bytes in front of job q+1 of 8
 constexpr uint32_t SLOT_FIXED = 46;          // u16: constant bytes of a line (incl. '\n')
 
 // lengths of the 'K' strings (the host needs them for the slots' constant-byte prefixes)
@@ -160,58 +147,147 @@ KGM_HD constexpr uint32_t k_len(uint32_t idx) {
        : idx == K_NL || idx == K_DASH || idx == K_ZERO ? 1u : idx == K_NONE ? 4u : idx == K_EMPTY ? 0u : 10u;
 }
 
-// ---- measuring a line: its variable bytes in front of every job boundary ------------------------
-// 7 x 9 bits (a line whose variable cells exceed 511 bytes is left to the generic path).  `r`
-// = the record's run words.  *total receives all variable bytes of the line.
+// ---- measuring a line: the bytes of its variable cells -----------------------------------------
 template <bool POD>
-KGM_HD uint64_t measure_line(const uint32_t *r, uint32_t *total) {
+KGM_HD uint32_t line_var_bytes(const uint32_t *r) {
   uint32_t acc = 0;
-  uint64_t packed = 0;
   constexpr int NS = POD ? (int)POD_SEGS : (int)NODE_SEGS;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
   for (int k = 0; k < NS; ++k) {
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-    for (int q = 1; q < 8; ++q)
-      if ((POD ? jb8_pod(q) : jb8_node(q)) == (uint32_t)k) packed |= (uint64_t)acc << (9 * (q - 1));
     const uint32_t e = POD ? seg_pod(k) : seg_node(k);
     if ((e >> 6) == 2u) acc += rw_len(r[e & 63u]);
   }
-  *total = acc;
-  return packed;
+  return acc;
 }
 
 // ---- composing --------------------------------------------------------------------------------
-// Writes the segments of job `q8 .. q8 + nq8` (of 8) of one line into the word array B.
-//   ca      byte offset of the constant area (CA2) in B
-//   tmpl    byte offset of the line's slot in B
-//   rec     byte offset of the line's record in B
-//   dst     byte offset of the line's first byte in B
-//   qoff    measure_line() of the line
-// Only bytes of the job's own segments are written (byte stores at segment ends), so the jobs of
-// a line, and neighbouring lines, can be written by different lanes.
-KGM_HD void compose_job(uint32_t *B, uint32_t ca, uint32_t pod, uint32_t q8, uint32_t nq8, uint32_t tmpl,
-                        uint32_t rec, uint32_t dst, uint64_t qoff) {
+// A lane writes its line front to back.  The bytes not yet stored (fewer than 4) wait in `pend`,
+// low byte first; only whole aligned words are stored.  A line that starts inside a word stores
+// that word with zeros in the bytes of its predecessor; the predecessor's last bytes are OR-ed
+// into it afterwards (lw_finish), when every lane of the round has written its words.
+struct LineWriter {
+  uint32_t *d;        // next aligned word of the destination
+  uint32_t pend;      // pending bytes, low byte first; bytes >= fill are zero
+  uint32_t fill;      // 0..3
+};
+KGM_HD uint32_t shl8(uint32_t v, uint32_t nbytes) { return nbytes >= 4u ? 0u : v << (8u * nbytes); }
+KGM_HD uint32_t shr8(uint32_t v, uint32_t nbytes) { return nbytes >= 4u ? 0u : v >> (8u * nbytes); }
+
+// r bytes (1..3), the low bytes of `cur` (its other bytes zero)
+KGM_HD void lw_tail(LineWriter &w, uint32_t cur, uint32_t r) {
+  const uint32_t x = w.pend | shl8(cur, w.fill), total = w.fill + r;
+  if (total >= 4u) {
+    *w.d++ = x;
+    w.pend = shr8(cur, 4u - w.fill);
+    w.fill = total - 4u;
+  } else {
+    w.pend = x;
+    w.fill = total;
+  }
+}
+// n bytes starting at byte `a` (0..3) of the aligned word array src[]; reads src[0 .. (a+n+3)/4]
+KGM_HD void lw_put(LineWriter &w, const uint32_t *src, uint32_t a, uint32_t n) {
+  const uint32_t sa = 8u * a, full = n >> 2;
+  uint32_t lo = src[0];
+  if (full) {
+    // whole words: the stream word (source realigned) goes out behind the pending bytes
+    const uint32_t sh = 8u * w.fill;
+    uint32_t prev = shl8(w.pend, 4u - w.fill);       // pending bytes at the top of `prev`
+    for (uint32_t j = 0; j < full; ++j) {
+      const uint32_t hi = src[j + 1];
+      const uint32_t cur = funnel_r(lo, hi, sa);
+#if defined(__CUDA_ARCH__)
+      w.d[j] = __funnelshift_l(prev, cur, sh);
+#else
+      w.d[j] = sh ? (prev >> (32u - sh)) | (cur << sh) : cur;
+#endif
+      prev = cur;
+      lo = hi;
+    }
+    w.d += full;
+    w.pend = shr8(prev, 4u - w.fill);
+  }
+  const uint32_t r = n & 3u;
+  if (r) lw_tail(w, funnel_r(lo, src[full + 1], sa) & low_mask(r), r);
+}
+// n bytes of a slot piece: `g` is 16-byte aligned, the piece starts at its first byte and is
+// padded to a multiple of 16 bytes
+KGM_HD void lw_put_piece(LineWriter &w, const uint4 *g, uint32_t n) {
+  const uint32_t sh = 8u * w.fill;
+  uint32_t prev = shl8(w.pend, 4u - w.fill);
+  uint32_t *d = w.d;
+  uint32_t left = n;
+  auto word = [&](uint32_t cur) {
+#if defined(__CUDA_ARCH__)
+    *d++ = __funnelshift_l(prev, cur, sh);
+#else
+    *d++ = sh ? (prev >> (32u - sh)) | (cur << sh) : cur;
+#endif
+    prev = cur;
+  };
+  for (; left >= 16u; left -= 16u, ++g) {
+#if defined(__CUDA_ARCH__)
+    const uint4 v = __ldg(g);
+#else
+    const uint4 v = *g;
+#endif
+    word(v.x); word(v.y); word(v.z); word(v.w);
+  }
+  uint32_t last = 0;
+  if (left) {
+#if defined(__CUDA_ARCH__)
+    const uint4 v = __ldg(g);
+#else
+    const uint4 v = *g;
+#endif
+    const uint32_t fullw = left >> 2;
+    if (fullw > 0) word(v.x);
+    if (fullw > 1) word(v.y);
+    if (fullw > 2) word(v.z);
+    last = fullw == 0 ? v.x : fullw == 1 ? v.y : fullw == 2 ? v.z : v.w;
+  }
+  w.d = d;
+  w.pend = shr8(prev, 4u - w.fill);
+  const uint32_t r = left & 3u;
+  if (r) lw_tail(w, last & low_mask(r), r);
+}
+
+// Writes one line at byte offset `dst` of the word array B.  `ca` = byte offset of the constant
+// area (CA2) in B, `slot` = the line's template slot (global memory), `rec` = byte offset of its
+// record in B.  Returns the writer: its pending bytes still have to be stored (lw_finish).
+KGM_HD LineWriter compose_line(uint32_t *B, uint32_t ca, uint32_t pod, const uint8_t *slot, uint32_t rec,
+                               uint32_t dst) {
   const uint8_t *Bb = reinterpret_cast<const uint8_t *>(B);
-  const uint64_t pack = pod ? jb8_pack(true) : jb8_pack(false);
-  const uint32_t k0 = (uint32_t)(pack >> (5u * q8)) & 31u, k1 = (uint32_t)(pack >> (5u * (q8 + nq8))) & 31u;
-  uint32_t at = dst;
-  if (q8) {
-    at += *reinterpret_cast<const uint16_t *>(Bb + tmpl + SLOT_CPRE + 2u * (q8 - 1u));
-    at += (uint32_t)(qoff >> (9u * (q8 - 1u))) & 511u;
-  }
   const uint8_t *st = Bb + ca + CA2::SEGTAB + (pod ? 32u : 0u);
-  for (uint32_t k = k0; k < k1; ++k) {
+  const uint32_t *sw = reinterpret_cast<const uint32_t *>(slot);
+  const uint32_t nseg = pod ? POD_SEGS : NODE_SEGS;
+  LineWriter w;
+  w.d = B + (dst >> 2);
+  w.fill = dst & 3u;
+  w.pend = 0;
+  for (uint32_t k = 0; k < nseg; ++k) {
     const uint32_t e = st[k], type = e >> 6;
-    const uint32_t base = type == 0u ? tmpl : type == 1u ? ca + CA2::KTAB : rec;
-    const uint32_t w = B[(base >> 2) + (e & 63u)];
-    const uint32_t len = rw_len(w);
-    if (len) copy_run(B, at, rw_off(w) + (type == 0u ? tmpl : 0u), len);
-    at += len;
+    if (type == 0u) {
+#if defined(__CUDA_ARCH__)
+      const uint32_t pw = __ldg(sw + (e & 63u));
+#else
+      const uint32_t pw = sw[e & 63u];
+#endif
+      lw_put_piece(w, reinterpret_cast<const uint4 *>(slot + rw_off(pw)), rw_len(pw));
+    } else {
+      const uint32_t pw = B[(((type == 1u ? ca + CA2::KTAB : rec)) >> 2) + (e & 63u)];
+      const uint32_t len = rw_len(pw), so = rw_off(pw);
+      if (len) lw_put(w, B + (so >> 2), so & 3u, len);
+    }
   }
+  return w;
+}
+// The last bytes of a line, after every line of the round has been written: OR-ed into the word
+// the next line has started (`has_next`), or stored as they are.
+KGM_HD void lw_finish(const LineWriter &w, bool has_next) {
+  if (w.fill) *w.d = has_next ? (*w.d | w.pend) : w.pend;
 }
 
 // ---- parsing: the row parsers of kgm_fast.cuh, returning runs relative to the text window -------

@@ -119,9 +119,9 @@ inline bool build_template_block(const std::string &host, uint32_t node_fixed,
 
 // ---- template slots of k_poll2 (kgm_poll2_leaf.cuh) -------------------------------------------
 // One slot per node (the two pieces of its node_gpu lines) and per gated container (the five
-// pieces of its pod_gpu lines): header | piece bytes, 16-byte aligned and padded.
-//   header  8 run words relative to the slot start (piece i), 7 x u16 constant bytes in front of
-//           job 1..7 (of 8), u16 constant bytes of a whole line incl. its '\n'
+// pieces of its pod_gpu lines): header | piece bytes, every piece on a 16-byte boundary.
+//   header  8 run words relative to the slot start (piece i), ..., u16 constant bytes of a whole
+//           line incl. its '\n' at byte 46
 // Appends the slot to `pool` and returns true; false (pool untouched) if a piece is too long.
 inline bool build_slot(bool pod, const std::string *pieces, int npieces, std::vector<uint8_t> &pool,
                        size_t *start_out, size_t *len_out) {
@@ -131,16 +131,13 @@ inline bool build_slot(bool pod, const std::string *pieces, int npieces, std::ve
   for (int i = 0; i < npieces; ++i) {
     if (pieces[i].size() > 2000) return false;
     W[i] = rw(at, (uint32_t)pieces[i].size());
-    at += (uint32_t)pieces[i].size();
+    at += ((uint32_t)pieces[i].size() + 15u) & ~15u;
   }
   if (at > 8192) return false;
-  uint16_t tail[8];
+  uint16_t tail[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   uint32_t cst = 0;
   const int ns = pod ? (int)POD_SEGS : (int)NODE_SEGS;
-  for (int k = 0; k <= ns; ++k) {
-    for (int q = 1; q < 8; ++q)
-      if ((pod ? jb8_pod(q) : jb8_node(q)) == (uint32_t)k) tail[q - 1] = (uint16_t)cst;
-    if (k == ns) break;
+  for (int k = 0; k < ns; ++k) {
     const uint32_t e = pod ? seg_pod(k) : seg_node(k);
     if ((e >> 6) == 0u) cst += rw_len(W[e & 63u]);
     else if ((e >> 6) == 1u) cst += k_len(e & 63u);
@@ -151,8 +148,10 @@ inline bool build_slot(bool pod, const std::string *pieces, int npieces, std::ve
   const uint8_t *wp = reinterpret_cast<const uint8_t *>(W), *tp = reinterpret_cast<const uint8_t *>(tail);
   pool.insert(pool.end(), wp, wp + 32);
   pool.insert(pool.end(), tp, tp + 16);
-  for (int i = 0; i < npieces; ++i) pool.insert(pool.end(), pieces[i].begin(), pieces[i].end());
-  while (pool.size() & 15) pool.push_back(0);
+  for (int i = 0; i < npieces; ++i) {
+    pool.insert(pool.end(), pieces[i].begin(), pieces[i].end());
+    while (pool.size() & 15) pool.push_back(0);
+  }
   *len_out = pool.size() - *start_out;
   return true;
 }

@@ -123,7 +123,7 @@ SIGNATURES = {
 }
 NOALLOC_MAX_ROWS = 16384
 ABI_VERSION = 3
-PIPELINE_AUTO, PIPELINE_STAGED, PIPELINE_FUSED_GENERIC, PIPELINE_FUSED_V1 = 0, 1, 2, 3
+PIPELINE_AUTO, PIPELINE_STAGED, PIPELINE_FUSED_GENERIC, PIPELINE_FUSED_V1, PIPELINE_FUSED_V2 = 0, 1, 2, 3, 4
 
 _lib = None
 

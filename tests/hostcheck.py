@@ -145,13 +145,26 @@ def fast_proc_row(row: bytes, shift=0):
                 hash=u64[0], pidkey=u64[1])
 
 
-# ---- k_poll2: lines written as independent jobs -----------------------------------------------
+# ---- k_poll2: lines written by the streaming line writer ---------------------------------------
+def _two_lines_or_none(n, out, align):
+    """(line, ok): the buffer holds 8 guard bytes, the line, and a second copy of it right behind
+    (the next lane's line); ok = nothing touched in front of the word the line starts in (a line
+    that starts inside a word stores zeros in its predecessor's bytes, which the predecessor
+    ORs its last bytes into) and both copies identical."""
+    if n < 0:
+        return None, True
+    raw = bytes(out[:2 * n + 16])
+    z = align & 3
+    front = raw[:8 - z] == b"\x5a" * (8 - z) and raw[8 - z:8] == b"\0" * z
+    return raw[8:8 + n], front and raw[8 + n:8 + 2 * n] == raw[8:8 + n]
+
+
 def p2_node_line(host, row: bytes, sid, shift=0, align=0, jobs=4):
     out = (C.c_ubyte * 20000)()
     planned = C.c_uint32()
     n = lib().hc_p2_node_line(host.encode(), row + b"\0" * 16, len(row), sid, shift, align, jobs, out,
                               C.byref(planned))
-    line, guards = _line_or_none(n, out)
+    line, guards = _two_lines_or_none(n, out, align)
     return line, planned.value, guards
 
 
@@ -161,7 +174,7 @@ def p2_busy_line(host, ns, cid, user, pod, prow: bytes, grow: bytes, sid, shift=
     n = lib().hc_p2_busy_line(host.encode(), ns.encode(), cid.encode(), user.encode(), pod.encode(),
                               prow + b"\0" * 16, len(prow), grow + b"\0" * 16, len(grow), sid, shift,
                               align, jobs, out, C.byref(planned))
-    line, guards = _line_or_none(n, out)
+    line, guards = _two_lines_or_none(n, out, align)
     return line, planned.value, guards
 
 
@@ -170,7 +183,7 @@ def p2_idle_line(host, ns, cid, user, pod, sid, align=0, jobs=4):
     planned = C.c_uint32()
     n = lib().hc_p2_idle_line(host.encode(), ns.encode(), cid.encode(), user.encode(), pod.encode(),
                               0xFFFFFFFF if sid is None else sid, align, jobs, out, C.byref(planned))
-    line, guards = _line_or_none(n, out)
+    line, guards = _two_lines_or_none(n, out, align)
     return line, planned.value, guards
 
 

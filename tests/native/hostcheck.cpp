@@ -262,7 +262,7 @@ static P2Mem p2_make(const uint8_t *gtext, uint32_t glen, uint32_t gshift, const
   m.grec = m.slot + r16((uint32_t)slot_len) + 16;
   m.prec = m.grec + p2::GREC_BYTES;
   m.stage = m.prec + p2::PREC_BYTES + 16;
-  m.words.assign((m.stage + 3 * MAX_LINE_BYTES) / 4, 0x5a5a5a5au);
+  m.words.assign((m.stage + 3 * MAX_LINE_BYTES) / 4 + 4096, 0x5a5a5a5au);
   p2::fill_ca2(m.bytes(), 0u);
   memcpy(m.bytes() + m.tg + gshift, gtext, glen);
   memcpy(m.bytes() + m.ta + ashift, atext, alen);
@@ -270,12 +270,21 @@ static P2Mem p2_make(const uint8_t *gtext, uint32_t glen, uint32_t gshift, const
   return m;
 }
 
-// all jobs of one line, last job first (they must not depend on each other)
-static uint32_t p2_write(P2Mem &m, uint32_t pod, uint32_t jobs, uint32_t rec, uint32_t dst, uint64_t qoff,
-                         uint32_t var) {
-  const uint32_t step = 8u / jobs;
-  for (uint32_t q = jobs; q-- > 0;) p2::compose_job(m.words.data(), 0u, pod, q * step, step, m.slot, rec, dst, qoff);
-  return *reinterpret_cast<const uint16_t *>(m.bytes() + m.slot + p2::SLOT_FIXED) + var;
+// One line through the line writer, at byte offset `dst`; a second copy of it is written right
+// behind (before the first one is finished), as the next lane of a round would, so that the
+// shared word between two lines is exercised.  Returns the line's length.
+static uint32_t p2_write(P2Mem &m, uint32_t pod, uint32_t rec, uint32_t dst, uint32_t var) {
+  const uint32_t len = *reinterpret_cast<const uint16_t *>(m.bytes() + m.slot + p2::SLOT_FIXED) + var;
+  // the slot is read as "global memory": give the writer its own aligned copy
+  static std::vector<p2::uint4> slotcopy;
+  slotcopy.assign(1024, p2::uint4{0, 0, 0, 0});
+  memcpy(slotcopy.data(), m.bytes() + m.slot, 8192);
+  const uint8_t *slot = reinterpret_cast<const uint8_t *>(slotcopy.data());
+  p2::LineWriter w2 = p2::compose_line(m.words.data(), 0u, pod, slot, rec, dst + len);
+  p2::LineWriter w1 = p2::compose_line(m.words.data(), 0u, pod, slot, rec, dst);
+  p2::lw_finish(w1, true);
+  p2::lw_finish(w2, false);
+  return len;
 }
 
 int hc_p2_node_line(const char *host, const uint8_t *row, uint32_t row_len, uint32_t sid, uint32_t shift,
@@ -287,12 +296,11 @@ int hc_p2_node_line(const char *host, const uint8_t *row, uint32_t row_len, uint
   p2::G2 g;
   if (!p2::parse_gpu_row2(m.words.data() + m.tg / 4, shift, shift + row_len, g)) return -1;
   p2::store_grec(m.words.data(), m.tg, m.grec, g, sid);
-  uint32_t var;
-  const uint64_t qoff = p2::measure_line<false>(m.words.data() + m.grec / 4, &var);
-  if (var > 511) return -1;
-  const uint32_t n = p2_write(m, 0u, jobs, m.grec, m.stage + 64 + align, qoff, var);
+  const uint32_t var = p2::line_var_bytes<false>(m.words.data() + m.grec / 4);
+  const uint32_t n = p2_write(m, 0u, m.grec, m.stage + 64 + align, var);
   *planned = n;
-  memcpy(out, m.bytes() + m.stage + 64 + align - 8, n + 16);      // 8 guard bytes either side
+  memcpy(out, m.bytes() + m.stage + 64 + align - 8, 2 * n + 16);  // 8 guard bytes in front, the second copy behind
+  (void)jobs;
   return (int)n;
 }
 
@@ -310,12 +318,11 @@ int hc_p2_busy_line(const char *host, const char *ns, const char *cid, const cha
   p2::P2 p;
   if (!p2::parse_proc_row2(m.words.data() + m.ta / 4, ashift, ashift + prow_len, p)) return -1;
   p2::store_prec(m.words.data(), m.ta, m.prec, p, m.words.data() + m.grec / 4);
-  uint32_t var;
-  const uint64_t qoff = p2::measure_line<true>(m.words.data() + m.prec / 4, &var);
-  if (var > 511) return -1;
-  const uint32_t n = p2_write(m, 1u, jobs, m.prec, m.stage + 64 + align, qoff, var);
+  const uint32_t var = p2::line_var_bytes<true>(m.words.data() + m.prec / 4);
+  const uint32_t n = p2_write(m, 1u, m.prec, m.stage + 64 + align, var);
   *planned = n;
-  memcpy(out, m.bytes() + m.stage + 64 + align - 8, n + 16);
+  memcpy(out, m.bytes() + m.stage + 64 + align - 8, 2 * n + 16);
+  (void)jobs;
   return (int)n;
 }
 
@@ -327,11 +334,11 @@ int hc_p2_idle_line(const char *host, const char *ns, const char *cid, const cha
   const uint8_t dummy[4] = {0, 0, 0, 0};
   P2Mem m = p2_make(dummy, 0, 0, dummy, 0, 0, pool, st, ln);
   p2::store_idle_rec(m.words.data(), 0u, m.prec, sid);
-  uint32_t var;
-  const uint64_t qoff = p2::measure_line<true>(m.words.data() + m.prec / 4, &var);
-  const uint32_t n = p2_write(m, 1u, jobs, m.prec, m.stage + 64 + align, qoff, var);
+  const uint32_t var = p2::line_var_bytes<true>(m.words.data() + m.prec / 4);
+  const uint32_t n = p2_write(m, 1u, m.prec, m.stage + 64 + align, var);
   *planned = n;
-  memcpy(out, m.bytes() + m.stage + 64 + align - 8, n + 16);
+  memcpy(out, m.bytes() + m.stage + 64 + align - 8, 2 * n + 16);
+  (void)jobs;
   return (int)n;
 }
 

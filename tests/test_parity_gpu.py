@@ -23,14 +23,15 @@ UNSUPPORTED_OK = {"err_quoted_first_cell": _ffi.DOC_UNSUPPORTED_QUOTE}
 
 
 PIPELINES = {"fused": _ffi.PIPELINE_AUTO, "staged": _ffi.PIPELINE_STAGED,
-             "fused-generic": _ffi.PIPELINE_FUSED_GENERIC, "fused-v1": _ffi.PIPELINE_FUSED_V1}
+             "fused-generic": _ffi.PIPELINE_FUSED_GENERIC, "fused-v2": _ffi.PIPELINE_FUSED_V2}
 
 
 @pytest.fixture(scope="module", params=list(PIPELINES))
 def mon(request):
-    """Every test runs three times: through the fused single-pass kernel (fast path, with its
-    in-kernel generic path for irregular documents), through the four staged kernels, and
-    through the fused kernel with the fast path switched off."""
+    """Every test runs four times: through the fused single-pass kernel the library picks (the
+    team kernel k_poll for batches of this size; fast path, with its in-kernel generic path for
+    irregular documents), through the four staged kernels, through the fused kernel with the fast
+    path switched off, and through the warp kernel k_poll2."""
     m = monitor.Monitor(0)
     m.set_pipeline(PIPELINES[request.param])
     m.pipeline_name = request.param
@@ -205,7 +206,7 @@ def test_full_config2_properties_and_sampled_parity(mon):
     else:
         # the clean fleet batch goes through the fast path entirely (or not at all when it is off)
         assert t["launches"] == 1 and t["fused"] == 1
-        assert t["slow_docs"] == (0 if mon.pipeline_name in ("fused", "fused-v1") else rp.n_docs)
+        assert t["slow_docs"] == (0 if mon.pipeline_name in ("fused", "fused-v2") else rp.n_docs)
         assert t["fused_ctas_per_sm"] in (1, 2)                     # 1 x 7 or 2 x 3/4 teams per SM
 
 

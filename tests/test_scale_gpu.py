@@ -22,10 +22,11 @@ from oracle import poll_oracle
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module", params=["fused", "staged"])
+@pytest.fixture(scope="module", params=["fused", "staged", "fused-v1"])
 def mon(request):
     m = monitor.Monitor(0)
-    m.set_pipeline({"fused": _ffi.PIPELINE_AUTO, "staged": _ffi.PIPELINE_STAGED}[request.param])
+    m.set_pipeline({"fused": _ffi.PIPELINE_AUTO, "staged": _ffi.PIPELINE_STAGED,
+                    "fused-v1": _ffi.PIPELINE_FUSED_V1}[request.param])
     m.pipeline_name = request.param
     yield m
     m.close()
