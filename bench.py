@@ -23,10 +23,14 @@ Printed JSON (one line, rank 0):
   roofline  the dominant kernel (k_poll: the whole fused pass; k_encode when staged):
           algorithmic bytes per launch / its CUDA-event time with the GPU to itself
           (roofline.launch_ms_source says where that time was taken)
-  cpu_baseline  the oracle port of gpu.py timed on this box's host cores (N=1, rank 0)
+  cpu_baseline  the reference (gpu.py main(), else the port) on one host core over a bounded
+          prefix of the workload (N=1, rank 0)
 
-`--impl reference` times the reference's CPU implementation of the path (the oracle port of
-gpu.py: the reference itself cannot travel to the GPU box) on all host cores.
+`--impl reference` times the reference's CPU implementation of the path on all host cores, every
+document of the configs[1] workload per step: the unmodified gpu.py main() under
+oracle/ref_harness.py (oracle/make_ref.py puts a git-ignored copy of the script into
+oracle/_ref/, which travels to the GPU box); the port oracle/poll_oracle.py only if that copy
+is missing.
 """
 from __future__ import annotations
 
@@ -134,29 +138,39 @@ def build_workload(config, rank):
 _RP = None
 
 
-def _oracle_docs(idx):
-    from oracle import poll_oracle
+def _cpu_poll():
+    """The CPU implementation the two CPU legs time: the reference's own main() (gpu.py:90-256)
+    under oracle/ref_harness.py when the script is there (/root/reference in the build container,
+    the copy oracle/make_ref.py put into oracle/_ref/ on the GPU box), else the port."""
+    from oracle import poll_oracle, ref_harness
+    if ref_harness.available():
+        return ref_harness.run_reference, "reference", "gpu.py main() unmodified, I/O seams stubbed (oracle/ref_harness.py)"
+    return poll_oracle.poll, "port", "oracle/poll_oracle.py (CPython port of gpu.py main(); oracle/_ref/gpu.py not found)"
+
+
+def _cpu_docs(idx):
+    poll = _cpu_poll()[0]
     n = 0
     for d in idx:
         s = _RP.nodes[int(_RP.doc_node[d])]
-        lines, err = poll_oracle.poll(s.name, _RP.gpu_texts[d], _RP.apps_texts[d], s.ps_text, s.stats_text,
-                                      s.top, s.inspect, s.smi_list)
+        lines, err = poll(s.name, _RP.gpu_texts[d], _RP.apps_texts[d], s.ps_text, s.stats_text, s.top, s.inspect,
+                          s.smi_list)
         n += len(lines)
     return n
 
 
 def cpu_baseline_single_core(rp, gpu_result, budget_s=12.0):
-    """Oracle port on ONE host core over a bounded prefix of the same workload (only the
-    oracle call is timed); doubles as a parity spot check of the GPU result on those
+    """The reference on ONE host core over a bounded prefix of the same workload (only the
+    reference call is timed); doubles as a parity spot check of the GPU result on those
     documents."""
-    from oracle import poll_oracle
+    poll, kind, what = _cpu_poll()
     spent = 0.0
     docs = samples = mismatches = 0
     for d in range(rp.n_docs):
         s = rp.nodes[int(rp.doc_node[d])]
         t0 = time.perf_counter()
-        lines, err = poll_oracle.poll(s.name, rp.gpu_texts[d], rp.apps_texts[d], s.ps_text, s.stats_text,
-                                      s.top, s.inspect, s.smi_list)
+        lines, err = poll(s.name, rp.gpu_texts[d], rp.apps_texts[d], s.ps_text, s.stats_text, s.top, s.inspect,
+                          s.smi_list)
         spent += time.perf_counter() - t0
         docs += 1
         samples += rp.gpu_texts[d].count("\n") - 1
@@ -164,15 +178,16 @@ def cpu_baseline_single_core(rp, gpu_result, budget_s=12.0):
             mismatches += 1
         if spent > budget_s:
             break
-    return {"value": samples / spent if spent else 0.0, "unit": "samples/s", "cores": 1, "kind": "port",
-            "sample": "first %d of %d documents of the same workload (%.1f s), oracle/poll_oracle.py "
-                      "(CPython port of gpu.py main()), 1 process" % (docs, rp.n_docs, spent),
+    return {"value": samples / spent if spent else 0.0, "unit": "samples/s", "cores": 1, "kind": kind,
+            "sample": "first %d of %d documents of the same workload (%.1f s), %s, 1 process"
+                      % (docs, rp.n_docs, spent, what),
             "parity_docs_checked": docs if gpu_result is not None else 0,
             "parity_mismatches": mismatches}
 
 
 def run_reference_arm(args):
-    """`--impl reference`: the reference's CPU implementation of the path on all host cores."""
+    """`--impl reference`: the reference's CPU implementation of the path on all host cores, every
+    document of the workload in every step."""
     global _RP
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -180,32 +195,34 @@ def run_reference_arm(args):
     import multiprocessing as mp
     rp, _ = build_workload(args.config, 0)
     _RP = rp
+    _, kind, what = _cpu_poll()
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-    sample_docs = min(rp.n_docs, max(cores * 16, 240))
+    # the whole configs[1] batch per step; of the larger configs a bounded sample (10 000 documents)
+    sample_docs = min(rp.n_docs, 10000)
     per_doc_samples = rp.n_samples() / rp.n_docs
-    chunks = [list(range(i, sample_docs, cores)) for i in range(cores)]
+    chunks = [list(range(i, sample_docs, cores * 4)) for i in range(cores * 4)]
     ctx = mp.get_context("fork")
     times = []
     with ctx.Pool(cores) as pool:
         for step in range(args.warmup + args.steps):
             t0 = time.perf_counter()
-            pool.map(_oracle_docs, chunks)
+            pool.map(_cpu_docs, chunks, chunksize=1)
             dt = time.perf_counter() - t0
             if step >= args.warmup:
                 times.append(dt)
     ms = 1e3 * sum(times) / len(times)
     value = sample_docs * per_doc_samples / (ms / 1e3)
+    sample = ("all %d documents of the workload per step" % rp.n_docs if sample_docs == rp.n_docs else
+              "%d of %d documents per step" % (sample_docs, rp.n_docs))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "samples/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
         "config": {"workload": workload_name(args.config), "docs_per_step": sample_docs,
-                   "note": "each step is a bounded sample of the workload"},
-        "cpu_baseline": {"value": value, "unit": "samples/s", "cores": cores, "kind": "port",
-                         "sample": "%d of %d documents per step, oracle/poll_oracle.py (CPython port of "
-                                   "gpu.py main(); the reference script itself is not on this box), "
-                                   "%d processes" % (sample_docs, rp.n_docs, cores)},
+                   "docs_per_gpu": rp.n_docs, "samples_per_gpu": rp.n_samples()},
+        "cpu_baseline": {"value": value, "unit": "samples/s", "cores": cores, "kind": kind,
+                         "sample": "%s, %s, %d processes" % (sample, what, cores)},
         "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }

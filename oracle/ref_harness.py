@@ -7,10 +7,12 @@ seams replaced:
   * ``gpu.os.popen``       (gpu.py:221-223) -> canned ``nvidia-smi -L | cut`` list
   * ``gpu.requests.post``  (gpu.py:145,218,252) -> capture of the POSTed line
 
-The reference tree exists only in the build container, never on the GPU box, so nothing
-here may be imported by ``-m gpu`` tests, ``smoke()`` or ``bench.py``.  It is used by
-``tests/golden/make_golden.py`` (fixture generation) and by the CPU-only differential test
-that pins ``oracle/poll_oracle.py`` against the real script.
+The reference tree exists only in the build container.  ``oracle/make_ref.py`` (run by
+``__graft_entry__.build()``) puts an unmodified copy of the script into the git-ignored
+``oracle/_ref/``, which travels to the GPU box; there this harness is used by ``bench.py``'s
+two CPU legs only (``--impl reference`` and ``cpu_baseline``), never by the product.  In the
+build container it is also used by ``tests/golden/make_golden.py`` (fixture generation) and
+by the CPU-only differential test that pins ``oracle/poll_oracle.py`` against the real script.
 """
 from __future__ import annotations
 
@@ -20,7 +22,13 @@ import io
 import os
 import warnings
 
+import sys
+import types
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
 REFERENCE_DIR = os.environ.get("KGM_REFERENCE_DIR", "/root/reference")
+if not os.path.isfile(os.path.join(REFERENCE_DIR, "gpu.py")):
+    REFERENCE_DIR = os.path.join(_HERE, "_ref")          # the copy oracle/make_ref.py made
 _gpu = None
 
 
@@ -28,9 +36,21 @@ def available() -> bool:
     return os.path.isfile(os.path.join(REFERENCE_DIR, "gpu.py"))
 
 
+def _ensure_requests():
+    """gpu.py imports `requests` only to POST (gpu.py:145); the harness replaces that call, so
+    a box without the package gets an empty stand-in module."""
+    try:
+        import requests  # noqa: F401
+    except Exception:
+        stub = types.ModuleType("requests")
+        stub.post = lambda *a, **k: None
+        sys.modules["requests"] = stub
+
+
 def _load():
     global _gpu
     if _gpu is None:
+        _ensure_requests()
         spec = importlib.util.spec_from_file_location(
             "_kgm_reference_gpu", os.path.join(REFERENCE_DIR, "gpu.py"))
         mod = importlib.util.module_from_spec(spec)
