@@ -256,11 +256,6 @@ def run_kgm_arm(args):
     # stdout carries the one JSON line only: whatever libraries print there goes to stderr
     json_fd = os.dup(1)
     os.dup2(2, 1)
-    if world > 1:
-        # leave a few CTA slots of every GPU to the NCCL kernel that signals a landed step
-        # (push gather: a 4-byte all-reduce), so that it runs beside the persistent poll
-        # kernel of the next step instead of after it
-        os.environ.setdefault("KGM_RESERVE_CTAS", "6")
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -297,7 +292,7 @@ def run_kgm_arm(args):
     acc = {k: [] for k in keys}
     done_samples = 0
 
-    host_s = {"encode_call": 0.0, "gather_call": 0.0}
+    host_s = {"encode_call": 0.0, "gather_call": 0.0, "finish_wait": 0.0}
 
     # Steps are queued without waiting for their results: every context has at most one
     # kgm_encode_resident_async in flight, finished (sizes, overflow check, kernel times)
@@ -341,24 +336,21 @@ def run_kgm_arm(args):
         t0 = time.perf_counter()
         if use_async:
             finish(v)
+            if timed:
+                host_s["finish_wait"] += time.perf_counter() - t0
             if serialize and last_launch[0] is not None:
                 ext[v].wait_event(last_launch[0])    # k_poll launches of different contexts do not overlap
             push = gather is not None and gather.mode == "push"
-            if push:                                 # the kernels write this step's shard straight into its slot on rank 0
-                ptr, nbytes = gather.push_slot()
-                free = gather.push_wait()
-                if free is not None:
-                    ext[v].wait_event(free)
-                mon.set_output_buffer(ptr, nbytes)
-            r = mon.encode_resident_async()
+            if push:                                 # one library call: wait, encode straight into the slot on the
+                r = gather.push_step(mon)            # step's gathering rank, tell it the shard has landed
+            else:
+                r = mon.encode_resident_async()
             if serialize:
                 last_launch[0] = torch.cuda.Event()
                 last_launch[0].record(ext[v])
             t1 = time.perf_counter()
             fin = None
-            if push:
-                gather.start_push(ext[v])            # (slot reuse is governed by push_wait, not by the context)
-            elif gather is not None:
+            if gather is not None and not push:
                 fin = gather.start_device(int(r.lines), ext[v])
             inflight[v] = (timed, fin)
             if timed:
@@ -415,24 +407,41 @@ def run_kgm_arm(args):
         seen = [None] * world
         dist.all_gather_object(seen, (concat_check, pack_ms))
         concat_check, pack_ms = seen[holder]
+    # clocks / throttle reasons: ONE nvidia-smi (rank 0), started well before the timed region so
+    # that its start-up does not fall into it; it keeps sampling through the region and through
+    # an untimed repetition of the same steps right after it (the region itself is a few
+    # milliseconds, shorter than one sampling period)
+    clocks = ClockSampler(local_rank) if rank == 0 else None
+    if clocks:
+        clocks.__enter__()
+        time.sleep(0.6)
     sync_all()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     wall0 = time.perf_counter()
-    with ClockSampler(local_rank) as clocks:
-        ev0.record()
-        for i in range(args.steps):
-            step(n_warm + i, True)
-        drain()
-        if gather:
-            gather.finish()
-        ev1.record()
-        torch.cuda.synchronize(device)
-        if args.steps * 0.3e-3 < 0.5:                # keep the region long enough for a few clock samples
-            time.sleep(0.3)
+    ev0.record()
+    for i in range(args.steps):
+        step(n_warm + i, True)
+    drain()
+    if gather:
+        gather.finish()
+    ev1.record()
+    torch.cuda.synchronize(device)
     sync_all()
     wall_ms = 1e3 * (time.perf_counter() - wall0)
     region_ms = ev0.elapsed_time(ev1)
     step_ms = region_ms / args.steps
+    n_extra = int(min(4000, max(20, 500.0 / max(step_ms, 1e-3))))   # ~0.5 s of the same steps, untimed, under the sampler
+    if world > 1:                                    # (every rank must run the same number of steps)
+        t = torch.tensor([n_extra], dtype=torch.int64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        n_extra = int(t.item())
+    for extra in range(n_extra):
+        step(n_warm + args.steps + extra, False)
+    drain()
+    if gather:
+        gather.finish()
+    if clocks:
+        clocks.__exit__(None, None, None)
     mean = {k: sum(v) / len(v) for k, v in acc.items()}
     if not serialize:
         # the launches of the timed region overlap, so their own event times include waiting
@@ -567,6 +576,10 @@ def run_kgm_arm(args):
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks.summary(),
         }
+        if world > 1:
+            line["gather_mode"] = gather.mode
+            line["concat_verified"] = bool(concat_check)
+            line["pack_ms"] = pack_ms
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline_single_core(rps[0], host_result)
         os.write(json_fd, (json.dumps(line) + "\n").encode())

@@ -278,6 +278,38 @@ void  kgm_host_free(void *p);
 int  kgm_concat_shards(const uint8_t *slots, uint64_t stride, const int64_t *counts, uint32_t world,
                        uint8_t *out, uint64_t out_cap, uint64_t *totals_out, void *stream);
 
+/* Stream-ordered counters between the GPUs of one job (no counterpart in the reference).  The
+ * ranks tell each other "my shard of step k has landed in your slot" and "that slot set is free
+ * again" through 32-bit counters that only grow, kept in memory every rank has mapped (CUDA IPC,
+ * peer access), instead of running a collective per step.
+ *   kgm_stream_signal_flags  behind everything queued on `stream` so far, raises each of the
+ *                            n <= KGM_MAX_FLAG_TARGETS counters to `value` (system-scope atomic max
+ *                            with release: signals from different streams may arrive out of order)
+ *   kgm_stream_wait_flags    holds `stream` until each of the n <= 32 consecutive counters at `flags`
+ *                            has reached `value` (wrap-safe comparison; a one-warp kernel that polls)
+ * All pointers are device pointers valid on the current device.                              */
+#define KGM_MAX_FLAG_TARGETS 16
+int  kgm_stream_signal_flags(void *stream, uint32_t *const *targets, uint32_t n, uint32_t value);
+int  kgm_stream_wait_flags(void *stream, const uint32_t *flags, uint32_t n, uint32_t value);
+
+/* One step of a multi-GPU job in one call (no counterpart in the reference): on the context's
+ * stream, wait until the counter at `wait_flag` has reached `wait_value` (skipped if NULL), encode
+ * the resident batch into `slot` (as kgm_set_output_buffer + kgm_encode_resident_async), then
+ * store `signal_value` to `signal_flag` (skipped if NULL).  `slot` is typically this rank's
+ * fixed-stride slot on the step's gathering GPU.  Finish with kgm_encode_finish.             */
+int  kgm_push_step(kgm_ctx *ctx, void *slot, uint64_t slot_bytes, const uint32_t *wait_flag, uint32_t wait_value,
+                   uint32_t *signal_flag, uint32_t signal_value, kgm_result *out);
+
+/* The same step with the shard carried by a copy engine instead of the poll kernel's own
+ * stores (no counterpart in the reference): the context encodes into its own buffer; on a second
+ * stream, behind the kernel, wait for `wait_flag`, copy {header, lines} (`slot_bytes`, at most
+ * the context's output capacity) to `slot` -- typically peer memory -- and store `signal_value`
+ * to `signal_flag`.  The kernel never waits for another GPU and writes local memory only; the
+ * copy overlaps the next step's kernel.  The context's buffer is reused only after its last copy
+ * has left it.                                                                               */
+int  kgm_push_copy_step(kgm_ctx *ctx, void *slot, uint64_t slot_bytes, const uint32_t *wait_flag,
+                        uint32_t wait_value, uint32_t *signal_flag, uint32_t signal_value, kgm_result *out);
+
 /* Stage-1 tokenizer for callers that may not allocate device memory.  (No counterpart in
  * the reference; it exists for deployment reasons only.)
  *
@@ -305,7 +337,9 @@ int  kgm_concat_shards(const uint8_t *slots, uint64_t stride, const int64_t *cou
  *             on it has finished
  *
  * The first call on a device looks up the device address of the fixed array
- * (cudaGetSymbolAddress); make that first call before any stream capture begins.  All
+ * (cudaGetSymbolAddress); make that first call before any stream capture begins.  Every call
+ * copies the overflow flag back and waits for the stream, so it returns with the outputs
+ * complete.  All
  * calls on a device share the one array and it keeps the previous call's contents: the
  * entry point clears what has to start at zero itself, but two calls whose GPU work
  * overlaps (different streams or threads) race on it -- serialise them.                  */

@@ -115,6 +115,8 @@ struct kgm_ctx {
   // chunked end-to-end path: copies and kernels of consecutive chunks overlap
   cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
   cudaEvent_t ev_in[MAX_CHUNKS] = {}, ev_k[MAX_CHUNKS] = {};
+  cudaEvent_t ev_enc_done = nullptr, ev_copy_done = nullptr;   // kgm_push_copy_step
+  bool copy_pending = false;
   HostBuf h_chunk;                         // per chunk: posted totals {lines, bytes, seq} + counters
   HostBuf h_docarr;                        // staging of the per-document arrays
   uint64_t post_seq = 0;
@@ -943,6 +945,8 @@ int kgm_create(kgm_ctx **out, int device) {
     e = cudaEventCreate(&ctx->ev_in[i]);
     if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev_k[i]);
   }
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_enc_done, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_copy_done, cudaEventDisableTiming);
   cudaDeviceProp prop;
   if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
   if (e != cudaSuccess) { kgm_destroy(ctx); cudaGetLastError(); return KGM_E_CUDA; }
@@ -967,6 +971,7 @@ void kgm_destroy(kgm_ctx *ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  if (ctx->s_d2h) cudaStreamSynchronize(ctx->s_d2h);
   DevBuf *dev[] = {&ctx->f_cont_begin, &ctx->f_nerr_parse, &ctx->f_nerr_join, &ctx->f_gated,
                    &ctx->f_err_inspect, &ctx->f_err_emit, &ctx->f_vis_begin, &ctx->f_vis_off,
                    &ctx->f_vis_bytes, &ctx->f_vis_hash, &ctx->f_node_piece, &ctx->f_node_fixed,
@@ -988,6 +993,8 @@ void kgm_destroy(kgm_ctx *ctx) {
     if (ctx->ev_in[i]) cudaEventDestroy(ctx->ev_in[i]);
     if (ctx->ev_k[i]) cudaEventDestroy(ctx->ev_k[i]);
   }
+  if (ctx->ev_enc_done) cudaEventDestroy(ctx->ev_enc_done);
+  if (ctx->ev_copy_done) cudaEventDestroy(ctx->ev_copy_done);
   if (ctx->s_h2d) cudaStreamDestroy(ctx->s_h2d);
   if (ctx->s_d2h) cudaStreamDestroy(ctx->s_d2h);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -1311,6 +1318,54 @@ int kgm_set_output_buffer(kgm_ctx *ctx, void *dev_ptr, uint64_t bytes) {
   }
   ctx->ext_out = static_cast<uint8_t *>(dev_ptr);
   ctx->ext_out_bytes = bytes & ~15ull;
+  return KGM_OK;
+}
+
+int kgm_push_step(kgm_ctx *ctx, void *slot, uint64_t slot_bytes, const uint32_t *wait_flag, uint32_t wait_value,
+                  uint32_t *signal_flag, uint32_t signal_value, kgm_result *out) {
+  if (!ctx || !out || !slot) return KGM_E_INVALID;
+  CU(cudaSetDevice(ctx->device));
+  int rc;
+  if (slot != ctx->ext_out || (slot_bytes & ~15ull) != ctx->ext_out_bytes) {
+    if ((rc = kgm_set_output_buffer(ctx, slot, slot_bytes))) return rc;
+  }
+  if (wait_flag && (rc = kgm_stream_wait_flags(ctx->stream, wait_flag, 1, wait_value))) return rc;
+  ctx->have_result = false;
+  if ((rc = launch_resident(ctx, true))) return rc;
+  ctx->async_pending = true;
+  ctx->n_lines = 0; ctx->n_bytes = 0;
+  fill_result_dev(ctx, out);
+  if (signal_flag) {
+    uint32_t *t[1] = {signal_flag};
+    if ((rc = kgm_stream_signal_flags(ctx->stream, t, 1, signal_value))) return rc;
+  }
+  return KGM_OK;
+}
+
+int kgm_push_copy_step(kgm_ctx *ctx, void *slot, uint64_t slot_bytes, const uint32_t *wait_flag, uint32_t wait_value,
+                       uint32_t *signal_flag, uint32_t signal_value, kgm_result *out) {
+  if (!ctx || !out || !slot || (reinterpret_cast<uintptr_t>(slot) & 15)) return KGM_E_INVALID;
+  CU(cudaSetDevice(ctx->device));
+  int rc;
+  if (ctx->ext_out && (rc = kgm_set_output_buffer(ctx, nullptr, 0))) return rc;    // the context's own buffer
+  if (ctx->copy_pending) CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_copy_done, 0));   // ... once its last copy has left it
+  ctx->have_result = false;
+  if ((rc = launch_resident(ctx, true))) return rc;
+  ctx->async_pending = true;
+  ctx->n_lines = 0; ctx->n_bytes = 0;
+  fill_result_dev(ctx, out);
+  CU(cudaEventRecord(ctx->ev_enc_done, ctx->stream));
+  CU(cudaStreamWaitEvent(ctx->s_d2h, ctx->ev_enc_done, 0));
+  if (wait_flag && (rc = kgm_stream_wait_flags(ctx->s_d2h, wait_flag, 1, wait_value))) return rc;
+  const uint64_t have = ((ctx->out_cap + 16 + OUT_HEADER) & ~15ull);
+  CU(cudaMemcpyAsync(slot, ctx->work.out - OUT_HEADER, std::min<uint64_t>(slot_bytes & ~15ull, have), cudaMemcpyDefault,
+                     ctx->s_d2h));
+  if (signal_flag) {
+    uint32_t *t[1] = {signal_flag};
+    if ((rc = kgm_stream_signal_flags(ctx->s_d2h, t, 1, signal_value))) return rc;
+  }
+  CU(cudaEventRecord(ctx->ev_copy_done, ctx->s_d2h));
+  ctx->copy_pending = true;
   return KGM_OK;
 }
 

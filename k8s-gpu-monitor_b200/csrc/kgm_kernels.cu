@@ -800,6 +800,58 @@ extern "C" int kgm_concat_shards(const uint8_t *slots, uint64_t stride, const in
 }
 
 // ======================================================================================
+// Stream-ordered flags between GPUs (kgm_stream_wait_flags / kgm_stream_signal_flags)
+// ======================================================================================
+// The ranks of a multi-GPU job tell each other "my shard of step k has landed in your memory"
+// and "slot set k is free again" through 32-bit counters in peer-mapped memory instead of a
+// collective per step: a one-warp kernel stores the values behind the poll kernel in stream
+// order, another one-warp kernel holds a stream until the counters it names have been reached.
+namespace kgm {
+namespace {
+
+struct FlagTargets { uint32_t *p[KGM_MAX_FLAG_TARGETS]; };
+
+__global__ void k_signal_flags(FlagTargets t, uint32_t n, uint32_t value) {
+  if (threadIdx.x < n) {
+    __threadfence_system();                          // everything this stream wrote before is visible first
+    // max, not store: the steps of one rank run on several streams and may finish out of order,
+    // and a counter must never go back
+    asm volatile("red.release.sys.global.max.u32 [%0], %1;" ::"l"(t.p[threadIdx.x]), "r"(value) : "memory");
+  }
+}
+
+__global__ void k_wait_flags(const uint32_t *flags, uint32_t n, uint32_t value) {
+  if (threadIdx.x < n) {
+    for (;;) {
+      uint32_t v;
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + threadIdx.x) : "memory");
+      if ((int32_t)(v - value) >= 0) break;          // counters only grow (wrap-safe comparison)
+      __nanosleep(200);
+    }
+  }
+}
+
+}  // namespace
+}  // namespace kgm
+
+extern "C" int kgm_stream_signal_flags(void *stream, uint32_t *const *targets, uint32_t n, uint32_t value) {
+  if (!targets || n == 0 || n > KGM_MAX_FLAG_TARGETS) return KGM_E_INVALID;
+  kgm::FlagTargets t{};
+  for (uint32_t i = 0; i < n; ++i) {
+    if (!targets[i] || (reinterpret_cast<uintptr_t>(targets[i]) & 3)) return KGM_E_INVALID;
+    t.p[i] = targets[i];
+  }
+  kgm::k_signal_flags<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(t, n, value);
+  return cudaGetLastError() == cudaSuccess ? KGM_OK : KGM_E_CUDA;
+}
+
+extern "C" int kgm_stream_wait_flags(void *stream, const uint32_t *flags, uint32_t n, uint32_t value) {
+  if (!flags || n == 0 || n > 32 || (reinterpret_cast<uintptr_t>(flags) & 3)) return KGM_E_INVALID;
+  kgm::k_wait_flags<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(flags, n, value);
+  return cudaGetLastError() == cudaSuccess ? KGM_OK : KGM_E_CUDA;
+}
+
+// ======================================================================================
 // Allocation-free tokenizer entry point (kgm_tokenize_gpu_noalloc, include/kgm.h)
 // ======================================================================================
 // Some processes that want the per-GPU samples of a batch are not allowed to take device
@@ -879,6 +931,7 @@ extern "C" int kgm_tokenize_gpu_noalloc(const uint8_t *gpu_csv, const uint64_t *
     k_tokenize_gpu_noalloc<<<blocks, TOK_THREADS, 0, s>>>(gpu_csv, gpu_off, n_docs, scratch, max_rows,
                                                           doc_row0, doc_nrows, doc_err, util, mem_used,
                                                           mem_total);
+    if (cudaGetLastError() != cudaSuccess) return KGM_E_CUDA;     // a launch that did not happen writes nothing
   }
   uint32_t head[2] = {0, 0};
   if (cudaMemcpyAsync(head, scratch, sizeof(head), cudaMemcpyDeviceToHost, s) != cudaSuccess ||

@@ -105,6 +105,12 @@ SIGNATURES = {
     "kgm_encode_finish": (C.c_int, [C.c_void_p, C.POINTER(KgmResult)]),
     "kgm_set_output_buffer": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
     "kgm_stream": (C.c_void_p, [C.c_void_p]),
+    "kgm_stream_signal_flags": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]),
+    "kgm_stream_wait_flags": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]),
+    "kgm_push_copy_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p,
+                                     C.c_uint32, C.POINTER(KgmResult)]),
+    "kgm_push_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32,
+                                C.POINTER(KgmResult)]),
     "kgm_output_capacity": (C.c_uint64, [C.c_void_p]),
     "kgm_fetch_result": (C.c_int, [C.c_void_p, C.POINTER(KgmResult)]),
     "kgm_get_timing": (C.c_int, [C.c_void_p, C.POINTER(KgmTiming)]),

@@ -214,6 +214,21 @@ class Monitor:
         _check(self._lib.kgm_set_output_buffer(self._ctx, C.c_void_p(dev_ptr or None), int(nbytes)),
                "kgm_set_output_buffer", self._ctx, self._lib)
 
+    def push_step(self, slot_ptr: int, slot_bytes: int, wait_flag: int, wait_value: int, signal_flag: int,
+                  signal_value: int, copy_engine=False) -> _ffi.KgmResult:
+        """kgm_push_step: one step of a multi-GPU job in one call -- wait for a counter, encode the
+        resident batch into ``slot_ptr``, bump a counter -- all on the context's stream.  With
+        ``copy_engine`` (kgm_push_copy_step) the kernel writes the context's own buffer and a copy
+        engine carries the result to the slot behind it."""
+        res = self._async_buf
+        fn = self._lib.kgm_push_copy_step if copy_engine else self._lib.kgm_push_step
+        rc = fn(self._ctx, C.c_void_p(slot_ptr), int(slot_bytes), C.c_void_p(wait_flag or None),
+                                     int(wait_value) & 0xFFFFFFFF, C.c_void_p(signal_flag or None),
+                                     int(signal_value) & 0xFFFFFFFF, C.byref(res))
+        if rc != _ffi.KGM_OK:
+            _check(rc, "kgm_push_step", self._ctx, self._lib)
+        return res
+
     @property
     def stream_handle(self) -> int:
         """The cudaStream_t the context queues its work on (kgm_stream)."""

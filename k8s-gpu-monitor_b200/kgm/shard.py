@@ -82,9 +82,10 @@ class ShardGather:
 
     ``push`` (CUDA, ``push=True``, needs CUDA IPC between the ranks): the gathering GPU owns
     fixed-stride slots that every rank maps; the library's kernels write each shard and its
-    {n_bytes, n_lines} header straight into its slot while they encode
-    (``push_slot`` / ``push_wait`` / ``start_push``), NCCL carries a 4-byte all-reduce per
-    step.  With ``rotate_root`` step k is gathered on rank k mod world.
+    {n_bytes, n_lines} header straight into its slot while they encode, and the ranks tell each
+    other what has landed through counters in the same mapped memory (``push_step``: one
+    library call per step, no collective).  With ``rotate_root`` step k is gathered on rank
+    k mod world.
 
     ``slots`` (CUDA otherwise): the shards travel as fixed-size NCCL transfers into the
     fixed-stride slots -- ``start_device``: one all-gather straight out of the library's
@@ -125,15 +126,20 @@ class ShardGather:
             if push:
                 self._open_push()
 
+    FLAG_BYTES = 256                                 # per gathering rank: landed[world] (u32) at 0, ack (u32) at 128
+
     def _open_push(self):
-        """Push mode: every gathering rank owns PUSH_SETS sets of fixed-stride slots and every
-        other rank maps them (CUDA IPC, NVLink peer access); the library's kernels then write
-        each shard and its size header straight into its slot on the step's gathering rank
-        while they encode (kgm_set_output_buffer), and the only per-step collective is a tiny
-        all-reduce that tells the gathering rank the step has landed and the writers that an
-        older set is free again.  With ``rotate_root`` the gathering rank of step k is k mod
-        world: every step's concatenation still lands whole on one GPU, but the ingress of
-        (world - 1) shards per step is spread over all NVLink ports instead of one."""
+        """Push mode: every gathering rank owns PUSH_SETS sets of fixed-stride slots plus a block
+        of counters, and every other rank maps them (CUDA IPC, NVLink peer access).  A step on
+        a rank is ONE library call (kgm_push_step) that queues, on the context's stream: wait
+        for a counter, the poll kernel writing the shard and its size header straight into its
+        slot on the step's gathering rank (kgm_set_output_buffer), and a store of "landed" to
+        that rank's counter block.  The gathering rank of a step waits for all `world` landed
+        counters on a stream of its own and then bumps its `ack` counter; writers read it to
+        know how far everybody has come.  No collective runs per step.  With ``rotate_root``
+        the gathering rank of step k is k mod world: every step's concatenation still lands
+        whole on one GPU, but the ingress of (world - 1) shards per step is spread over all
+        NVLink ports instead of one."""
         ok = torch.ones(1, dtype=torch.int32, device=self.device)
         # How far a rank may run ahead of the last step that has landed everywhere.  With a
         # rotating root the windows differ by rank (rank r: world - r + 1 steps): every rank
@@ -141,8 +147,9 @@ class ShardGather:
         # write to `world` different gathering GPUs instead of all to the same one.
         skew = self.rotate_root and os.environ.get("KGM_PUSH_SKEW", "1") == "1"
         self.push_ahead = (self.world - self.rank + 1) if skew else 3
-        self.PUSH_SETS = (self.world + 2) if skew else 4
-        total = self.PUSH_SETS * self.world * self.stride
+        self.PUSH_SETS = 4                           # a set is reused when its step is > world + 1 steps back
+        self.flag_off = self.PUSH_SETS * self.world * self.stride
+        total = self.flag_off + self.FLAG_BYTES
         roots = range(self.world) if self.rotate_root else (0,)
         self.push_bufs = {}
         try:
@@ -171,63 +178,62 @@ class ShardGather:
         if int(ok.item()) != 1:
             self.push_bufs = {}
             return
-        self.flag = torch.zeros(1, dtype=torch.int32, device=self.device)
-        self.push_fin = {}                           # step -> event after its all-reduce
-        self.push_step = 0
+        torch.cuda.synchronize(self.device)          # the zeroed counters are in place before anybody writes
+        dist.barrier(group=self.group)
+        self.push_step_no = 0
         self.last_root = 0
+        # who carries a shard to the gathering GPU: a copy engine behind the poll kernel (the
+        # kernel then writes local memory only and never waits for another GPU; default), or the
+        # poll kernel's own stores into the peer slot (KGM_PUSH_KERNEL_STORES=1)
+        self.copy_engine = os.environ.get("KGM_PUSH_KERNEL_STORES", "0") != "1"
         self.mode = "push"
 
     def push_root(self, k=None):
         """The rank that gathers step k (default: the next step)."""
-        k = self.push_step if k is None else k
+        k = self.push_step_no if k is None else k
         return k % self.world if self.rotate_root else 0
 
+    def _uses(self, k):
+        return k // self.world if self.rotate_root else k          # how often step k's root has gathered before
+
     def _push_offset(self, k):
-        uses = k // self.world if self.rotate_root else k          # how often this root has gathered before
-        return (uses % self.PUSH_SETS) * self.world * self.stride
+        return (self._uses(k) % self.PUSH_SETS) * self.world * self.stride
 
-    def push_slot(self):
-        """(device pointer, bytes) of this rank's slot for the NEXT step: hand it to
-        kgm_set_output_buffer, wait for ``push_wait()`` on the producer's stream, queue the
-        encode, then call ``start_push``."""
-        k = self.push_step
-        buf = self.push_bufs[self.push_root(k)]
-        return buf.data_ptr() + self._push_offset(k) + self.rank * self.stride, self.stride
+    def _flag_ptr(self, root, idx):
+        return self.push_bufs[root].data_ptr() + self.flag_off + 4 * idx
 
-    def push_wait(self):
-        """The event after which the next step's slot may be written again (None: at once):
-        the all-reduce of step k - push_ahead.  The set step k writes was last used at least
-        PUSH_SETS steps earlier; its gathering rank entered the all-reduce of the step after
-        that behind whatever it did with the set, and the awaited all-reduce completed long
-        before step k starts, so consecutive steps still overlap."""
-        return self.push_fin.get(self.push_step - self.push_ahead)
-
-    def start_push(self, producer):
-        """After the encode of this step has been queued on ``producer``: tells every rank,
-        on the device, that this rank's shard has landed.  Returns the event after which the
-        step's gathering rank holds every shard."""
-        k = self.push_step
-        self.push_step += 1
+    def push_step(self, mon):
+        """One step: queues on ``mon``'s stream (kgm_push_step) the wait for the step
+        ``push_ahead`` back to have landed everywhere, the encode of ``mon``'s resident batch
+        into this rank's slot on the step's gathering rank, and the "landed" store.  Returns
+        the library's (unsized) device result; finish with ``mon.encode_finish()``."""
+        import ctypes as C
+        k = self.push_step_no
+        self.push_step_no += 1
         self.k += 1
-        ready = torch.cuda.Event()
-        ready.record(producer)
-        with torch.cuda.stream(self.stream):
-            self.stream.wait_event(ready)
-            dist.all_reduce(self.flag, group=self.group)
-            fin = torch.cuda.Event()
-            fin.record(self.stream)
-        self.push_fin[k] = fin
-        self.push_fin.pop(k - 2 * self.PUSH_SETS, None)
+        root, uses = self.push_root(k), self._uses(k)
+        slot = self.push_bufs[root].data_ptr() + self._push_offset(k) + self.rank * self.stride
+        j = k - self.push_ahead
+        wait_flag, wait_value = (self._flag_ptr(self.push_root(j), 32), self._uses(j) + 1) if j >= 0 else (0, 0)
+        res = mon.push_step(slot, self.stride, wait_flag, wait_value, self._flag_ptr(root, self.rank), uses + 1,
+                            copy_engine=self.copy_engine)
         self._packed = False
-        self.pending[k & 1] = [_EventWork(fin)]
-        self.last_root = self.push_root(k)
-        if self.rank == self.last_root:
+        self.last_root = root
+        if self.rank == root:
+            # this rank gathers the step: all shards landed -> acknowledge, on the gather's own stream
+            st = C.c_void_p(self.stream.cuda_stream)
+            rc = self._lib.kgm_stream_wait_flags(st, C.c_void_p(self._flag_ptr(root, 0)), self.world,
+                                                 (uses + 1) & 0xFFFFFFFF)
+            ack = (C.c_void_p * 1)(self._flag_ptr(root, 32))
+            rc = rc or self._lib.kgm_stream_signal_flags(st, ack, 1, (uses + 1) & 0xFFFFFFFF)
+            if rc != 0:
+                raise RuntimeError("flag kernels failed: %d" % rc)
             base = self._push_offset(k)
             self.slots = self.push_bufs[self.rank][base:base + self.world * self.stride]
             self.all_slots = self.slots
             if self.final is None:
                 self.final = torch.empty(self.cap * self.world, dtype=torch.uint8, device=self.device)
-        return fin
+        return res
 
     def _init_slots(self):
         """CUDA, default mode: fixed-stride slots on rank 0, sizes stay on the device."""
