@@ -141,12 +141,23 @@ class ShardGather:
         whole on one GPU, but the ingress of (world - 1) shards per step is spread over all
         NVLink ports instead of one."""
         ok = torch.ones(1, dtype=torch.int32, device=self.device)
-        # How far a rank may run ahead of the last step that has landed everywhere.  With a
-        # rotating root the windows differ by rank (rank r: world - r + 1 steps): every rank
-        # runs as far ahead as it may, so the ranks settle one step apart and at any moment
-        # write to `world` different gathering GPUs instead of all to the same one.
+        # who carries a shard to the gathering GPU: a copy engine behind the poll kernel (the
+        # kernel then writes local memory only and never waits for another GPU; default), or the
+        # poll kernel's own stores into the peer slot (KGM_PUSH_KERNEL_STORES=1)
+        self.copy_engine = os.environ.get("KGM_PUSH_KERNEL_STORES", "0") != "1"
+        # How far a rank may run ahead of the last step that has landed everywhere.  A whole
+        # step lands on ONE GPU (7 x 46 MB at N=8: 0.36 ms of its NVLink ingress), so several
+        # steps, bound for different gathering GPUs, must be in flight at once.  Copy engines:
+        # 2 x world steps for every rank (each context's copy stream carries one).  Kernel
+        # stores with a rotating root: windows that differ by rank (rank r: world - r + 1 steps),
+        # so that the ranks settle one step apart and write to `world` different GPUs.
         skew = self.rotate_root and os.environ.get("KGM_PUSH_SKEW", "1") == "1"
-        self.push_ahead = (self.world - self.rank + 1) if skew else 3
+        if self.copy_engine and self.rotate_root:
+            self.push_ahead = 2 * self.world
+        else:
+            self.push_ahead = (self.world - self.rank + 1) if skew else 3
+        if os.environ.get("KGM_PUSH_AHEAD"):         # (experiments) at most (PUSH_SETS - 1) x world: a set must not be overtaken
+            self.push_ahead = max(1, min(int(os.environ["KGM_PUSH_AHEAD"]), 3 * self.world if self.rotate_root else 3))
         self.PUSH_SETS = 4                           # a set is reused when its step is > world + 1 steps back
         self.flag_off = self.PUSH_SETS * self.world * self.stride
         total = self.flag_off + self.FLAG_BYTES
@@ -182,10 +193,6 @@ class ShardGather:
         dist.barrier(group=self.group)
         self.push_step_no = 0
         self.last_root = 0
-        # who carries a shard to the gathering GPU: a copy engine behind the poll kernel (the
-        # kernel then writes local memory only and never waits for another GPU; default), or the
-        # poll kernel's own stores into the peer slot (KGM_PUSH_KERNEL_STORES=1)
-        self.copy_engine = os.environ.get("KGM_PUSH_KERNEL_STORES", "0") != "1"
         self.mode = "push"
 
     def push_root(self, k=None):

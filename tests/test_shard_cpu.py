@@ -126,7 +126,7 @@ def test_push_mode_slot_arithmetic():
         for rotate in (False, True):
             stride = 4096
             sets = 4
-            ahead = [(world - r + 1) if rotate else 3 for r in range(world)]
+            ahead = [2 * world if rotate else 3 for r in range(world)]     # the widest window shard.py uses
             gs = []
             for r in range(world):
                 g = ShardGather.__new__(ShardGather)
