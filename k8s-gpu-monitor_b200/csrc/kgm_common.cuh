@@ -160,6 +160,7 @@ struct GpuRowScan {
   uint32_t sig;           // of them, from the first non-zero one on
   uint64_t val;
   bool cell_first, lead, over;
+  uint32_t quote;         // cell 0 only: 0 = not quoted, 1 = inside "...", 2 = closed, waiting for the ','
 
   KGM_HDM void begin(uint32_t row_off, uint32_t row_end) {
     r = GpuRow();
@@ -167,7 +168,7 @@ struct GpuRowScan {
     r.key_hash = hash_init();
     r.power = NONE32;
     base = row_off; ci = 0; len = 0; pending_cr = 0; ndig = 0; sig = 0; val = 0;
-    cell_first = true; lead = true; over = false;
+    cell_first = true; lead = true; over = false; quote = 0;
   }
   KGM_HDM uint32_t sat32() const { return (over || sig > 10 || val > 0xffffffffull) ? 0xffffffffu : (uint32_t)val; }
   KGM_HDM void close_cell(uint32_t p) {
@@ -188,8 +189,31 @@ struct GpuRowScan {
     if (pending_cr) { r.flags |= RF_CR; pending_cr = 0; }
     len = p + 1;
     if (c >= 0x80u) r.flags |= RF_HIBYTE;
-    if (c == ',') { close_cell(p); ++ci; cell_first = true; return; }
-    if (cell_first) { if (c == '"') r.flags |= RF_QUOTE; cell_first = false; }
+    // csv.reader: a first cell "..." is the text between the quotes (gpu.py:47).  Taken here when
+    // the quotes close right in front of the delimiter and hold no quote, comma or line end;
+    // every other use of a leading quote stays flagged.
+    if (quote == 1) {
+      if (c == '"') { quote = 2; r.cell_end[0] = (uint16_t)p; if (lead) r.key_lo = (uint16_t)p; return; }
+      if (c == ',') r.flags |= RF_QUOTE;             // a delimiter inside the quotes is content to csv
+    } else if (quote == 2) {
+      if (c != ',') r.flags |= RF_QUOTE;             // csv appends what follows the closing quote
+    }
+    if (c == ',' && quote != 1) {
+      if (quote == 2) {                              // cell 0 ended at its closing quote
+        if (p > 65535u) r.flags |= RF_LONG;
+        quote = 0; ndig = 0; sig = 0; val = 0; over = false;
+      } else {
+        close_cell(p);
+      }
+      ++ci; cell_first = true; return;
+    }
+    if (cell_first) {
+      cell_first = false;
+      if (c == '"') {
+        if (ci == 0) { quote = 1; return; }
+        r.flags |= RF_QUOTE;
+      }
+    }
     if (ci == 0) {
       if (lead && is_str_space(c)) return;
       if (lead) { r.key_lo = (uint16_t)p; lead = false; }
@@ -202,7 +226,9 @@ struct GpuRowScan {
   }
   KGM_HDM void finish() {
     if (len == 0) { r.ncells = 0; return; }       // blank line: csv yields [] (KeyError gpu.py:51)
-    close_cell(len);
+    if (quote == 1) r.flags |= RF_QUOTE;            // the quoted cell runs on into the next line
+    if (quote == 2) { quote = 0; ndig = 0; sig = 0; val = 0; over = false; }   // row = one quoted cell
+    else close_cell(len);
     r.ncells = (uint8_t)(ci + 1 > 255u ? 255u : ci + 1);
   }
 };
@@ -244,7 +270,9 @@ struct ProcRowScan {
     if (c == '\r') { ++pending_cr; return; }
     if (pending_cr) { r.flags |= RF_CR; pending_cr = 0; }
     len = p + 1;
-    if (c >= 0x80u) r.flags |= RF_HIBYTE;
+    // process_name (cell 1) is only copied, minus its ' ' characters (gpu.py:203): its UTF-8
+    // bytes pass through.  Elsewhere a non-ASCII byte could be whitespace or a digit to Python.
+    if (c >= 0x80u && ci != 1) r.flags |= RF_HIBYTE;
     if (c == ',') { close_cell(p); ++ci; cell_first = true; return; }
     if (cell_first) { if (c == '"') r.flags |= RF_QUOTE; cell_first = false; }
     if (ci == 0) {

