@@ -5,8 +5,12 @@
 // -4 <= exp10 < 16 and d[.ddd]e+XX otherwise, with ".0" appended to integers.  This
 // header produces those bytes on the device (and, for the CPU unit tests, on the host).
 //
-// Digit generation is a Ryu-class algorithm: scale the three neighbours of the value by a
-// 128-bit fixed-point power of ten, then strip digits while they stay distinguishable.
+// Digit generation follows Ulf Adams' Ryu algorithm ("Ryu: fast float-to-string conversion",
+// PLDI 2018; reference implementation github.com/ulfjack/ryu, dual-licensed Apache-2.0 /
+// Boost-1.0): scale the three neighbours of the value by a 128-bit fixed-point power of five,
+// then strip digits while they stay distinguishable.  The helper names and multiplier constants
+// (pow5_bits, log10_pow2, log10_pow5, mul_shift) are Ryu's; the code was restated for this
+// library (device-compatible, non-negative finite inputs only), not copied from a release.
 // Tables come from gen/make_d2s_tables.py.  Only finite, non-negative inputs occur on
 // this path (used*100.0/total with used,total < 2^64, total != 0).
 #pragma once

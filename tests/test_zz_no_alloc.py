@@ -8,10 +8,15 @@ through the C ABI twice in a row (the second call on a different, smaller batch,
 anything left in the shared array by the first call would show) and checks what it
 decodes -- gpu_util, mem_used, mem_total per sample -- against what the ordinary entry point
 (kgm_encode_batch) prints for the same texts.  The values are integers: the comparison is
-exact, like every other parity test here.
+exact, like every other parity test here.  The same values are also derived from the text
+with the oracle's own rules (csv.reader cells, poll_oracle.digits_of), and a batch with a
+damaged document and a repeated uuid pins what the entry point reports for those: raw rows in
+text order (no last-row-wins dictionary) and a per-document parse status.
 
 The file name makes pytest collect it last; it also passes when run alone.
 """
+import csv
+import io
 import re
 
 import numpy as np
@@ -41,7 +46,19 @@ def _reference_samples(mon, rp):
     return out
 
 
-def _noalloc_samples(lib, rp, max_rows):
+def _oracle_samples(gpu_texts):
+    """The same three integers per --query-gpu row, from the text alone: cells as csv.reader
+    splits them (gpu.py:47), digits as gpu.py:133-134,138 strip them."""
+    from oracle import poll_oracle
+    out = []
+    for text in gpu_texts:
+        rows = list(csv.reader(io.StringIO(text)))[1:]                   # header dropped blind (gpu.py:67-68)
+        dig = lambda row, i: poll_oracle.digits_of(row[i]) if i < len(row) else ""
+        out.append([(int(dig(r, 1) or 0), int(dig(r, 4) or 0), int(dig(r, 3) or 0)) for r in rows])
+    return out
+
+
+def _noalloc_samples(lib, rp, max_rows, want_err=None):
     import torch
     dev = torch.device("cuda", 0)
     texts = [t.encode() for t in rp.gpu_texts]
@@ -67,7 +84,10 @@ def _noalloc_samples(lib, rp, max_rows):
         return rc, None
     row0, nrows, err = row0.cpu().numpy(), nrows.cpu().numpy(), err.cpu().numpy()
     util, used, total = util.cpu().numpy(), used.cpu().numpy(), total.cpu().numpy()
-    assert not err.any()
+    if want_err is None:
+        assert not err.any()
+    else:
+        assert err.tolist() == want_err
     out = []
     for d in range(n):
         a, k = int(row0[d]), int(nrows[d])
@@ -90,10 +110,30 @@ def test_noalloc_tokenizer_matches_the_ordinary_entry_point_twice_in_a_row():
         want_first = _reference_samples(mon, first)
         want_second = _reference_samples(mon, second)
     rc, got = _noalloc_samples(lib, first, 256)
-    assert rc == 0 and got == want_first
+    assert rc == 0 and got == want_first == _oracle_samples(first.gpu_texts)
     rc, got = _noalloc_samples(lib, second, 64)          # straight after, smaller batch
-    assert rc == 0 and got == want_second
+    assert rc == 0 and got == want_second == _oracle_samples(second.gpu_texts)
     assert sum(len(r) for r in want_first) == 96 and sum(len(r) for r in want_second) == 18
+
+
+def test_noalloc_tokenizer_reports_raw_rows_and_parse_status():
+    """A blank line inside a text is a parse-level failure of that document (KeyError at
+    gpu.py:51); a repeated uuid is NOT folded (the entry point returns rows, the dictionary
+    semantics of gpu.py:54 belong to the full path); "[N/A]" cells decode to 0."""
+    pytest.importorskip("torch")
+    lib = _ffi.load()
+    rp = replay.make_replay(seed=34, nodes=1, ticks=3, gpus=4, containers=1, procs_per_container=1)
+    rows = rp.gpu_texts[1].split("\n")
+    rp.gpu_texts[1] = "\n".join(rows[:2] + [""] + rows[2:])             # blank line after the first row
+    rows = rp.gpu_texts[2].split("\n")
+    uuid = rows[1].split(",")[0]
+    rp.gpu_texts[2] = "\n".join(rows[:3] + ["%s, [N/A], [N/A], 100 MiB, 7 MiB, 93 MiB" % uuid] + rows[3:])
+    rc, got = _noalloc_samples(lib, rp, 64, want_err=[0, _ffi.DOC_KEY_ERROR, 0])
+    assert rc == 0
+    want = _oracle_samples(rp.gpu_texts)
+    assert got[0] == want[0] and got[2] == want[2]
+    assert len(got[2]) == 5 and got[2][2] == (0, 7, 100)                 # the repeated uuid stays a row of its own
+    assert [r for r in got[1] if r != (0, 0, 0)] == want[1][:1] + want[1][2:]   # the blank line is a row without cells
 
 
 def test_noalloc_tokenizer_refuses_what_does_not_fit():
