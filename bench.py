@@ -113,23 +113,78 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def build_workload(config, rank):
-    from kgm import replay
+def _replay_of_nodes(replay, seed, node_ids, ticks, tick0=0, **node_kw):
+    """A replay of the given hosts (global host numbers), all ticks of a host together."""
+    snaps = [replay.make_node(seed, n, **node_kw) for n in node_ids]
+    doc_node, doc_tick, gt, at = [], [], [], []
+    for i, (n, snap) in enumerate(zip(node_ids, snaps)):
+        for t in range(ticks):
+            a, b2 = replay.make_texts(seed, n, snap, tick0 + t)
+            doc_node.append(i); doc_tick.append(tick0 + t); gt.append(a); at.append(b2)
+    return replay.Replay(seed, snaps, np.asarray(doc_node, np.int32), np.asarray(doc_tick, np.int32), gt, at)
+
+
+def build_workload(config, rank, world=1, variant=0):
+    """(replay, fleet entries, shard info) of this rank.
+      config1/2  every rank its own fleet (weak scaling; `rank` numbers the fleet)
+      config3    ONE fleet of 1000 hosts, 40 of the 600 ticks, hosts partitioned over the ranks by
+                 kgm/shard.py assign_hosts (strong scaling)
+      config4    12 500 hosts, one window of 4 ticks (`variant` = which window); the ranks' hosts by
+                 assign_hosts; the hour is 900 such windows, streamed: encoded, handed on, discarded
+      config5    skewed fleet (Zipf pods per host, short-lived pods, MIG hosts), hosts partitioned by
+                 assign_hosts with their text bytes as weights"""
+    from kgm import replay, shard
     from kgm.fleet import node_entry
-    kw = dict(replay.CONFIGS[config])
-    if config == "config3":
-        # one streamed batch of configs[2]: all 1000 nodes x 40 ticks (of the 600), built from 4
-        # distinct ticks replicated 10 times so that host-side generation stays in seconds
-        kw["ticks"] = 4
-        base = replay.make_replay(seed=0, node_base=rank * kw["nodes"], **kw)
-        order = [n * 4 + (t % 4) for t in range(40) for n in range(kw["nodes"])]
-        rp = replay.Replay(base.seed, base.nodes, base.doc_node[order],
-                           np.asarray([t for t in range(40) for _ in range(kw["nodes"])], np.int32),
-                           [base.gpu_texts[d] for d in order], [base.apps_texts[d] for d in order])
-    else:
+    info = None
+    if config in ("config1", "config2"):
+        kw = dict(replay.CONFIGS[config])
         rp = replay.make_replay(seed=0, node_base=rank * kw["nodes"], **kw)
+    elif config == "config3":
+        kw = dict(replay.CONFIGS["config3"])
+        nodes, distinct, span = kw.pop("nodes"), 4, 40
+        kw.pop("ticks")
+        names = ["k8s-node-gpu-%05d" % n for n in range(nodes)]
+        owner = shard.assign_hosts(names, [1] * nodes, world)
+        mine = [n for n in range(nodes) if owner[n] == rank]
+        base = _replay_of_nodes(replay, 0, mine, distinct, **kw)
+        # tick-major inside the batch; 4 distinct ticks replicated to 40 so that host-side
+        # generation stays in seconds
+        order = [i * distinct + (t % distinct) for t in range(span) for i in range(len(mine))]
+        rp = replay.Replay(base.seed, base.nodes, base.doc_node[order],
+                           np.asarray([t for t in range(span) for _ in mine], np.int32),
+                           [base.gpu_texts[d] for d in order], [base.apps_texts[d] for d in order])
+        info = {"hosts_total": nodes, "hosts_this_rank": len(mine), "partition": "assign_hosts, equal weights"}
+    elif config == "config4":
+        nodes, window = 12500, 4
+        names = ["k8s-node-gpu-%05d" % n for n in range(nodes)]
+        owner = shard.assign_hosts(names, [1] * nodes, 8)          # always the 8-GPU partition: rank r takes part r,
+        mine = [n for n in range(nodes) if owner[n] == rank]       # so a rank's work does not change with the world size
+        rp = _replay_of_nodes(replay, 0, mine, window, tick0=variant * window, gpus=8, containers=8,
+                              procs_per_container=4)
+        info = {"hosts_total": nodes, "hosts_this_rank": len(mine), "window_ticks": window,
+                "windows_per_hour": 3600 // window, "partition": "assign_hosts, equal weights (one eighth per rank)"}
+    elif config == "config5":
+        full = replay.make_skewed_replay(seed=5, hosts=240, epochs=2, ticks_per_epoch=6, max_containers=160)
+        hosts = sorted({s.name for s in full.nodes})
+        weight = {h: 0 for h in hosts}
+        for d in range(full.n_docs):
+            weight[full.nodes[int(full.doc_node[d])].name] += len(full.gpu_texts[d]) + len(full.apps_texts[d])
+        owner = dict(zip(hosts, shard.assign_hosts(hosts, [weight[h] for h in hosts], world)))
+        keep = [d for d in range(full.n_docs) if owner[full.nodes[int(full.doc_node[d])].name] == rank]
+        used = sorted({int(full.doc_node[d]) for d in keep})
+        remap = {n: i for i, n in enumerate(used)}
+        rp = replay.Replay(full.seed, [full.nodes[n] for n in used],
+                           np.asarray([remap[int(full.doc_node[d])] for d in keep], np.int32),
+                           full.doc_tick[keep], [full.gpu_texts[d] for d in keep], [full.apps_texts[d] for d in keep])
+        loads = [sum(w for h, w in weight.items() if owner[h] == r) for r in range(world)]
+        info = {"hosts_total": len(hosts), "hosts_this_rank": sum(1 for h in hosts if owner[h] == rank),
+                "partition": "assign_hosts, text bytes per host as weights",
+                "input_bytes_max_over_mean": max(loads) / (sum(loads) / world),
+                "largest_host_share": max(weight.values()) / sum(weight.values())}
+    else:
+        raise ValueError(config)
     entries = [node_entry(s.name, s.ps_text, s.stats_text, s.top, s.inspect, s.smi_list) for s in rp.nodes]
-    return rp, entries
+    return rp, entries, info
 
 
 # ---------------------------------------------------------------------------------------
@@ -174,7 +229,7 @@ def cpu_baseline_single_core(rp, gpu_result, budget_s=12.0):
         spent += time.perf_counter() - t0
         docs += 1
         samples += rp.gpu_texts[d].count("\n") - 1
-        if gpu_result is not None and (err is not None or gpu_result.lines(d) != lines):
+        if gpu_result is not None and (gpu_result.error(d) != err or gpu_result.lines(d) != lines):
             mismatches += 1
         if spent > budget_s:
             break
@@ -193,7 +248,7 @@ def run_reference_arm(args):
     if rank != 0:
         return 0
     import multiprocessing as mp
-    rp, _ = build_workload(args.config, 0)
+    rp, _, _ = build_workload(args.config, 0)
     _RP = rp
     _, kind, what = _cpu_poll()
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
@@ -235,7 +290,12 @@ def workload_name(config):
             "config2": "configs[1]: 64-node fleet batch, 512 GPUs, 2048 pods, 60 ticks at 1 Hz "
                        "(3840 documents, 30720 samples) per GPU",
             "config3": "configs[2] streamed: one batch of 1k nodes, 8k GPUs, 40k processes x 40 of the 600 ticks "
-                       "(40000 documents, 320000 samples; 4 distinct ticks replicated)"}[config]
+                       "(40000 documents, 320000 samples; 4 distinct ticks replicated), hosts partitioned over the ranks",
+            "config4": "configs[3] streamed: 12.5k nodes, 100k GPUs, windows of 4 ticks (900 per hour; 3 distinct "
+                       "windows resident per rank, visited in turn), one eighth of the hosts per rank",
+            "config5": "configs[4] stress: 240 hosts, Zipf(1.2) pods per host up to 160, pods replaced between "
+                       "epochs, every third host MIG (utilization [N/A], idle pods see MIG uuids), hosts "
+                       "partitioned over the ranks by text bytes"}[config]
 
 
 # ---------------------------------------------------------------------------------------
@@ -262,10 +322,17 @@ def run_kgm_arm(args):
     device = torch.device("cuda", local_rank)
 
     # ---- ROTATE distinct batches of the workload per rank, each resident in its own context ----
-    rotate = 1 if args.config == "config3" else ROTATE
+    # resident batches per rank, visited in turn: configs[1] 4 fleets (4 x 60 MB > L2); the large
+    # configs are larger than L2 by themselves (config4: 3 distinct windows of the hour)
+    sharded = args.config in ("config3", "config4", "config5")
+    rotate = {"config3": 1, "config4": 3, "config5": 4}.get(args.config, ROTATE)
     mons, batches, rps = [], [], []
+    shard_info = None
     for v in range(rotate):
-        rp, entries = build_workload(args.config, rank * rotate + v)
+        if sharded:
+            rp, entries, shard_info = build_workload(args.config, rank, world, variant=v if args.config == "config4" else 0)
+        else:
+            rp, entries, _ = build_workload(args.config, rank * rotate + v)
         mon = monitor.Monitor(local_rank)
         mon.set_pipeline({"fused": 0, "staged": 1, "fused-generic": 2, "fused-v1": 3, "fused-v2": 4}[args.pipeline])
         mon.load_fleet(entries)
@@ -517,9 +584,10 @@ def run_kgm_arm(args):
         line = {
             "metric": METRIC, "value": samples_total / (step_ms * args.steps * 1e-3), "unit": "samples/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+            "higher_is_better": True, "scaling": "strong" if args.config in ("config3", "config5") else "weak",
+            "vs_baseline": None, "dtype": "u8",
             "data": "synthetic",
-            "config": {"workload": workload_name(args.config), "docs_per_gpu": b0.n_docs,
+            "config": {"workload": workload_name(args.config), "docs_per_gpu": b0.n_docs, "shard": shard_info,
                        "samples_per_gpu": samples_step[0], "lines_per_gpu": n_lines,
                        "input_bytes_per_gpu": b0.gpu_bytes + b0.apps_bytes,
                        "output_bytes_per_gpu": n_bytes,
@@ -597,7 +665,7 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="kgm", choices=["kgm", "reference"])
-    ap.add_argument("--config", default="config2", choices=["config1", "config2", "config3"])
+    ap.add_argument("--config", default="config2", choices=["config1", "config2", "config3", "config4", "config5"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--pipeline", default="fused", choices=["fused", "staged", "fused-generic", "fused-v1", "fused-v2"])
     args = ap.parse_args()

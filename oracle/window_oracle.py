@@ -96,3 +96,26 @@ def windows(docs, window_ticks):
             a = g[m]
             a["mean"] = a["sum"] / a["count"] if a["count"] else 0.0
     return dict(sorted(groups.items()))
+
+
+def lines(groups, host_of_node, cid_of_container, window_ticks, t0_ns=0, tick_ns=10 ** 9):
+    """The groups of windows() in line form (PARITY UNPINNED like the rest of this file):
+    node_gpu_w / pod_gpu_w measurements with explicit nanosecond timestamps (the window's last
+    tick), mirroring what the dashboards compute in InfluxQL over node_gpu / pod_gpu fields
+    (gpu.py:136-143,206-216)."""
+    out = []
+    for (kind, entity, gid, window), g in groups.items():
+        fields = []
+        for m, name in (("gpu_util", "gpu_util"), ("mem", "mem_used"), ("power", "power")):
+            a = g[m]
+            if a["count"]:
+                fields += ["%s_min=%d" % (name, a["min"]), "%s_max=%d" % (name, a["max"]),
+                           "%s_mean=%s" % (name, repr(a["mean"])), "%s_last=%d" % (name, a["last"])]
+        fields.append("samples=%di" % g["count"])
+        gid_s = "None" if gid == NONE_ID else str(gid)
+        ts = t0_ns + ((window + 1) * window_ticks - 1) * tick_ns
+        host = host_of_node[g["node"]]
+        head = ("node_gpu_w,host=%s,gpu_id=%s" % (host, gid_s) if kind == 0 else
+                "pod_gpu_w,host=%s,containerid=%s,gpu_id=%s" % (host, cid_of_container[entity], gid_s))
+        out.append("%s %s %d" % (head, ",".join(fields), ts))
+    return out

@@ -63,6 +63,12 @@ def test_windows_of_a_clean_fleet_match_the_oracle(mon, window_ticks, power):
     got = mon.window_reduce(window_ticks)
     want = _oracle_groups(rp, entries, rp.gpu_texts, rp.apps_texts, rp.doc_node, rp.doc_tick, window_ticks)
     _compare(got, want)
+    # ... and in line form (node_gpu_w / pod_gpu_w with nanosecond timestamps)
+    from kgm import sink
+    hosts = [s.name for s in rp.nodes]
+    cids = [c.cid for e in entries for c in e.containers]
+    assert sink.window_lines(got, hosts, cids, window_ticks, t0_ns=1_700_000_000 * 10 ** 9) == \
+        window_oracle.lines(want, hosts, cids, window_ticks, t0_ns=1_700_000_000 * 10 ** 9)
     if power:
         assert int(got["power_count"].sum()) > 0
     else:
