@@ -325,7 +325,7 @@ def run_kgm_arm(args):
     # resident batches per rank, visited in turn: configs[1] 4 fleets (4 x 60 MB > L2); the large
     # configs are larger than L2 by themselves (config4: 3 distinct windows of the hour)
     sharded = args.config in ("config3", "config4", "config5")
-    rotate = {"config3": 1, "config4": 3, "config5": 4}.get(args.config, ROTATE)
+    rotate = {"config3": 2, "config4": 3, "config5": 4}.get(args.config, ROTATE)
     mons, batches, rps = [], [], []
     shard_info = None
     for v in range(rotate):
