@@ -124,7 +124,7 @@ struct kgm_ctx {
   // k_poll2 (one warp per document)
   bool poll2_ok = false;                   // the current batch fits k_poll2's slices
   Poll2Params poll2{};
-  DevBuf f_node_fast2, f_nslot_off, f_tslot_off, f_slot_pool;
+  DevBuf f_node_fast2, f_nslot_off, f_tslot_off, f_slot_pool, f_ca2;
   uint32_t p2_max_nc = 1, p2_max_slot = 64, p2_max_fixed = 0, p2_max_idle = 0, p2_any = 0;
   std::vector<uint8_t> h_node_fast2;
   bool all_nodes_fast2 = false;
@@ -982,7 +982,7 @@ void kgm_destroy(kgm_ctx *ctx) {
                    &ctx->w_status, &ctx->w_doc_line_off, &ctx->w_doc_byte_off, &ctx->w_totals,
                    &ctx->w_line_off, &ctx->w_out, &ctx->w_flush, &ctx->w_ticket, &ctx->w_scan,
                    &ctx->f_node_fast, &ctx->f_tb_off, &ctx->f_tb_len, &ctx->f_tb_pool, &ctx->f_pid16,
-                   &ctx->f_vis_hash2, &ctx->f_node_fast2, &ctx->f_nslot_off, &ctx->f_tslot_off, &ctx->f_slot_pool,
+                   &ctx->f_vis_hash2, &ctx->f_node_fast2, &ctx->f_nslot_off, &ctx->f_tslot_off, &ctx->f_slot_pool, &ctx->f_ca2,
                    &ctx->w_win_samples, &ctx->w_win_groups, &ctx->w_win_temp};
   for (DevBuf *b : dev) b->release();
   HostBuf *host[] = {&ctx->h_small, &ctx->h_lines, &ctx->h_line_off, &ctx->h_doc_line_off, &ctx->h_status,
@@ -1189,6 +1189,11 @@ int kgm_load_fleet(kgm_ctx *ctx, const kgm_fleet *fl) {
   if ((rc = upload(ctx, ctx->f_nslot_off, nslot_off.data(), nslot_off.size()))) return rc;
   if ((rc = upload(ctx, ctx->f_tslot_off, tslot_off.data(), tslot_off.size()))) return rc;
   if ((rc = upload(ctx, ctx->f_slot_pool, slot_pool.data(), slot_pool.size()))) return rc;
+  {
+    std::vector<uint8_t> ca2((p2::CA2::BYTES + 15u) & ~15u, 0);   // the constant area every CTA of k_poll2 starts from
+    p2::fill_ca2(ca2.data(), 0u);
+    if ((rc = upload(ctx, ctx->f_ca2, ca2.data(), ca2.size()))) return rc;
+  }
   if ((rc = upload(ctx, ctx->f_cont_begin, fl->cont_begin, (size_t)nn + 1))) return rc;
   if ((rc = upload(ctx, ctx->f_nerr_parse, fl->node_err_parse, nn))) return rc;
   if ((rc = upload(ctx, ctx->f_nerr_join, fl->node_err_join, nn))) return rc;
@@ -1242,6 +1247,7 @@ int kgm_load_fleet(kgm_ctx *ctx, const kgm_fleet *fl) {
   f.nslot_off = ctx->f_nslot_off.as<uint32_t>();
   f.tslot_off = ctx->f_tslot_off.as<uint32_t>();
   f.slot_pool = ctx->f_slot_pool.as<uint8_t>();
+  f.ca2 = ctx->f_ca2.as<uint4>();
   ctx->p2_max_nc = p2_max_nc; ctx->p2_max_slot = p2_max_slot; ctx->p2_max_fixed = p2_max_fixed;
   ctx->p2_max_idle = p2_max_idle; ctx->p2_any = p2_any;
   ctx->h_node_fast2 = node_fast2;

@@ -46,6 +46,7 @@ struct FleetDev {
   const uint32_t *nslot_off;     // per node: its slot in slot_pool, in 16-byte units
   const uint32_t *tslot_off;     // per container: its slot (0 for containers that are not gated)
   const uint8_t *slot_pool;      // 16-byte aligned slots, padded so that slot_bytes can be read from any of them
+  const uint4 *ca2;              // image of the k_poll2 constant area (p2::CA2, run words relative to offset 0)
 };
 
 enum : int { CTR_GROW = 0, CTR_PROW = 1, CTR_DESC = 2, CTR_OVERFLOW = 3, CTR_SLOW = 4, CTR_COUNT = 8,

@@ -98,9 +98,9 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
 
   // ---- gpu rows: one lane per row (gpu.py:104-109,119-143) ----
   uint32_t *grec = S + (sl.grec >> 2);
+  uint64_t my_hash = 0;                              // lane j: the key hash of gpu row j
   {
     bool rok = true;
-    uint64_t my_hash = 0;
     if (l < ng) {
       G2 g;
       rok = parse_gpu_row2(TG, gstart[l], gstart[l + 1] - 1u, g);
@@ -131,21 +131,22 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
     bool ok = true;
     P2 p;
     p.pidkey = ~0ull;
+    p.khash = 0;
     uint32_t nm = 0, c_first = NONE32, sid = NONE32, emit_c = NONE32, dg = 0;
     if (valid) {
       ok = parse_proc_row2(TA, pstart[r], pstart[r + 1] - 1u, p);
       if (ok && p.pidkey != ~0ull) pid_probe(f, n, p.pidkey, &nm, &c_first);
     }
+    // first gpu row with this key hash (the hashes come from the lanes that parsed the gpu rows);
+    // length and bytes are compared once, afterwards
+    for (uint32_t j = 0; j < ng; ++j) {
+      const uint64_t hj = __shfl_sync(FULL, my_hash, j);
+      if (sid == NONE32 && hj == p.khash) sid = j;
+    }
     if (valid && ok) {
-      // first gpu row with this hash and length; the bytes are compared once, afterwards
-      for (uint32_t j = 0; j < ng && sid == NONE32; ++j) {
-        const uint32_t *gr = grec + GREC_WORDS * j;
-        if (gr[GREC_HASH] == (uint32_t)p.khash && gr[GREC_HASH + 1] == (uint32_t)(p.khash >> 32) &&
-            rw_len(gr[GREC_KEY]) == p.key.len)
-          sid = j;
-      }
-      ok = sid != NONE32 &&                          // no such uuid: KeyError gpu.py:151 (a hash collision also declines)
-           keys_equal(TA, p.key.off, S, rw_off(grec[GREC_WORDS * sid + GREC_KEY]), p.key.len);
+      const uint32_t gk = sid != NONE32 ? grec[GREC_WORDS * sid + GREC_KEY] : 0u;
+      ok = sid != NONE32 && rw_len(gk) == p.key.len &&   // no such uuid: KeyError gpu.py:151 (a hash collision also declines)
+           keys_equal(TA, p.key.off, S, rw_off(gk), p.key.len);
       if (ok && p.pidkey != ~0ull) {
         if (nm > 1) ok = false;                      // a pid listed by several containers
         if (nm == 1 && c_first < nc && f.gated[cb + c_first]) emit_c = c_first;
@@ -377,17 +378,15 @@ __device__ __noinline__ void p2_slow_doc(uint32_t d, const BatchDev &b, const Fl
   __syncwarp();
 }
 
+// (the parameters are __grid_constant__: the generic path takes them by reference, which would
+// otherwise make every thread copy them to its local memory)
 __global__ void __launch_bounds__(P2_MAX_THREADS, 1)
-k_poll2(BatchDev b, FleetDev f, WorkDev w, FusedParams P, Poll2Params Q) {
+k_poll2(const __grid_constant__ BatchDev b, const __grid_constant__ FleetDev f, const __grid_constant__ WorkDev w,
+        const __grid_constant__ FusedParams P, const __grid_constant__ Poll2Params Q) {
   extern __shared__ __align__(16) uint32_t S[];
-  uint8_t *Sb = reinterpret_cast<uint8_t *>(S);
-  // constant strings and tables (same for every CTA)
-  for (uint32_t i = threadIdx.x; i < ((CA2::BYTES + 15u) & ~15u) / 4; i += blockDim.x) S[i] = 0;
-  __syncthreads();
-  if (threadIdx.x == 0) fill_ca2_strings(Sb);
-  if (threadIdx.x == 32) fill_ca2_tables(Sb, 0u);
-  if (threadIdx.x >= 64 && threadIdx.x < 96) fill_ca2_segtab(Sb, (int)threadIdx.x - 64);
-  for (uint32_t v = threadIdx.x; v <= MAX_FAST_SID; v += blockDim.x) fill_const_decimal(Sb, v);
+  // constant strings and tables: the image kgm_load_fleet built (same for every CTA)
+  for (uint32_t i = threadIdx.x; i < ((CA2::BYTES + 15u) & ~15u) / 16; i += blockDim.x)
+    reinterpret_cast<uint4 *>(S)[i] = __ldg(f.ca2 + i);
   // the counters of the NEXT launch start from zero (this launch uses the other set)
   if (blockIdx.x == 0 && threadIdx.x < CTR_COUNT) P.next_counters[threadIdx.x] = 0;
   __syncthreads();

@@ -254,10 +254,13 @@ KGM_HD void lw_put_piece(LineWriter &w, const uint4 *g, uint32_t n) {
   if (r) lw_tail(w, last & low_mask(r), r);
 }
 
+// The table-driven form of compose_line (below): one loop over the segment table in the constant
+// area.  Kept as the plain statement of what a line is (the CPU tests compare the two); the
+// kernels call the unrolled form.
 // Writes one line at byte offset `dst` of the word array B.  `ca` = byte offset of the constant
 // area (CA2) in B, `slot` = the line's template slot (global memory), `rec` = byte offset of its
 // record in B.  Returns the writer: its pending bytes still have to be stored (lw_finish).
-KGM_HD LineWriter compose_line(uint32_t *B, uint32_t ca, uint32_t pod, const uint8_t *slot, uint32_t rec,
+KGM_HD LineWriter compose_line_table(uint32_t *B, uint32_t ca, uint32_t pod, const uint8_t *slot, uint32_t rec,
                                uint32_t dst) {
   const uint8_t *Bb = reinterpret_cast<const uint8_t *>(B);
   const uint8_t *st = Bb + ca + CA2::SEGTAB + (pod ? 32u : 0u);
@@ -283,6 +286,210 @@ KGM_HD LineWriter compose_line(uint32_t *B, uint32_t ca, uint32_t pod, const uin
     }
   }
   return w;
+}
+// ---- the unrolled form --------------------------------------------------------------------------
+// The same line, with what is known at compile time taken out of the loop: the segment sequence
+// is unrolled, the 'K' strings are immediates, a cell of at most 8 bytes (nearly all of them) is
+// appended without a branch, the record sits in registers, and the slot is read as ONE stream of
+// 16-byte units two units ahead of its use (the pieces lie behind each other in the slot).
+KGM_HD uint32_t fsl(uint32_t lo, uint32_t hi, uint32_t s) {            // ((hi:lo) << s) >> 32, s in {0,8,16,24}
+#if defined(__CUDA_ARCH__)
+  return __funnelshift_l(lo, hi, s);
+#else
+  return s ? (lo >> (32u - s)) | (hi << s) : hi;
+#endif
+}
+// n <= 8 bytes: v0 holds the first four, v1 the rest, bytes from n on are zero
+KGM_HD void lw_put8(LineWriter &w, uint32_t v0, uint32_t v1, uint32_t n) {
+  const uint32_t sh = 8u * w.fill;
+  const uint32_t x0 = w.pend | (v0 << sh), x1 = fsl(v0, v1, sh), x2 = fsl(v1, 0u, sh);
+  const uint32_t total = w.fill + n, nw = total >> 2;
+  if (nw >= 1u) w.d[0] = x0;
+  if (nw >= 2u) w.d[1] = x1;
+  w.pend = nw == 0u ? x0 : nw == 1u ? x1 : x2;
+  w.d += nw;
+  w.fill = total & 3u;
+}
+// exactly 8 bytes
+KGM_HD void lw_put_w2(LineWriter &w, uint32_t v0, uint32_t v1) {
+  const uint32_t sh = 8u * w.fill;
+  w.d[0] = w.pend | (v0 << sh);
+  w.d[1] = fsl(v0, v1, sh);
+  w.pend = fsl(v1, 0u, sh);
+  w.d += 2;
+}
+// word j of an n-byte string, zero padded (compile time)
+KGM_HD constexpr uint32_t kword(const char *s, uint32_t n, uint32_t j) {
+  uint32_t v = 0;
+  for (uint32_t i = 0; i < 4; ++i)
+    if (4 * j + i < n) v |= (uint32_t)(uint8_t)s[4 * j + i] << (8 * i);
+  return v;
+}
+template <uint32_t N>
+KGM_HD void lw_put_const(LineWriter &w, uint32_t k0, uint32_t k1, uint32_t k2, uint32_t k3) {
+  static_assert(N >= 1 && N <= 16, "a 'K' string");
+  if (N <= 8) {
+    lw_put8(w, k0, k1, N);
+  } else {
+    lw_put_w2(w, k0, k1);
+    lw_put8(w, k2, k3, N - 8u);
+  }
+}
+#define KGM_PUT_K(w, s)                                                                              \
+  do {                                                                                               \
+    constexpr uint32_t n_ = sizeof(s) - 1u, a_ = kword(s, n_, 0), b_ = kword(s, n_, 1),             \
+                       c_ = kword(s, n_, 2), d_ = kword(s, n_, 3);                                  \
+    lw_put_const<n_>(w, a_, b_, c_, d_);                                                             \
+  } while (0)
+
+// the cell a run word names (absolute offset in B); reads up to 11 bytes past the cell's first word
+KGM_HD void lw_put_cell(LineWriter &w, const uint32_t *B, uint32_t pw) {
+  const uint32_t len = rw_len(pw), so = rw_off(pw);
+  if (len == 0u) return;
+  if (len <= 8u) {
+    const uint32_t *p = B + (so >> 2);
+    const uint32_t s = 8u * (so & 3u);
+    const uint32_t a = p[0], b = p[1], c = p[2];
+    const uint32_t v0 = funnel_r(a, b, s) & low_mask(len < 4u ? len : 4u);
+    const uint32_t v1 = funnel_r(b, c, s) & low_mask(len > 4u ? len - 4u : 0u);
+    lw_put8(w, v0, v1, len);
+  } else {
+    lw_put(w, B + (so >> 2), so & 3u, len);
+  }
+}
+// a cell known to be at most 4 bytes (the short id: "None" or up to three digits)
+KGM_HD void lw_put_cell4(LineWriter &w, const uint32_t *B, uint32_t pw) {
+  const uint32_t len = rw_len(pw), so = rw_off(pw);
+  lw_put8(w, load4(B, so) & low_mask(len), 0u, len);
+}
+
+struct SlotStream {                                  // the 16-byte units of a slot behind its header
+  const uint4 *g;                                    // next unit to fetch
+  uint4 q0, q1;                                      // the next two units to use
+};
+KGM_HD uint4 ldg16(const uint4 *p) {
+#if defined(__CUDA_ARCH__)
+  return __ldg(p);
+#else
+  return *p;
+#endif
+}
+// (reads two units past the last piece: the pool ends with SLOT_SLACK spare bytes)
+constexpr uint32_t SLOT_SLACK = 32;
+KGM_HD void ss_open(SlotStream &s, const uint8_t *slot) {
+  s.g = reinterpret_cast<const uint4 *>(slot + SLOT_HEADER);
+  s.q0 = ldg16(s.g);
+  s.q1 = ldg16(s.g + 1);
+  s.g += 2;
+}
+KGM_HD uint4 ss_next(SlotStream &s) {
+  const uint4 r = s.q0;
+  s.q0 = s.q1;
+  s.q1 = ldg16(s.g++);
+  return r;
+}
+// the next piece of the stream, n bytes
+KGM_HD void lw_put_stream(LineWriter &w, SlotStream &s, uint32_t n) {
+  const uint32_t sh = 8u * w.fill;
+  uint32_t prev = shl8(w.pend, 4u - w.fill);
+  uint32_t *d = w.d;
+  uint32_t left = n;
+  auto word = [&](uint32_t cur) {
+    *d++ = fsl(prev, cur, sh);
+    prev = cur;
+  };
+  for (; left >= 16u; left -= 16u) {
+    const uint4 v = ss_next(s);
+    word(v.x); word(v.y); word(v.z); word(v.w);
+  }
+  uint32_t last = 0;
+  if (left) {
+    const uint4 v = ss_next(s);
+    const uint32_t fullw = left >> 2;
+    if (fullw > 0) word(v.x);
+    if (fullw > 1) word(v.y);
+    if (fullw > 2) word(v.z);
+    last = fullw == 0 ? v.x : fullw == 1 ? v.y : fullw == 2 ? v.z : v.w;
+  }
+  w.d = d;
+  w.pend = shr8(prev, 4u - w.fill);
+  const uint32_t r = left & 3u;
+  if (r) lw_tail(w, last & low_mask(r), r);
+}
+
+template <bool POD>
+KGM_HD LineWriter compose_line_t(uint32_t *B, const uint8_t *slot, uint32_t rec, uint32_t dst) {
+  const uint4 *hp = reinterpret_cast<const uint4 *>(slot);
+  const uint4 h0 = ldg16(hp);                        // run words of pieces 0..3 (the lengths are used)
+  uint32_t h4 = 0;
+  if (POD) {
+#if defined(__CUDA_ARCH__)
+    h4 = __ldg(reinterpret_cast<const uint32_t *>(slot) + 4);
+#else
+    h4 = reinterpret_cast<const uint32_t *>(slot)[4];
+#endif
+  }
+  SlotStream s;
+  ss_open(s, slot);
+  uint32_t r[8];
+#if defined(__CUDA_ARCH__)
+  {
+    const uint4 a = *reinterpret_cast<const uint4 *>(B + (rec >> 2)), b = *reinterpret_cast<const uint4 *>(B + (rec >> 2) + 4);
+    r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w; r[4] = b.x; r[5] = b.y; r[6] = b.z; r[7] = b.w;
+  }
+#else
+  for (int i = 0; i < 8; ++i) r[i] = B[(rec >> 2) + i];
+#endif
+  LineWriter w;
+  w.d = B + (dst >> 2);
+  w.fill = dst & 3u;
+  w.pend = 0;
+  if (!POD) {                                        // seg_node(0..14)
+    lw_put_stream(w, s, rw_len(h0.x));
+    lw_put_cell4(w, B, r[GREC_SID]);
+    KGM_PUT_K(w, " gpu_util=");
+    lw_put_cell(w, B, r[GREC_UTIL]);
+    KGM_PUT_K(w, ",mem_util=");
+    { const uint32_t pw = r[GREC_FSTR]; lw_put(w, B + (rw_off(pw) >> 2), rw_off(pw) & 3u, rw_len(pw)); }   // (never empty)
+    KGM_PUT_K(w, ",mem_used=");
+    lw_put_cell(w, B, r[GREC_MU]);
+    KGM_PUT_K(w, ",mem_total=");
+    lw_put_cell(w, B, r[GREC_MT]);
+    lw_put_stream(w, s, rw_len(h0.y));
+    lw_put_cell4(w, B, r[GREC_SID]);
+    KGM_PUT_K(w, ",mem_free=");
+    lw_put_cell(w, B, r[GREC_MF]);
+  } else {                                           // seg_pod(0..19)
+    lw_put_stream(w, s, rw_len(h0.x));
+    lw_put_cell4(w, B, r[PREC_SID]);
+    lw_put_stream(w, s, rw_len(h0.y));
+    lw_put_cell(w, B, r[PREC_PID]);
+    KGM_PUT_K(w, ",gpu_util_t=");
+    lw_put_cell(w, B, r[PREC_UTIL]);
+    lw_put_stream(w, s, rw_len(h0.z));
+    lw_put_cell(w, B, r[PREC_NAME + 0]);
+    lw_put_cell(w, B, r[PREC_NAME + 1]);
+    lw_put_cell(w, B, r[PREC_NAME + 2]);
+    lw_put_cell(w, B, r[PREC_NAME + 3]);
+    lw_put_stream(w, s, rw_len(h0.w));
+    lw_put_cell(w, B, r[PREC_PID]);
+    KGM_PUT_K(w, "\",gpu_id_v=\"");
+    lw_put_cell4(w, B, r[PREC_SID]);
+    lw_put_stream(w, s, rw_len(h4));
+    lw_put_cell(w, B, r[PREC_UTIL]);
+    KGM_PUT_K(w, ",used_memory=");
+    lw_put_cell(w, B, r[PREC_MEM]);
+  }
+  lw_put8(w, 10u, 0u, 1u);                           // '\n'
+  return w;
+}
+// Writes one line at byte offset `dst` of the word array B: `slot` = the line's template slot
+// (global memory), `rec` = byte offset of its record in B (16-byte aligned).  Returns the writer:
+// its pending bytes still have to be stored (lw_finish).  (`ca` is the table form's.)
+KGM_HD LineWriter compose_line(uint32_t *B, uint32_t ca, uint32_t pod, const uint8_t *slot, uint32_t rec,
+                               uint32_t dst) {
+  (void)ca;
+  return pod ? compose_line_t<true>(B, slot, rec, dst) : compose_line_t<false>(B, slot, rec, dst);
 }
 // The last bytes of a line, after every line of the round has been written: OR-ed into the word
 // the next line has started (`has_next`), or stored as they are.

@@ -284,6 +284,11 @@ static uint32_t p2_write(P2Mem &m, uint32_t pod, uint32_t rec, uint32_t dst, uin
   p2::LineWriter w1 = p2::compose_line(m.words.data(), 0u, pod, slot, rec, dst);
   p2::lw_finish(w1, true);
   p2::lw_finish(w2, false);
+  // the table-driven form of the same line, further up in the stage at the same alignment
+  const uint32_t dst2 = ((dst + 2 * len + 64) & ~3u) + 64 + (dst & 3u);
+  p2::LineWriter w3 = p2::compose_line_table(m.words.data(), 0u, pod, slot, rec, dst2);
+  p2::lw_finish(w3, false);
+  if (w1.fill != w3.fill || memcmp(m.bytes() + dst, m.bytes() + dst2, len) != 0) return 0xffffffffu;
   return len;
 }
 
@@ -298,6 +303,7 @@ int hc_p2_node_line(const char *host, const uint8_t *row, uint32_t row_len, uint
   p2::store_grec(m.words.data(), m.tg, m.grec, g, sid);
   const uint32_t var = p2::line_var_bytes<false>(m.words.data() + m.grec / 4);
   const uint32_t n = p2_write(m, 0u, m.grec, m.stage + 64 + align, var);
+  if (n == 0xffffffffu) return -9;                 // unrolled and table-driven forms differ
   *planned = n;
   memcpy(out, m.bytes() + m.stage + 64 + align - 8, 2 * n + 16);  // 8 guard bytes in front, the second copy behind
   (void)jobs;
@@ -320,6 +326,7 @@ int hc_p2_busy_line(const char *host, const char *ns, const char *cid, const cha
   p2::store_prec(m.words.data(), m.ta, m.prec, p, m.words.data() + m.grec / 4);
   const uint32_t var = p2::line_var_bytes<true>(m.words.data() + m.prec / 4);
   const uint32_t n = p2_write(m, 1u, m.prec, m.stage + 64 + align, var);
+  if (n == 0xffffffffu) return -9;                 // unrolled and table-driven forms differ
   *planned = n;
   memcpy(out, m.bytes() + m.stage + 64 + align - 8, 2 * n + 16);
   (void)jobs;
@@ -336,6 +343,7 @@ int hc_p2_idle_line(const char *host, const char *ns, const char *cid, const cha
   p2::store_idle_rec(m.words.data(), 0u, m.prec, sid);
   const uint32_t var = p2::line_var_bytes<true>(m.words.data() + m.prec / 4);
   const uint32_t n = p2_write(m, 1u, m.prec, m.stage + 64 + align, var);
+  if (n == 0xffffffffu) return -9;                 // unrolled and table-driven forms differ
   *planned = n;
   memcpy(out, m.bytes() + m.stage + 64 + align - 8, 2 * n + 16);
   (void)jobs;
