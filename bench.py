@@ -524,6 +524,7 @@ def run_kgm_arm(args):
         mean = {k: sum(v) / len(v) for k, v in iso.items()}
     last_t = mons[0].timing()
     fused = bool(last_t["fused"])
+    kernel_name = mons[0].last_kernel() if fused else "k_encode"
     launches_per_step = int(last_t["launches"])
     slow_docs = int(last_t["slow_docs"])
 
@@ -575,10 +576,13 @@ def run_kgm_arm(args):
         algo_bytes = b0.gpu_bytes + b0.apps_bytes + n_bytes             # per launch, this rank
         achieved = algo_bytes / (enc_ms * 1e-3) / 1e9
         traffic = None
-        tpath = os.path.join(ROOT, "profiles", "poll_traffic.json" if fused else "encode_traffic.json")
+        tpath = os.path.join(ROOT, "profiles", {"k_poll": "poll_traffic.json", "k_poll2": "poll2_traffic.json"}.get(
+            kernel_name, "encode_traffic.json"))
         if os.path.isfile(tpath):
             try:
-                traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+                tj = json.load(open(tpath))
+                # (measured on the configs[1] batch: only that workload's line carries it)
+                traffic = tj.get("dram_bytes_per_launch") if args.config == "config2" else None
             except Exception:
                 traffic = None
         line = {
@@ -622,11 +626,11 @@ def run_kgm_arm(args):
             "host_ms_per_step_rank0": {k: round(1e3 * v / args.steps, 4) for k, v in host_s.items()},
             "wall_ms_region": wall_ms,
             "pipeline_frac_of_peak": algo_bytes / (mean["total_ms"] * 1e-3) / 1e9 / peak,
-            "pipeline": "fused (k_poll)" if fused else "staged (k_tokenize, k_join, k_scan, k_encode)",
+            "pipeline": "fused (%s)" % kernel_name if fused else "staged (k_tokenize, k_join, k_scan, k_encode)",
             "slow_docs_per_step": slow_docs,
             "fused_ctas_per_sm": int(last_t.get("fused_ctas_per_sm", 0)),
             "docs_in_flight_per_sm": int(last_t.get("docs_in_flight_per_sm", 0)),
-            "roofline": {"bound": "hbm", "kernel": "k_poll" if fused else "k_encode", "achieved": achieved,
+            "roofline": {"bound": "hbm", "kernel": kernel_name, "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                          "algorithmic_bytes_per_launch": algo_bytes, "peak_source": peak_src,
                          "frac_of_nominal_8TBs": achieved / 8000.0,

@@ -194,6 +194,9 @@ uint64_t kgm_output_capacity(kgm_ctx *ctx);
 int  kgm_fetch_result(kgm_ctx *ctx, kgm_result *out_host);
 
 int  kgm_get_timing(kgm_ctx *ctx, kgm_timing *out);
+/* Which kernel the last run went through: 0 = the four staged kernels, 1 = k_poll (two-warp
+ * teams), 2 = k_poll2 (one warp per document); negative = KGM_E_*.                        */
+int  kgm_last_kernel(kgm_ctx *ctx);
 
 /* ---- stage 3: time-window reductions -------------------------------------------------
  * No counterpart in the reference: gpu.py:136-143,206-216 emit raw per-poll lines with no

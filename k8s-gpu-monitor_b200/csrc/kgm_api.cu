@@ -248,13 +248,13 @@ int ensure_workspace(kgm_ctx *ctx) {
 
 // The batch goes through the fused kernel unless it was switched off or does not fit.
 // Two fused kernels: k_poll (two-warp teams, 7 - 8 documents in flight per SM, whole document
-// staged) finishes a batch of a few waves sooner; k_poll2 (one warp per document, 12 - 18 in
-// flight) has the higher throughput once a launch runs many waves (measured crossover between
-// the configs[1] batch, 3840 documents, and the configs[2] batch, 40 000: profiles/README.md).
+// staged) has the shorter path per document and takes the small batches; k_poll2 (one warp per
+// document, 16 in flight) takes every batch that fills the GPU at least once (measured on the
+// configs[1] batch, 3840 documents, and the configs[2] batch, 40 000: profiles/README.md).
 bool use_poll2(const kgm_ctx *ctx) {
   if (ctx->pipeline == KGM_PIPELINE_STAGED || ctx->pipeline == KGM_PIPELINE_FUSED_V1 || !ctx->poll2_ok) return false;
   if (ctx->pipeline == KGM_PIPELINE_FUSED_V2 || !ctx->fused_ok) return true;
-  return ctx->batch.n_docs >= (uint32_t)ctx->sms * 64u;
+  return ctx->batch.n_docs >= (uint32_t)ctx->sms * 16u;          // at least one full wave of k_poll2
 }
 bool use_fused(const kgm_ctx *ctx) {
   return use_poll2(ctx) || (ctx->pipeline != KGM_PIPELINE_STAGED && ctx->fused_ok);
@@ -619,6 +619,11 @@ void plan_poll2(kgm_ctx *ctx, const kgm_batch *b, uint64_t max_g, uint64_t max_a
   const uint32_t lines = ctx->force_lines ? ctx->force_lines : 16u;
   Poll2Params q{};
   if (!poll2_layout(ctx, lines, max_g, max_a, &q)) return;
+  // Rounds: pod lines first in a batch of a few waves (the documents start together and wait for
+  // each other's sizes: a longer first round hides more of that), node lines first in a long
+  // one (measured both ways on the configs[1] and configs[2] batches, profiles/README.md).
+  q.pods_first = b->n_docs < 4u * (uint32_t)ctx->sms * 16u ? 1u : 0u;
+  if (const char *env = getenv("KGM_POLL2_PODS_FIRST")) q.pods_first = atoi(env) ? 1u : 0u;
   ctx->poll2 = q;
   ctx->poll2_ok = true;
 }
@@ -1581,6 +1586,11 @@ int kgm_get_timing(kgm_ctx *ctx, kgm_timing *out) {
   if (!ctx || !out) return KGM_E_INVALID;
   *out = ctx->timing;
   return KGM_OK;
+}
+
+int kgm_last_kernel(kgm_ctx *ctx) {
+  if (!ctx) return KGM_E_INVALID;
+  return ctx->last_fused ? (ctx->last_poll2 ? 2 : 1) : 0;
 }
 
 int kgm_flush_l2(kgm_ctx *ctx, uint64_t bytes) {

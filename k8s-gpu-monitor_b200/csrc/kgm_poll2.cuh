@@ -269,9 +269,12 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
 
   uint64_t line0 = 0, byte0 = 0;
   bool resolved = false, fits_out = true;
-  uint32_t i0 = 0;
+  // The rounds start with the pod lines and end with the node lines (the output order is the
+  // documents' either way): the look-back is resolved after the first round has been composed,
+  // and the longer that takes, the fewer documents wait for their predecessors there.
+  uint32_t i0 = (Q.pods_first && nl > ng) ? ng : 0u, left = nl;
   do {
-    // a round: up to 32 lines of one kind (the node lines come first) whose bytes fit the stage
+    // a round: up to 32 lines of one kind whose bytes fit the stage
     uint32_t i1 = min(i0 < ng ? ng : nl, i0 + 32u), r_lo = 0;
     if (nl) {
       r_lo = loff[i0];
@@ -332,15 +335,16 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
         uint4 o;
         o.x = __funnelshift_r(a0, a1, sh); o.y = __funnelshift_r(a1, a2, sh);
         o.z = __funnelshift_r(a2, a3, sh); o.w = __funnelshift_r(a3, a4, sh);
-        *reinterpret_cast<uint4 *>(g + head + 16u * v) = o;
+        __stcs(reinterpret_cast<uint4 *>(g + head + 16u * v), o);      // written once, read by the copy engine: streaming
       }
     }
     const uint32_t done = head + 16u * nvec;
     if (l < nbytes - done) g[done + l] = st[done + l];
-    i0 = i1;
+    left -= i1 - i0;
+    i0 = i1 == nl ? 0u : i1;
     __syncwarp();                                    // the stage may be overwritten
     STAGE_MARK(9);                                   // copy-out
-  } while (i0 < nl);
+  } while (left);
   return true;
 }
 

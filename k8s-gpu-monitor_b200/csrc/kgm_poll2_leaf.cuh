@@ -363,9 +363,13 @@ KGM_HD void lw_put_cell4(LineWriter &w, const uint32_t *B, uint32_t pw) {
   lw_put8(w, load4(B, so) & low_mask(len), 0u, len);
 }
 
+#ifndef KGM_SS_DEPTH
+#define KGM_SS_DEPTH 2
+#endif
+constexpr int SS_DEPTH = KGM_SS_DEPTH;               // units fetched ahead of their use
 struct SlotStream {                                  // the 16-byte units of a slot behind its header
   const uint4 *g;                                    // next unit to fetch
-  uint4 q0, q1;                                      // the next two units to use
+  uint4 q[SS_DEPTH];                                 // the next units to use
 };
 KGM_HD uint4 ldg16(const uint4 *p) {
 #if defined(__CUDA_ARCH__)
@@ -374,18 +378,23 @@ KGM_HD uint4 ldg16(const uint4 *p) {
   return *p;
 #endif
 }
-// (reads two units past the last piece: the pool ends with SLOT_SLACK spare bytes)
-constexpr uint32_t SLOT_SLACK = 32;
+// (reads SS_DEPTH units past the last piece: the pool ends with SLOT_SLACK spare bytes)
+constexpr uint32_t SLOT_SLACK = 16u * SS_DEPTH;
 KGM_HD void ss_open(SlotStream &s, const uint8_t *slot) {
   s.g = reinterpret_cast<const uint4 *>(slot + SLOT_HEADER);
-  s.q0 = ldg16(s.g);
-  s.q1 = ldg16(s.g + 1);
-  s.g += 2;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int i = 0; i < SS_DEPTH; ++i) s.q[i] = ldg16(s.g + i);
+  s.g += SS_DEPTH;
 }
 KGM_HD uint4 ss_next(SlotStream &s) {
-  const uint4 r = s.q0;
-  s.q0 = s.q1;
-  s.q1 = ldg16(s.g++);
+  const uint4 r = s.q[0];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int i = 0; i + 1 < SS_DEPTH; ++i) s.q[i] = s.q[i + 1];
+  s.q[SS_DEPTH - 1] = ldg16(s.g++);
   return r;
 }
 // the next piece of the stream, n bytes

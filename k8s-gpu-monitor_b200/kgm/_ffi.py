@@ -114,6 +114,7 @@ SIGNATURES = {
     "kgm_output_capacity": (C.c_uint64, [C.c_void_p]),
     "kgm_fetch_result": (C.c_int, [C.c_void_p, C.POINTER(KgmResult)]),
     "kgm_get_timing": (C.c_int, [C.c_void_p, C.POINTER(KgmTiming)]),
+    "kgm_last_kernel": (C.c_int, [C.c_void_p]),
     "kgm_set_pipeline": (C.c_int, [C.c_void_p, C.c_int]),
     "kgm_debug_stage_clocks": (C.c_int, [C.c_void_p]),
     "kgm_debug_chunk_times": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),

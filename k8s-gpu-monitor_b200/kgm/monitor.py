@@ -273,6 +273,11 @@ class Monitor:
         _check(self._lib.kgm_get_timing(self._ctx, C.byref(t)), "kgm_get_timing", self._ctx, self._lib)
         return {k: getattr(t, k) for k, _ in _ffi.KgmTiming._fields_}
 
+    def last_kernel(self) -> str:
+        """The kernel(s) the last run went through."""
+        k = self._lib.kgm_last_kernel(self._ctx)
+        return {0: "k_tokenize, k_join, k_scan, k_encode", 1: "k_poll", 2: "k_poll2"}[k]
+
     def set_pipeline(self, mode):
         """PIPELINE_AUTO (fused kernel when the batch fits), PIPELINE_STAGED, PIPELINE_FUSED_GENERIC."""
         _check(self._lib.kgm_set_pipeline(self._ctx, int(mode)), "kgm_set_pipeline", self._ctx, self._lib)

@@ -5,7 +5,14 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "k8s-gpu-monitor_b200"), os.path.join(ROOT, "tests")]
 from kgm import _ffi, monitor, replay
 from fleet_util import entry_of_snap
-rp = replay.make_replay(seed=0, **replay.CONFIGS["config2"])
+CFG = dict(replay.CONFIGS[os.environ.get("KGM_CFG", "config2")])
+if "KGM_TICKS" in os.environ: CFG["ticks"] = int(os.environ["KGM_TICKS"])
+rp = replay.make_replay(seed=0, **CFG)
+if os.environ.get("KGM_TICK_MAJOR"):                 # documents tick by tick instead of host by host
+    import numpy as np
+    order = np.lexsort((rp.doc_node, rp.doc_tick))
+    rp = replay.Replay(rp.seed, rp.nodes, rp.doc_node[order], rp.doc_tick[order],
+                       [rp.gpu_texts[d] for d in order], [rp.apps_texts[d] for d in order])
 names2 = {1: "windows+rows", 2: "gpu rows", 3: "process rows", 4: "containers+lines", 5: "publish", 6: "slot wait",
           7: "compose", 8: "look-back+wait", 9: "copy-out"}
 names = {1: "A work", 2: "A wait", 3: "B work", 4: "B wait", 5: "C work", 6: "C wait", 7: "busy entries+wait",
