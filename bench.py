@@ -328,11 +328,21 @@ def run_kgm_arm(args):
     rotate = {"config3": 2, "config4": 3, "config5": 4}.get(args.config, ROTATE)
     mons, batches, rps = [], [], []
     shard_info = None
+    # configs[1] on several GPUs: a whole step lands on ONE gathering GPU ((N - 1) x 46 MB through its
+    # NVLink ingress: 0.36 ms at N = 8, longer than three steps' kernels), so N steps, bound for N different
+    # GPUs, have to be in flight for the transfers to stay off the critical path: N contexts per rank,
+    # over the same `distinct` fleets
+    distinct = rotate
+    if not sharded and world > rotate:
+        rotate = min(world, 8)
+    built = {}
     for v in range(rotate):
         if sharded:
             rp, entries, shard_info = build_workload(args.config, rank, world, variant=v if args.config == "config4" else 0)
         else:
-            rp, entries, _ = build_workload(args.config, rank * rotate + v)
+            if v % distinct not in built:
+                built[v % distinct] = build_workload(args.config, rank * distinct + v % distinct)
+            rp, entries, _ = built[v % distinct]
         mon = monitor.Monitor(local_rank)
         mon.set_pipeline({"fused": 0, "staged": 1, "fused-generic": 2, "fused-v1": 3, "fused-v2": 4}[args.pipeline])
         mon.load_fleet(entries)
@@ -595,8 +605,8 @@ def run_kgm_arm(args):
                        "samples_per_gpu": samples_step[0], "lines_per_gpu": n_lines,
                        "input_bytes_per_gpu": b0.gpu_bytes + b0.apps_bytes,
                        "output_bytes_per_gpu": n_bytes,
-                       "l2": "%d distinct resident batches per GPU visited round-robin (%d MB working set > 126 MB "
-                             "L2), no flush inside the timed bracket" % (rotate, rotate * algo_bytes // 1000000),
+                       "l2": "%d resident batches per GPU (%d distinct fleets) visited round-robin (%d MB working set "
+                             "> 126 MB L2), no flush inside the timed bracket" % (rotate, distinct, rotate * algo_bytes // 1000000),
                        "parallelism": ("hosts sharded over %d ranks, no data-path collective inside the poll path; "
                                        "per step every rank's encoded shard and its {bytes, lines} header are "
                                        "gathered (%s; inside the timed bracket, queued on the device behind the "
