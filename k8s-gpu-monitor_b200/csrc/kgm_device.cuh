@@ -122,6 +122,7 @@ struct Poll2Params {
   uint32_t off_tg, off_ta, off_grec, off_prec, off_cnt, off_cstart, off_plan, off_loff, off_toff, off_stage;
   uint32_t off_gstart, off_pstart, off_cp, off_digest;   // parse-time tables, inside the stage
   uint32_t pods_first;           // compose the pod rounds before the node round
+  uint32_t cta_tickets;          // tickets per CTA (`warps` documents at a time) instead of per warp
 };
 
 void launch_poll(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P, int blocks,

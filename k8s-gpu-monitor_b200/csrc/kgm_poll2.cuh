@@ -125,6 +125,7 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
   //      inside the container ----
   uint32_t *prec = S + (sl.prec >> 2);
   uint32_t *cp = S + (sl.cp >> 2), *digest = S + (sl.digest >> 2);
+  bool doc_key = false;
   for (uint32_t r0 = 0; r0 < np; r0 += 32) {
     const uint32_t r = r0 + l;
     const bool valid = r < np;
@@ -143,10 +144,10 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
       const uint64_t hj = __shfl_sync(FULL, my_hash, j);
       if (sid == NONE32 && hj == p.khash) sid = j;
     }
-    if (valid && ok) {
-      const uint32_t gk = sid != NONE32 ? grec[GREC_WORDS * sid + GREC_KEY] : 0u;
-      ok = sid != NONE32 && rw_len(gk) == p.key.len &&   // no such uuid: KeyError gpu.py:151 (a hash collision also declines)
-           keys_equal(TA, p.key.off, S, rw_off(gk), p.key.len);
+    if (valid && ok && sid == NONE32) doc_key = true;  // no gpu row has this uuid: KeyError gpu.py:151 once every row is read
+    if (valid && ok && sid != NONE32) {
+      const uint32_t gk = grec[GREC_WORDS * sid + GREC_KEY];
+      ok = rw_len(gk) == p.key.len && keys_equal(TA, p.key.off, S, rw_off(gk), p.key.len);   // (a hash collision declines)
       if (ok && p.pidkey != ~0ull) {
         if (nm > 1) ok = false;                      // a pid listed by several containers
         if (nm == 1 && c_first < nc && f.gated[cb + c_first]) emit_c = c_first;
@@ -156,7 +157,7 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
     if (!__all_sync(FULL, ok)) return false;
     // duplicate (pid, gpu) keys keep the first row's place and the last row's values (gpu.py:54):
     // screened by digest, any hit goes to the generic path
-    const bool screened = valid && p.pidkey != ~0ull;
+    const bool screened = valid && p.pidkey != ~0ull && sid != NONE32;
     const uint32_t act = __ballot_sync(FULL, screened);
     bool dup = false;
     if (screened) {
@@ -176,7 +177,7 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
       pos = base + __popc(peers & lanemask_lt());
     }
     if (valid) {
-      store_prec(S, sl.ta, sl.prec + PREC_BYTES * r, p, grec + GREC_WORDS * sid);
+      if (sid != NONE32) store_prec(S, sl.ta, sl.prec + PREC_BYTES * r, p, grec + GREC_WORDS * sid);
       cp[r] = (screened ? 0x80000000u : 0u) | ((emit_c == NONE32 ? CP_NONE : emit_c) << 16) | pos;
       digest[r] = dg;
     }
@@ -184,9 +185,12 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
   }
 
   STAGE_MARK(3);                                     // process rows
+  // A process row that names no gpu of this poll: every table has been read and the node lines have
+  // gone out when gpu.py:151 raises, so the document is its node lines and the KeyError.
+  doc_key = __any_sync(FULL, doc_key);
   // ---- containers in docker stats order: busy lines, or idle lines (gpu.py:174-253) ----
   uint32_t total_pod = 0, total_idle = 0;
-  for (uint32_t c0 = 0; c0 < nc; c0 += 32) {
+  for (uint32_t c0 = 0; c0 < (doc_key ? 0u : nc); c0 += 32) {
     const uint32_t c = c0 + l;
     uint32_t lines = 0, idle = 0;
     if (c < nc && f.gated[cb + c]) {
@@ -215,7 +219,7 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
     toff[l] = f.nslot_off[n];
     loff[l] = f.node_fixed[n] + 1u + line_var_bytes<false>(grec + GREC_WORDS * l);
   }
-  for (uint32_t c = l; c < nc; c += 32) {            // idle containers: one line per visible uuid (gpu.py:221-250)
+  for (uint32_t c = l; c < (doc_key ? 0u : nc); c += 32) {   // idle containers: one line per visible uuid (gpu.py:221-250)
     const uint32_t cw = cnt[c];
     if (!(cw & 0x8000u)) continue;
     const uint32_t gc = cb + c, nvis = f.vis_begin[gc + 1] - f.vis_begin[gc];
@@ -239,7 +243,7 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
       loff[idx] = f.cont_fixed[gc] + 1u + line_var_bytes<true>(prec + PREC_WORDS * ir);
     }
   }
-  for (uint32_t r = l; r < np; r += 32) {            // busy lines (gpu.py:190-219)
+  for (uint32_t r = l; r < (doc_key ? 0u : np); r += 32) {   // busy lines (gpu.py:190-219)
     const uint32_t c = (cp[r] >> 16) & 0x7fffu;
     if (c == CP_NONE) continue;
     const uint32_t gc = cb + c, idx = ng + cstart[c] + (cp[r] & 0xffffu);
@@ -299,7 +303,7 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
       if (l == 0) {
         w.doc_line_off[d] = line0;
         w.doc_byte_off[d] = byte0;
-        w.doc_status[d] = 0; w.doc_nlines[d] = nl; w.doc_nbytes[d] = nb;
+        w.doc_status[d] = doc_key ? (int32_t)DOC_KEY : 0; w.doc_nlines[d] = nl; w.doc_nbytes[d] = nb;
         if (d + 1 == b.n_docs) {
           w.doc_line_off[b.n_docs] = line0 + nl;
           w.doc_byte_off[b.n_docs] = byte0 + nb;
@@ -405,11 +409,23 @@ k_poll2(const __grid_constant__ BatchDev b, const __grid_constant__ FleetDev f, 
   sl.gstart = base + Q.off_gstart; sl.pstart = base + Q.off_pstart; sl.cp = base + Q.off_cp; sl.digest = base + Q.off_digest;
   const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(S);
 
+  __shared__ unsigned long long cta_base;
   for (;;) {
     unsigned long long t = 0;
-    if (l == 0) t = atomicAdd(P.ticket, 1ull) - P.ticket_base;
-    t = __shfl_sync(FULL, t, 0);
-    if (t >= b.n_docs) break;
+    if (Q.cta_tickets) {
+      // the warps of a CTA start their documents together, `warps` consecutive ones at a time, so
+      // that they run through the same code at about the same time
+      __syncthreads();
+      if (threadIdx.x == 0) cta_base = atomicAdd(P.ticket, (unsigned long long)Q.warps) - P.ticket_base;
+      __syncthreads();
+      if (cta_base >= b.n_docs) break;
+      t = cta_base + warp;
+      if (t >= b.n_docs) continue;
+    } else {
+      if (l == 0) t = atomicAdd(P.ticket, 1ull) - P.ticket_base;
+      t = __shfl_sync(FULL, t, 0);
+      if (t >= b.n_docs) break;
+    }
     const uint32_t d = (uint32_t)t;
     if (P.allow_fast && p2_fast_doc(d, b, f, w, P, Q, S, s0, sl)) continue;
     cp_async_wait_all();

@@ -22,11 +22,11 @@ from oracle import poll_oracle
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module", params=["fused", "staged", "fused-v1"])
+@pytest.fixture(scope="module", params=["fused", "staged", "fused-v1", "fused-v2"])
 def mon(request):
     m = monitor.Monitor(0)
     m.set_pipeline({"fused": _ffi.PIPELINE_AUTO, "staged": _ffi.PIPELINE_STAGED,
-                    "fused-v1": _ffi.PIPELINE_FUSED_V1}[request.param])
+                    "fused-v1": _ffi.PIPELINE_FUSED_V1, "fused-v2": _ffi.PIPELINE_FUSED_V2}[request.param])
     m.pipeline_name = request.param
     yield m
     m.close()
@@ -86,3 +86,8 @@ def test_config5_shape_skewed_short_lived_pods_and_mig(mon):
         t = mon.timing()
         # the dying documents go generic, and the few whose texts exceed a warp's slice
         assert t["fused"] == 1 and died <= t["slow_docs"] < rp.n_docs // 3
+    if mon.pipeline_name == "fused-v2":
+        # k_poll2 answers the KeyError of gpu.py:151 itself (node lines, then the status): only the
+        # documents whose texts exceed a warp's slice go generic
+        t = mon.timing()
+        assert t["fused"] == 1 and t["slow_docs"] < died
