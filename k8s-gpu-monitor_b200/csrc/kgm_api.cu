@@ -609,7 +609,7 @@ bool poll2_layout(kgm_ctx *ctx, uint32_t lines, uint64_t max_g, uint64_t max_a, 
     if (a > 4096) a = a * 3 / 4; else if (g > 1024) g = g * 3 / 4; else return false;
   }
   if (Q.slice_bytes * 4u > dyn_max) return false;
-  Q.warps = std::min<uint32_t>(20u, dyn_max / Q.slice_bytes);
+  Q.warps = std::min<uint32_t>((uint32_t)poll2_max_warps(), dyn_max / Q.slice_bytes);
   if (ctx->force_warps) Q.warps = std::max(1u, std::min(Q.warps, ctx->force_warps));
   *out = Q;
   return true;

@@ -29,7 +29,12 @@ namespace {
 
 using namespace p2;
 
-constexpr int P2_MAX_THREADS = 640;                  // 20 warps x 102 registers
+// Shared memory holds 16 - 17 documents of the bench configurations, so the kernel is compiled for
+// 16 warps and 128 registers (no spills); 20 warps x 96 registers measured the same or slower.
+#ifndef KGM_P2_MAX_WARPS
+#define KGM_P2_MAX_WARPS 16
+#endif
+constexpr int P2_MAX_THREADS = 32 * KGM_P2_MAX_WARPS;
 
 __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void *g) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(g) : "memory");
@@ -436,6 +441,7 @@ k_poll2(const __grid_constant__ BatchDev b, const __grid_constant__ FleetDev f, 
 
 }  // namespace
 
+int poll2_max_warps() { return KGM_P2_MAX_WARPS; }
 int poll2_smem_bytes(const Poll2Params &Q) { return (int)(((CA2::BYTES + 15u) & ~15u) + Q.warps * Q.slice_bytes); }
 
 void launch_poll2(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P, const Poll2Params &Q,
