@@ -1528,24 +1528,43 @@ int kgm_window_reduce(kgm_ctx *ctx, uint32_t window_ticks, int want_host_copy, k
   if (n_desc == 0) return KGM_OK;
   // samples
   const size_t n = n_desc;
-  const size_t sample_bytes = 12 * ((n * 8 + 255) & ~(size_t)255) + 4096;
+  const size_t sample_bytes = 6 * ((n * 8 + 255) & ~(size_t)255) + 4096;
   CU(ctx->w_win_samples.ensure(sample_bytes));
   Carver c{ctx->w_win_samples.as<uint8_t>()};
   WinSamples s{};
-  s.key = c.take<uint64_t>(n); s.key_sorted = c.take<uint64_t>(n); s.order = c.take<uint64_t>(n);
-  s.idx = c.take<uint32_t>(n); s.idx_sorted = c.take<uint32_t>(n);
+  s.key = c.take<uint64_t>(n); s.order = c.take<uint64_t>(n);
+  s.idx = c.take<uint32_t>(n);
   for (int m = 0; m < 3; ++m) s.val[m] = c.take<uint32_t>(n);
   s.node = c.take<uint32_t>(n);
-  uint32_t *head = c.take<uint32_t>(n), *seg_incl = c.take<uint32_t>(n);
-  const size_t temp_bytes = window_sort_temp_bytes(n_desc);
-  CU(ctx->w_win_temp.ensure(temp_bytes));
-  CU(launch_window_samples(ctx->batch, ctx->work, n_desc, window_ticks, s, ctx->w_win_temp.p, temp_bytes, head,
-                           seg_incl, ctx->stream));
-  CU(cudaGetLastError());
+  // the batch's largest short id and its window range size the index space
+  CU(ctx->w_win_temp.ensure(256));
   uint32_t *h32 = ctx->h_small.as<uint32_t>();
-  CU(cudaMemcpyAsync(h32, seg_incl + (n - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  h32[0] = 0; h32[1] = 0xffffffffu; h32[2] = 0; h32[3] = 0;
+  CU(cudaMemcpyAsync(ctx->w_win_temp.p, h32, 16, cudaMemcpyHostToDevice, ctx->stream));
+  CU(launch_window_samples(ctx->batch, ctx->work, n_desc, window_ticks, s, ctx->w_win_temp.as<uint32_t>(), ctx->stream));
+  CU(cudaMemcpyAsync(h32, ctx->w_win_temp.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  if (h32[1] == 0xffffffffu) return KGM_OK;                    // no line was emitted
+  WinIndex x{};
+  x.n_nodes = ctx->fleet.n_nodes;
+  x.sid_slots = h32[0] + 2u;                                   // ids 0 .. max, and "None"
+  x.min_win = h32[1];
+  x.n_win = h32[2] - h32[1] + 1u;
+  const uint64_t size64 = ((uint64_t)ctx->fleet.n_nodes + ctx->fleet.n_containers) * x.sid_slots * x.n_win;
+  if (size64 > (1ull << 28)) return KGM_E_LIMIT;               // (1 GiB of flags: a batch that spans too many windows)
+  x.size = (uint32_t)size64;
+  const uint32_t tiles = window_scan_tiles(x.size);
+  const size_t flag_bytes = (((size_t)x.size + 1) * 4 + 255) & ~(size_t)255;
+  CU(ctx->w_win_temp.ensure(flag_bytes + ((size_t)tiles + 1) * 4 + 256));
+  uint32_t *flags = ctx->w_win_temp.as<uint32_t>();
+  uint32_t *tops = reinterpret_cast<uint32_t *>(ctx->w_win_temp.as<uint8_t>() + flag_bytes);
+  CU(cudaMemsetAsync(flags, 0, flag_bytes, ctx->stream));
+  CU(launch_window_index(s, n_desc, x, flags, tops, ctx->stream));
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(h32, flags + x.size, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   const uint32_t n_groups = h32[0];
+  const uint32_t *seg_incl = flags;                            // index -> group
   if (n_groups == 0) return KGM_OK;
   size_t group_bytes = 0;
   (void)carve_groups(nullptr, n_groups, &group_bytes);

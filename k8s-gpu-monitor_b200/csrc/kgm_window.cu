@@ -11,14 +11,13 @@
 // window): count, and per value min / max / sum (-> mean) / last (by tick, then line order).
 //
 // Data flow: the staged tokenizer + join leave the token tables and the line plan in the
-// workspace; k_win_samples turns every planned line into (key, order, values); the keys are
-// radix-sorted (CUB, plumbing); k_win_reduce stages a tile of sorted samples in shared
-// memory and reduces runs of equal keys with warp shuffles, one atomic per (warp, run);
-// k_win_last / k_win_final fill in the "last" values, the means and the unpacked keys.
+// workspace; k_win_samples turns every planned line into (key, order, values) and finds the
+// batch's largest short id and its window range.  A key is then a DIRECT index: series slot
+// (node ordinal, or nodes + container ordinal) x short-id slot x window, so no sort is needed:
+// k_win_mark flags the indices that occur, an exclusive scan over the flags (k_scan_*, below)
+// numbers the groups in ascending key order, k_win_accum adds every sample to its group with
+// atomics, k_win_last / k_win_final fill in the "last" values, the means and the unpacked keys.
 #include <cuda_runtime.h>
-
-#include <cub/device/device_radix_sort.cuh>
-#include <cub/device/device_scan.cuh>
 
 #include "kgm_device.cuh"
 #include "kgm_window.cuh"
@@ -38,7 +37,9 @@ __device__ __forceinline__ uint64_t make_key(uint32_t kind, uint32_t entity, uin
 
 // One planned line -> one sample.  Lines past a document's raise point are planned but not
 // emitted (doc_nlines): they get the invalid key and sort to the end.
-__global__ void k_win_samples(BatchDev b, WorkDev w, uint32_t n_desc, uint32_t window_ticks, WinSamples s) {
+// scal[0] = largest short id of an emitted line (0xffff = None not counted), scal[1] = smallest window, scal[2] =
+// largest window (the host sizes the index space from them).
+__global__ void k_win_samples(BatchDev b, WorkDev w, uint32_t n_desc, uint32_t window_ticks, WinSamples s, uint32_t *scal) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_desc) return;
   const LineDesc ds = w.desc[i];
@@ -68,7 +69,19 @@ __global__ void k_win_samples(BatchDev b, WorkDev w, uint32_t n_desc, uint32_t w
     }
   }
   s.key[i] = key;
-  s.idx[i] = i;
+  {
+    const bool ok = key != KEY_INVALID;
+    const uint32_t sid = (uint32_t)(key >> 16) & 0xffffu, win = (uint32_t)key & 0xffffu;
+    const uint32_t am = __activemask();
+    const uint32_t mx_sid = __reduce_max_sync(am, ok && sid != 0xffffu ? sid : 0u);
+    const uint32_t mn_win = __reduce_min_sync(am, ok ? win : 0xffffffffu);
+    const uint32_t mx_win = __reduce_max_sync(am, ok ? win : 0u);
+    if ((threadIdx.x & 31u) == (uint32_t)__ffs(am) - 1u) {
+      atomicMax(scal + 0, mx_sid);
+      atomicMin(scal + 1, mn_win);
+      atomicMax(scal + 2, mx_win);
+    }
+  }
   {
     // "last" = greatest (tick, document, position in the document): 20 | 26 | 18 bits
     const uint32_t tick = d < b.n_docs ? b.doc_tick[d] : 0u;
@@ -77,13 +90,6 @@ __global__ void k_win_samples(BatchDev b, WorkDev w, uint32_t n_desc, uint32_t w
   }
   s.val[0][i] = util; s.val[1][i] = mem; s.val[2][i] = power;
   s.node[i] = node;
-}
-
-__global__ void k_win_heads(const uint64_t *key, uint32_t n, uint32_t *head) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const uint64_t k = key[i];
-  head[i] = (k != KEY_INVALID && (i == 0 || key[i - 1] != k)) ? 1u : 0u;
 }
 
 __global__ void k_win_init(WinGroups g, uint32_t n) {
@@ -99,103 +105,125 @@ __global__ void k_win_init(WinGroups g, uint32_t n) {
   }
 }
 
-struct Agg { uint32_t cnt, mn, mx; uint64_t sum, order; };
-
-__device__ __forceinline__ Agg agg_of(uint32_t v, uint64_t order) {
-  Agg a;
-  const bool has = v != NONE32;
-  a.cnt = has ? 1u : 0u; a.mn = has ? v : 0xffffffffu; a.mx = has ? v : 0u; a.sum = has ? v : 0ull;
-  a.order = has ? order : 0ull;
-  return a;
-}
-__device__ __forceinline__ Agg agg_merge(const Agg &a, const Agg &b) {
-  Agg r;
-  r.cnt = a.cnt + b.cnt; r.mn = min(a.mn, b.mn); r.mx = max(a.mx, b.mx); r.sum = a.sum + b.sum;
-  r.order = a.order > b.order ? a.order : b.order;
-  return r;
-}
-__device__ __forceinline__ Agg agg_shfl_up(const Agg &a, int delta) {
-  Agg r;
-  r.cnt = __shfl_up_sync(FULLMASK, a.cnt, delta); r.mn = __shfl_up_sync(FULLMASK, a.mn, delta);
-  r.mx = __shfl_up_sync(FULLMASK, a.mx, delta); r.sum = __shfl_up_sync(FULLMASK, a.sum, delta);
-  r.order = __shfl_up_sync(FULLMASK, a.order, delta);
-  return r;
+// key -> direct index (ascending in the key): see WinIndex in kgm_window.cuh
+__device__ __forceinline__ uint32_t index_of(uint64_t key, const WinIndex &x) {
+  const uint32_t kind = (uint32_t)(key >> 63), entity = (uint32_t)(key >> 32) & 0x7fffffffu;
+  const uint32_t sid = (uint32_t)(key >> 16) & 0xffffu, win = (uint32_t)key & 0xffffu;
+  const uint32_t slot = kind ? x.n_nodes + entity : entity;
+  const uint32_t sslot = sid == 0xffffu ? x.sid_slots - 1u : sid;
+  return (slot * x.sid_slots + sslot) * x.n_win + (win - x.min_win);
 }
 
-// Sorted samples -> groups.  A block stages its tile (gathered through the sort
-// permutation) in shared memory; each warp then runs a segmented inclusive scan over its 32
-// samples with shuffles, and the last lane of every run of equal groups adds the run's
-// aggregate to the group with atomics (a run continues across warps and blocks).
-__global__ void __launch_bounds__(WIN_THREADS) k_win_reduce(WinSamples s, const uint32_t *seg_incl, uint32_t n,
-                                                            WinGroups g) {
-  __shared__ uint32_t sh_seg[WIN_THREADS];
-  __shared__ uint32_t sh_val[3][WIN_THREADS];
-  __shared__ uint64_t sh_order[WIN_THREADS];
-  __shared__ uint64_t sh_key[WIN_THREADS];
-  __shared__ uint32_t sh_node[WIN_THREADS];
-  const uint32_t t = threadIdx.x, i = blockIdx.x * WIN_THREADS + t;
-  uint32_t seg = NONE32;
-  if (i < n && s.key_sorted[i] != KEY_INVALID) {
-    const uint32_t src = s.idx_sorted[i];
-    seg = seg_incl[i] - 1u;
-    sh_val[0][t] = s.val[0][src]; sh_val[1][t] = s.val[1][src]; sh_val[2][t] = s.val[2][src];
-    sh_order[t] = s.order[src];
-    sh_key[t] = s.key_sorted[i];
-    sh_node[t] = s.node[src];
+// flags[index] = 1 for every index that occurs; idx[i] = the sample's index (NONE32: not emitted)
+__global__ void k_win_mark(WinSamples s, uint32_t n, WinIndex x, uint32_t *flags) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t key = s.key[i];
+  uint32_t ix = NONE32;
+  if (key != KEY_INVALID) {
+    ix = index_of(key, x);
+    flags[ix] = 1u;
   }
-  sh_seg[t] = seg;
-  __syncthreads();
-  const uint32_t lane = t & 31u;
-  const uint32_t my = sh_seg[t];
-  const uint32_t prev = lane ? sh_seg[t - 1] : NONE32 - 1u;          // lane 0 starts a run inside the warp
-  const bool head = my != prev;
-  const uint32_t next = (lane == 31u) ? NONE32 - 2u : sh_seg[t + 1];
-  const bool tail = my != next;
-  uint32_t cnt = my != NONE32 ? 1u : 0u;
-  Agg a[3];
-#pragma unroll
-  for (int m = 0; m < 3; ++m) a[m] = my != NONE32 ? agg_of(sh_val[m][t], sh_order[t]) : agg_of(NONE32, 0);
-  // distance to the run's head inside the warp
-  const uint32_t heads = __ballot_sync(FULLMASK, head);
-  const uint32_t below = heads & (0xffffffffu >> (31u - lane));       // heads at or below this lane
-  const uint32_t run_start = 31u - __clz(below);
+  s.idx[i] = ix;
+}
+
+// ---- exclusive scan of a uint32 array, in place: tiles of SCAN_TILE, their totals, the add-back ----
+constexpr int SCAN_THREADS = 1024, SCAN_PER = 4, SCAN_TILE = SCAN_THREADS * SCAN_PER;
+
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *total) {   // every thread of the block
+  __shared__ uint32_t warp_sum[32];
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  uint32_t incl = v;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t c2 = __shfl_up_sync(FULLMASK, cnt, o);
-    Agg up[3];
-#pragma unroll
-    for (int m = 0; m < 3; ++m) up[m] = agg_shfl_up(a[m], o);
-    if (lane >= run_start + (uint32_t)o) {
-      cnt += c2;
-#pragma unroll
-      for (int m = 0; m < 3; ++m) a[m] = agg_merge(a[m], up[m]);
-    }
+    const uint32_t u = __shfl_up_sync(FULLMASK, incl, o);
+    if (lane >= (uint32_t)o) incl += u;
   }
-  if (tail && my != NONE32) {
-    atomicAdd(&g.count[my], cnt);
-    g.key[my] = sh_key[t];
-    g.node[my] = sh_node[t];
+  if (lane == 31u) warp_sum[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t ws = warp_sum[lane], wi = ws;
 #pragma unroll
-    for (int m = 0; m < 3; ++m) {
-      if (!a[m].cnt) continue;
-      atomicAdd(&g.m_count[m][my], a[m].cnt);
-      atomicMin(&g.m_min[m][my], a[m].mn);
-      atomicMax(&g.m_max[m][my], a[m].mx);
-      atomicAdd(reinterpret_cast<unsigned long long *>(&g.m_sum[m][my]), (unsigned long long)a[m].sum);
-      atomicMax(reinterpret_cast<unsigned long long *>(&g.m_order[m][my]), (unsigned long long)a[m].order);
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(FULLMASK, wi, o);
+      if (lane >= (uint32_t)o) wi += u;
     }
+    warp_sum[lane] = wi - ws;                        // exclusive over the warps
+    if (lane == 31u) *total = wi;
+  }
+  __syncthreads();
+  const uint32_t r = warp_sum[warp] + incl - v;
+  __syncthreads();                                   // warp_sum may be reused by the caller's next round
+  return r;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_tiles(uint32_t *a, uint32_t n, uint32_t *tops) {
+  __shared__ uint32_t total;
+  const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_PER;
+  uint32_t v[SCAN_PER], sum = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_PER; ++k) { v[k] = base + k < n ? a[base + k] : 0u; sum += v[k]; }
+  uint32_t ex = block_excl_scan(sum, &total);
+#pragma unroll
+  for (int k = 0; k < SCAN_PER; ++k) { if (base + k < n) a[base + k] = ex; ex += v[k]; }
+  if (threadIdx.x == 0) tops[blockIdx.x] = total;
+}
+// one block: tops[0 .. nt) -> exclusive, tops[nt] = the grand total
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_tops(uint32_t *tops, uint32_t nt) {
+  __shared__ uint32_t total;
+  uint32_t carry = 0;
+  for (uint32_t i0 = 0; i0 < nt; i0 += SCAN_THREADS) {
+    const uint32_t i = i0 + threadIdx.x;
+    const uint32_t v = i < nt ? tops[i] : 0u;
+    const uint32_t ex = block_excl_scan(v, &total);
+    if (i < nt) tops[i] = carry + ex;
+    carry += total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) tops[nt] = carry;
+}
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_add(uint32_t *a, uint32_t n, const uint32_t *tops, uint32_t nt) {
+  const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_PER, add = tops[blockIdx.x];
+#pragma unroll
+  for (int k = 0; k < SCAN_PER; ++k)
+    if (base + k < n) a[base + k] += add;
+  if (blockIdx.x == 0 && threadIdx.x == 0) a[n] = tops[nt];          // a[] has n + 1 entries
+}
+
+// Every emitted sample is added to its group: group = offs[index].
+__global__ void __launch_bounds__(WIN_THREADS) k_win_accum(WinSamples s, const uint32_t *offs, uint32_t n, WinGroups g) {
+  const uint32_t i = blockIdx.x * WIN_THREADS + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t ix = s.idx[i];
+  if (ix == NONE32) return;
+  const uint32_t my = offs[ix];
+  const uint64_t order = s.order[i];
+  atomicAdd(&g.count[my], 1u);
+  g.key[my] = s.key[i];                              // (the same value from every sample of the group)
+  g.node[my] = s.node[i];
+#pragma unroll
+  for (int m = 0; m < 3; ++m) {
+    const uint32_t v = s.val[m][i];
+    if (v == NONE32) continue;
+    atomicAdd(&g.m_count[m][my], 1u);
+    atomicMin(&g.m_min[m][my], v);
+    atomicMax(&g.m_max[m][my], v);
+    atomicAdd(reinterpret_cast<unsigned long long *>(&g.m_sum[m][my]), (unsigned long long)v);
+    atomicMax(reinterpret_cast<unsigned long long *>(&g.m_order[m][my]), (unsigned long long)order);
   }
 }
 
 // The value of the sample that holds the group's greatest (tick, line) order.
-__global__ void k_win_last(WinSamples s, const uint32_t *seg_incl, uint32_t n, WinGroups g) {
+__global__ void k_win_last(WinSamples s, const uint32_t *offs, uint32_t n, WinGroups g) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n || s.key_sorted[i] == KEY_INVALID) return;
-  const uint32_t src = s.idx_sorted[i], seg = seg_incl[i] - 1u;
-  const uint64_t order = s.order[src];
+  if (i >= n) return;
+  const uint32_t ix = s.idx[i];
+  if (ix == NONE32) return;
+  const uint32_t seg = offs[ix];
+  const uint64_t order = s.order[i];
 #pragma unroll
   for (int m = 0; m < 3; ++m) {
-    const uint32_t v = s.val[m][src];
+    const uint32_t v = s.val[m][i];
     if (v != NONE32 && g.m_order[m][seg] == order) g.m_last[m][seg] = v;
   }
 }
@@ -219,35 +247,38 @@ __global__ void k_win_final(WinGroups g, uint32_t n) {
 
 }  // namespace
 
-size_t window_sort_temp_bytes(uint32_t n) {
-  size_t a = 0, b = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, a, (const uint64_t *)nullptr, (uint64_t *)nullptr,
-                                  (const uint32_t *)nullptr, (uint32_t *)nullptr, (int)n);
-  cub::DeviceScan::InclusiveSum(nullptr, b, (const uint32_t *)nullptr, (uint32_t *)nullptr, (int)n);
-  return (a > b ? a : b) + 256;
-}
+uint32_t window_scan_tiles(uint64_t n) { return (uint32_t)((n + SCAN_TILE - 1) / SCAN_TILE); }
 
 cudaError_t launch_window_samples(const BatchDev &b, const WorkDev &w, uint32_t n_desc, uint32_t window_ticks,
-                                  const WinSamples &s, void *temp, size_t temp_bytes, uint32_t *head,
-                                  uint32_t *seg_incl, cudaStream_t st) {
+                                  const WinSamples &s, uint32_t *scal, cudaStream_t st) {
   if (!n_desc) return cudaSuccess;
   const int blocks = (int)((n_desc + WIN_THREADS - 1) / WIN_THREADS);
-  k_win_samples<<<blocks, WIN_THREADS, 0, st>>>(b, w, n_desc, window_ticks, s);
-  cudaError_t e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, s.key, s.key_sorted, s.idx, s.idx_sorted,
-                                                  (int)n_desc, 0, 64, st);
-  if (e != cudaSuccess) return e;
-  k_win_heads<<<blocks, WIN_THREADS, 0, st>>>(s.key_sorted, n_desc, head);
-  return cub::DeviceScan::InclusiveSum(temp, temp_bytes, head, seg_incl, (int)n_desc, st);
+  k_win_samples<<<blocks, WIN_THREADS, 0, st>>>(b, w, n_desc, window_ticks, s, scal);
+  return cudaGetLastError();
 }
 
-cudaError_t launch_window_reduce(const WinSamples &s, const uint32_t *seg_incl, uint32_t n_desc, const WinGroups &g,
+// flags[0 .. x.size] (zeroed by the caller) -> offs: offs[index] = the group of an index that occurs,
+// offs[x.size] = the number of groups.  tops: window_scan_tiles(x.size) + 1 words.
+cudaError_t launch_window_index(const WinSamples &s, uint32_t n_desc, const WinIndex &x, uint32_t *flags,
+                                uint32_t *tops, cudaStream_t st) {
+  if (!n_desc || !x.size) return cudaSuccess;
+  const int blocks = (int)((n_desc + WIN_THREADS - 1) / WIN_THREADS);
+  k_win_mark<<<blocks, WIN_THREADS, 0, st>>>(s, n_desc, x, flags);
+  const uint32_t nt = window_scan_tiles(x.size);
+  k_scan_tiles<<<nt, SCAN_THREADS, 0, st>>>(flags, x.size, tops);
+  k_scan_tops<<<1, SCAN_THREADS, 0, st>>>(tops, nt);
+  k_scan_add<<<nt, SCAN_THREADS, 0, st>>>(flags, x.size, tops, nt);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_window_reduce(const WinSamples &s, const uint32_t *offs, uint32_t n_desc, const WinGroups &g,
                                  uint32_t n_groups, cudaStream_t st) {
   if (!n_desc || !n_groups) return cudaSuccess;
   const int gb = (int)((n_groups + WIN_THREADS - 1) / WIN_THREADS);
   const int sb = (int)((n_desc + WIN_THREADS - 1) / WIN_THREADS);
   k_win_init<<<gb, WIN_THREADS, 0, st>>>(g, n_groups);
-  k_win_reduce<<<sb, WIN_THREADS, 0, st>>>(s, seg_incl, n_desc, g);
-  k_win_last<<<sb, WIN_THREADS, 0, st>>>(s, seg_incl, n_desc, g);
+  k_win_accum<<<sb, WIN_THREADS, 0, st>>>(s, offs, n_desc, g);
+  k_win_last<<<sb, WIN_THREADS, 0, st>>>(s, offs, n_desc, g);
   k_win_final<<<gb, WIN_THREADS, 0, st>>>(g, n_groups);
   return cudaGetLastError();
 }

@@ -10,11 +10,19 @@ struct BatchDev;
 struct WorkDev;
 
 struct WinSamples {               // one entry per planned line
-  uint64_t *key, *key_sorted;     // kind | entity | gpu_id | window; ~0 = line not emitted
-  uint32_t *idx, *idx_sorted;     // sort permutation
-  uint64_t *order;                // tick << 32 | line index: picks "last"
+  uint64_t *key;                  // kind | entity | gpu_id | window; ~0 = line not emitted
+  uint32_t *idx;                  // the key as a direct index (WinIndex); 0xffffffff = line not emitted
+  uint64_t *order;                // tick | document | position: picks "last"
   uint32_t *val[3];               // gpu_util, mem, power; 0xffffffff = the line has none
   uint32_t *node;
+};
+
+// The index space of a batch: (series slot x short-id slot x window), ascending in the key.
+// Series slot = node ordinal for node_gpu lines, n_nodes + container ordinal for pod_gpu lines;
+// short-id slot = the id, the last slot for "None".
+struct WinIndex {
+  uint32_t n_nodes, sid_slots, min_win, n_win;
+  uint32_t size;                  // (n_nodes + n_containers) * sid_slots * n_win
 };
 
 struct WinGroups {                // one entry per (series, window), ascending key order
@@ -26,11 +34,12 @@ struct WinGroups {                // one entry per (series, window), ascending k
   uint64_t *key, *m_order[3];     // internal
 };
 
-size_t window_sort_temp_bytes(uint32_t n);
+uint32_t window_scan_tiles(uint64_t n);
 cudaError_t launch_window_samples(const BatchDev &b, const WorkDev &w, uint32_t n_desc, uint32_t window_ticks,
-                                  const WinSamples &s, void *temp, size_t temp_bytes, uint32_t *head,
-                                  uint32_t *seg_incl, cudaStream_t st);
-cudaError_t launch_window_reduce(const WinSamples &s, const uint32_t *seg_incl, uint32_t n_desc, const WinGroups &g,
+                                  const WinSamples &s, uint32_t *scal, cudaStream_t st);
+cudaError_t launch_window_index(const WinSamples &s, uint32_t n_desc, const WinIndex &x, uint32_t *flags,
+                                uint32_t *tops, cudaStream_t st);
+cudaError_t launch_window_reduce(const WinSamples &s, const uint32_t *offs, uint32_t n_desc, const WinGroups &g,
                                  uint32_t n_groups, cudaStream_t st);
 
 }  // namespace kgm

@@ -38,3 +38,19 @@ def test_version_strings_and_struct_layout_without_a_gpu():
     assert C.sizeof(_ffi.KgmResult) == 56
     assert C.sizeof(_ffi.KgmTiming) == 48
     assert C.sizeof(_ffi.KgmFleet) == 8 + 16 + 8 * 3 + 8 + 8 * 3 + 16 * 4 + 8 + 16 + 8 + 16
+
+
+def test_every_kernel_in_the_library_is_the_repository_s_own():
+    """No library kernels (CUB sort / scan and the like): every device function of libkgm.so is
+    defined in csrc/ under the kgm namespace."""
+    import shutil
+    import subprocess
+    import pytest
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    out = subprocess.run(["cuobjdump", "-res-usage", build.build_library()], stdout=subprocess.PIPE,
+                         stderr=subprocess.DEVNULL, text=True).stdout
+    funcs = re.findall(r"Function (\S+):", out)
+    assert len(funcs) >= 10
+    foreign = [f for f in funcs if not f.startswith("_ZN3kgm")]
+    assert not foreign, foreign
