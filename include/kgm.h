@@ -173,8 +173,8 @@ int  kgm_encode_resident(kgm_ctx *ctx, kgm_result *out);
 int  kgm_encode_resident_async(kgm_ctx *ctx, kgm_result *out);
 int  kgm_encode_finish(kgm_ctx *ctx, kgm_result *out);
 
-/* Where the resident encodes (kgm_encode_resident, _async) write their result (no
- * counterpart in the reference): `dev_ptr` is any 16-byte aligned memory the context's
+/* Where the encodes (kgm_encode_resident, _async, and the device side of kgm_encode_batch) write
+ * their result (no counterpart in the reference): `dev_ptr` is any 16-byte aligned memory the context's
  * device can write -- its own, or a peer GPU's mapped into this process (CUDA IPC, peer
  * access), which is how the shards of a multi-GPU job land on the gathering GPU while the
  * kernel that encodes them is still running.  The 16-byte {n_bytes, n_lines} header goes
@@ -276,8 +276,9 @@ void  kgm_host_free(void *p);
  * on the current device; `counts` holds world x {int64 bytes, int64 lines}; totals_out (may
  * be NULL) receives {bytes, lines} of the concatenation.  With counts == NULL every slot
  * carries its own sizes instead: {int64 bytes, int64 lines} in its first 16 bytes, the
- * shard behind them (so that sizes and bytes arrive in one transfer).  Asynchronous on
- * `stream`.                                                                               */
+ * shard behind them (so that sizes and bytes arrive in one transfer).  A shard whose size
+ * exceeds its slot or the room left in `out` is left out, and totals_out then receives
+ * {UINT64_MAX, UINT64_MAX}: the output must not be used.  Asynchronous on `stream`.          */
 int  kgm_concat_shards(const uint8_t *slots, uint64_t stride, const int64_t *counts, uint32_t world,
                        uint8_t *out, uint64_t out_cap, uint64_t *totals_out, void *stream);
 

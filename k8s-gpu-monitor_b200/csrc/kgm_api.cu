@@ -732,7 +732,12 @@ int encode_pipelined(kgm_ctx *ctx, const kgm_batch *b, uint32_t chunks, kgm_resu
   int rc = prepare_batch(ctx, b, &gb, &ab);
   const auto t_prepared = now();
   if (rc) return rc;
-  if (!use_fused(ctx) || b->n_docs < 4 * chunks) { rc = upload_batch(ctx, b); return rc ? rc : 1; }
+  // (the lines land in one pinned, mapped buffer of the size of the device's: beyond 2 GiB of
+  // page-locked memory the plain path, which copies n_bytes only, takes the batch)
+  if (!use_fused(ctx) || b->n_docs < 4 * chunks || ctx->out_cap + 16 > (2ull << 30)) {
+    rc = upload_batch(ctx, b);
+    return rc ? rc : 1;
+  }
   const uint32_t n = b->n_docs;
   if ((rc = ensure_workspace(ctx))) return rc;
   constexpr size_t POST_WORDS = 8;                 // one 64-byte line per chunk
@@ -802,6 +807,11 @@ int encode_pipelined(kgm_ctx *ctx, const kgm_batch *b, uint32_t chunks, kgm_resu
     ctx->batch = whole; ctx->work = wfull; ctx->totals_external = false; ctx->chunk_launch = false;
     ctx->fused.carry = nullptr; ctx->fused.post = nullptr;
   };
+  struct Restore {                                 // every way out of the chunk loop puts the whole batch back
+    decltype(restore) &f;
+    bool armed = true;
+    ~Restore() { if (armed) f(); }
+  } guard{restore};
   uint64_t seq[MAX_CHUNKS];
   const uint32_t *d_cnt[MAX_CHUNKS];
   static_assert(CTR_RING > MAX_CHUNKS + 1, "the counter sets of all chunks must survive the call");
@@ -827,11 +837,12 @@ int encode_pipelined(kgm_ctx *ctx, const kgm_batch *b, uint32_t chunks, kgm_resu
     if (c == 0 || piece_of[c] != piece_of[c - 1]) CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_in[piece_of[c]], 0));
     if (c == 0) CU(cudaEventRecord(ctx->ev[EV_H2D], ctx->stream));
     rc = launch_pipeline(ctx);                     // cn > 0; sets wd.counters to this launch's set
-    if (rc) { restore(); return rc; }
+    if (rc) return rc;
     d_cnt[c] = wd.counters;
     CU(cudaEventRecord(ctx->ev_k[c], ctx->stream));
   }
   restore();
+  guard.armed = false;
   CU(cudaEventRecord(ctx->ev[EV_ENC], ctx->stream));
   const auto t_queued = now();
 
@@ -852,7 +863,7 @@ int encode_pipelined(kgm_ctx *ctx, const kgm_batch *b, uint32_t chunks, kgm_resu
     }
     if (!posted()) { overflow = true; break; }     // finished without totals: take the plain path
     const uint64_t nl = post[0] & 0xffffffffffffull, nb = post[1] & 0xffffffffffffull;
-    if (nb > ctx->out_cap || nl > ctx->desc_cap) { overflow = true; break; }
+    if (nb > ctx->work.out_cap || nl > ctx->desc_cap) { overflow = true; break; }   // (work.out_cap: the caller's buffer, if one is set)
     CU(cudaStreamWaitEvent(ctx->s_d2h, ctx->ev_k[c], 0));
     if (nb > bytes_done)
       CU(cudaMemcpyAsync(ctx->h_lines.as<uint8_t>() + bytes_done, ctx->work.out + bytes_done, nb - bytes_done,

@@ -756,11 +756,15 @@ __global__ void k_concat_shards(const uint8_t *slots, uint64_t stride, const lon
   // every block handles every shard in turn (grid-stride over 16-byte units); shard sizes
   // are read from device memory, the destination offset is their running sum
   uint64_t base = 0, lines = 0;
+  bool bad = false;
   for (uint32_t r = 0; r < world; ++r) {
     const long long *hdr = counts ? counts + 2 * r : reinterpret_cast<const long long *>(slots + (uint64_t)r * stride);
-    const uint64_t n = (uint64_t)hdr[0];
+    uint64_t n = (uint64_t)hdr[0];
     const uint8_t *src = slots + (uint64_t)r * stride + (counts ? 0 : 16);
-    if (base + n <= out_cap) {
+    // a size the slot cannot hold (a stale or damaged header) or that does not fit the output:
+    // the shard is left out and the totals say so
+    if (n > stride - (counts ? 0u : 16u) || base + n > out_cap) { bad = true; n = 0; }
+    if (n) {
       uint8_t *dst = out + base;
       const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (uint64_t)gridDim.x * blockDim.x;
       // bytes up to the destination's 16-byte boundary, realigned vectors, tail bytes
@@ -783,7 +787,10 @@ __global__ void k_concat_shards(const uint8_t *slots, uint64_t stride, const lon
     base += n;
     lines += (uint64_t)hdr[1];
   }
-  if (totals_out && blockIdx.x == 0 && threadIdx.x == 0) { totals_out[0] = base; totals_out[1] = lines; }
+  if (totals_out && blockIdx.x == 0 && threadIdx.x == 0) {
+    totals_out[0] = bad ? ~0ull : base;
+    totals_out[1] = bad ? ~0ull : lines;
+  }
 }
 
 }  // namespace
@@ -793,7 +800,15 @@ extern "C" int kgm_concat_shards(const uint8_t *slots, uint64_t stride, const in
                                  uint8_t *out, uint64_t out_cap, uint64_t *totals_out, void *stream) {
   if (!slots || !out || !world || (stride & 15) || (reinterpret_cast<uintptr_t>(slots) & 15))
     return KGM_E_INVALID;
-  kgm::k_concat_shards<<<148 * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  static int sm_count[64];                           // per device
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return KGM_E_CUDA;
+  int sms = dev >= 0 && dev < 64 ? sm_count[dev] : 0;
+  if (!sms) {
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) return KGM_E_CUDA;
+    if (dev >= 0 && dev < 64) sm_count[dev] = sms;
+  }
+  kgm::k_concat_shards<<<sms * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       slots, stride, reinterpret_cast<const long long *>(counts), world, out, out_cap,
       reinterpret_cast<unsigned long long *>(totals_out));
   return cudaGetLastError() == cudaSuccess ? KGM_OK : KGM_E_CUDA;

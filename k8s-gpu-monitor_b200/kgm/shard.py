@@ -423,7 +423,10 @@ class ShardGather:
             if not self._packed:
                 self.pack()
                 self.stream.synchronize()
-            return self.final[:int(self.totals_dev[0].item())]
+            total = int(self.totals_dev[0].item())
+            if total < 0:                            # {UINT64_MAX, UINT64_MAX}: a shard did not fit its slot or `final`
+                raise RuntimeError("kgm_concat_shards left a shard out (size header beyond the slot or the buffer)")
+            return self.final[:total]
         total = int(self.last_offsets[-1, 0])
         return self.final[:total]
 

@@ -51,3 +51,24 @@ def test_slots_that_carry_their_own_sizes():
     want = b"".join(host[r * stride + 16:r * stride + 16 + s].tobytes() for r, s in enumerate(sizes))
     assert out.cpu().numpy()[:len(want)].tobytes() == want
     assert totals.cpu().tolist() == [sum(sizes), sum(s + 5 for s in sizes)]
+
+
+def test_a_size_beyond_the_slot_or_the_output_is_reported():
+    """A header that claims more than its slot holds, or shards that do not fit the output:
+    the totals read {UINT64_MAX, UINT64_MAX} and nothing is written past the buffers."""
+    torch = pytest.importorskip("torch")
+    lib = _ffi.load()
+    dev = torch.device("cuda", 0)
+    stride = 4128
+    for sizes, out_bytes in (([700, 5000, 64], 8192), ([700, 800, 64], 1000)):
+        host = np.zeros(len(sizes) * stride, np.uint8)
+        for r, s in enumerate(sizes):
+            host[r * stride:r * stride + 16] = np.frombuffer(np.asarray([s, 1], np.int64).tobytes(), np.uint8)
+        slots = torch.from_numpy(host).to(dev)
+        out = torch.full((out_bytes + 64,), 0xEE, dtype=torch.uint8, device=dev)
+        totals = torch.zeros(2, dtype=torch.int64, device=dev)
+        assert lib.kgm_concat_shards(slots.data_ptr(), stride, None, len(sizes), out.data_ptr(), out_bytes,
+                                     totals.data_ptr(), None) == 0
+        torch.cuda.synchronize(dev)
+        assert totals.cpu().tolist() == [-1, -1]
+        assert out.cpu().numpy()[out_bytes:].tobytes() == b"\xee" * 64
