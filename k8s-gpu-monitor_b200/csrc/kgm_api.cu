@@ -622,10 +622,10 @@ void plan_poll2(kgm_ctx *ctx, const kgm_batch *b, uint64_t max_g, uint64_t max_a
   const uint32_t lines = ctx->force_lines ? ctx->force_lines : 16u;
   Poll2Params q{};
   if (!poll2_layout(ctx, lines, max_g, max_a, &q)) return;
-  // Rounds: pod lines first in a batch of a few waves (the documents start together and wait for
-  // each other's sizes: a longer first round hides more of that), node lines first in a long
-  // one (measured both ways on the configs[1] and configs[2] batches, profiles/README.md).
-  q.pods_first = b->n_docs < 4u * (uint32_t)ctx->sms * 16u ? 1u : 0u;
+  // Rounds: the pod lines first, the node lines last (the output order is the document's either
+  // way): the look-back is resolved after the first round, and the longer that round, the fewer
+  // documents wait there for their predecessors' sizes (measured on every bench configuration).
+  q.pods_first = 1u;
   if (const char *env = getenv("KGM_POLL2_PODS_FIRST")) q.pods_first = atoi(env) ? 1u : 0u;
   // tickets per CTA (its warps start `warps` consecutive documents together and so run through the
   // same code at about the same time: fewer instruction-cache misses) -- equal or faster on every
