@@ -492,13 +492,72 @@ KGM_HD LineWriter compose_line_t(uint32_t *B, const uint8_t *slot, uint32_t rec,
   lw_put8(w, 10u, 0u, 1u);                           // '\n'
   return w;
 }
-// Writes one line at byte offset `dst` of the word array B: `slot` = the line's template slot
-// (global memory), `rec` = byte offset of its record in B (16-byte aligned).  Returns the writer:
-// its pending bytes still have to be stored (lw_finish).  (`ca` is the table form's.)
+// ---- the loop form ------------------------------------------------------------------------------
+// One loop over the segment table with the same primitives as the unrolled form (slot stream,
+// branch-free short cells): a body of a few hundred instructions instead of the unrolled form's
+// 2000.  Built because 40 % of the composing warps' stall samples are instruction fetch
+// (profiles/README.md, round 2) -- and measured 7 - 9 % SLOWER than the unrolled form on every
+// bench configuration (it executes more instructions per line), so the kernels use the unrolled
+// form; -DKGM_COMPOSE_LOOP switches, the CPU tests compare all three forms byte for byte.
+// a cell of at most 16 bytes without a branch on its length; longer ones through lw_put
+KGM_HD void lw_put_cell16(LineWriter &w, const uint32_t *B, uint32_t pw) {
+  const uint32_t len = rw_len(pw), so = rw_off(pw);
+  if (len > 16u) { lw_put(w, B + (so >> 2), so & 3u, len); return; }
+  const uint32_t *p = B + (so >> 2);
+  const uint32_t s = 8u * (so & 3u);
+  const uint32_t a = p[0], b = p[1], c = p[2];
+  if (len <= 8u) {                                   // (one branch, taken alike by nearly all lanes of a segment)
+    const uint32_t v0 = funnel_r(a, b, s) & low_mask(len < 4u ? len : 4u);
+    const uint32_t v1 = funnel_r(b, c, s) & low_mask(len > 4u ? len - 4u : 0u);
+    lw_put8(w, v0, v1, len);
+  } else {
+    const uint32_t d = p[3], e = p[4];
+    lw_put_w2(w, funnel_r(a, b, s), funnel_r(b, c, s));
+    const uint32_t r = len - 8u;
+    const uint32_t v0 = funnel_r(c, d, s) & low_mask(r < 4u ? r : 4u);
+    const uint32_t v1 = funnel_r(d, e, s) & low_mask(r > 4u ? r - 4u : 0u);
+    lw_put8(w, v0, v1, r);
+  }
+}
+KGM_HD LineWriter compose_line_loop(uint32_t *B, uint32_t ca, uint32_t pod, const uint8_t *slot, uint32_t rec,
+                                    uint32_t dst) {
+  const uint8_t *Bb = reinterpret_cast<const uint8_t *>(B);
+  const uint8_t *st = Bb + ca + CA2::SEGTAB + (pod ? 32u : 0u);
+  const uint32_t *sw = reinterpret_cast<const uint32_t *>(slot);
+  const uint32_t *kt = B + ((ca + CA2::KTAB) >> 2), *rw_ = B + (rec >> 2);
+  const uint32_t nseg = pod ? POD_SEGS : NODE_SEGS;
+  SlotStream s;
+  ss_open(s, slot);
+  LineWriter w;
+  w.d = B + (dst >> 2);
+  w.fill = dst & 3u;
+  w.pend = 0;
+  for (uint32_t k = 0; k < nseg; ++k) {
+    const uint32_t e = st[k], type = e >> 6, idx = e & 63u;
+    if (type == 0u) {
+#if defined(__CUDA_ARCH__)
+      const uint32_t pw = __ldg(sw + idx);
+#else
+      const uint32_t pw = sw[idx];
+#endif
+      lw_put_stream(w, s, rw_len(pw));
+    } else {
+      lw_put_cell16(w, B, type == 1u ? kt[idx] : rw_[idx]);
+    }
+  }
+  return w;
+}
+// Writes one line at byte offset `dst` of the word array B: `ca` = byte offset of the constant area
+// in B, `slot` = the line's template slot (global memory), `rec` = byte offset of its record in B
+// (16-byte aligned).  Returns the writer: its pending bytes still have to be stored (lw_finish).
 KGM_HD LineWriter compose_line(uint32_t *B, uint32_t ca, uint32_t pod, const uint8_t *slot, uint32_t rec,
                                uint32_t dst) {
+#if defined(KGM_COMPOSE_LOOP)
+  return compose_line_loop(B, ca, pod, slot, rec, dst);
+#else
   (void)ca;
   return pod ? compose_line_t<true>(B, slot, rec, dst) : compose_line_t<false>(B, slot, rec, dst);
+#endif
 }
 // The last bytes of a line, after every line of the round has been written: OR-ed into the word
 // the next line has started (`has_next`), or stored as they are.

@@ -289,6 +289,11 @@ static uint32_t p2_write(P2Mem &m, uint32_t pod, uint32_t rec, uint32_t dst, uin
   p2::LineWriter w3 = p2::compose_line_table(m.words.data(), 0u, pod, slot, rec, dst2);
   p2::lw_finish(w3, false);
   if (w1.fill != w3.fill || memcmp(m.bytes() + dst, m.bytes() + dst2, len) != 0) return 0xffffffffu;
+  // ... and the loop form, further up again
+  const uint32_t dst3 = ((dst2 + len + 64) & ~3u) + 64 + (dst & 3u);
+  p2::LineWriter w4 = p2::compose_line_loop(m.words.data(), 0u, pod, slot, rec, dst3);
+  p2::lw_finish(w4, false);
+  if (w1.fill != w4.fill || memcmp(m.bytes() + dst, m.bytes() + dst3, len) != 0) return 0xffffffffu;
   return len;
 }
 
