@@ -161,6 +161,7 @@ def build_workload(config, rank, world=1, variant=0):
         mine = [n for n in range(nodes) if owner[n] == rank]       # so a rank's work does not change with the world size
         rp = _replay_of_nodes(replay, 0, mine, window, tick0=variant * window, gpus=8, containers=8,
                               procs_per_container=4)
+        rp.node_ids, rp.window, rp.tick0 = mine, window, variant * window      # (for the device-side generator)
         info = {"hosts_total": nodes, "hosts_this_rank": len(mine), "window_ticks": window,
                 "windows_per_hour": 3600 // window, "partition": "assign_hosts, equal weights (one eighth per rank)"}
     elif config == "config5":
@@ -336,6 +337,7 @@ def run_kgm_arm(args):
     if not sharded and world > rotate:
         rotate = min(world, 8)
     built = {}
+    device_gen = None
     for v in range(rotate):
         if sharded:
             rp, entries, shard_info = build_workload(args.config, rank, world, variant=v if args.config == "config4" else 0)
@@ -347,7 +349,18 @@ def run_kgm_arm(args):
         mon.set_pipeline({"fused": 0, "staged": 1, "fused-generic": 2, "fused-v1": 3, "fused-v2": 4}[args.pipeline])
         mon.load_fleet(entries)
         batch = mon.make_batch(rp.gpu_texts, rp.apps_texts, rp.doc_node, rp.doc_tick, pinned=True)
-        mon.upload(batch)
+        if args.config == "config4":
+            # the resident window comes from the device-side generator (kgm_replay_fill): same bytes as the
+            # host generator's (tests/test_replay_gpu.py; sizes re-checked here), never on the host
+            from kgm import replay_device
+            if device_gen is None:
+                device_gen = replay_device.DeviceReplay(rp.nodes, rp.node_ids, 0, device=local_rank)
+            win = device_gen.window(rp.tick0, rp.window)
+            if (win.gpu_bytes, win.apps_bytes, win.n_docs) != (batch.gpu_bytes, batch.apps_bytes, batch.n_docs):
+                raise SystemExit("device generator and host generator disagree on the window's sizes")
+            win.upload(mon)
+        else:
+            mon.upload(batch)
         mons.append(mon); batches.append(batch); rps.append(rp)
     samples_step = [rp.n_samples() for rp in rps]
     sizes = []
@@ -538,6 +551,44 @@ def run_kgm_arm(args):
     launches_per_step = int(last_t["launches"])
     slow_docs = int(last_t["slow_docs"])
 
+    # ---- configs[3] streamed: window after window of the hour, generated on the device, encoded, ----
+    # ---- checksummed (sizes) and discarded; untimed by the contract's bracket, reported on its own ----
+    stream_info = None
+    if args.config == "config4" and device_gen is not None and args.stream_windows > 0:
+        mon = mons[0]
+        if gather is not None and gather.mode == "push":
+            mon.set_output_buffer(0, 0)
+        torch.cuda.synchronize(device)
+        t0 = time.perf_counter()
+        done_w = tot_lines = tot_bytes = tot_samples = 0
+        win_ticks = rps[0].window
+        for wdx in range(args.stream_windows):
+            win = device_gen.window(wdx * win_ticks, win_ticks)
+            win.upload(mon)
+            r = mon.encode_resident()
+            tot_lines += int(r.n_lines); tot_bytes += int(r.n_bytes)
+            tot_samples += samples_step[0]           # every window has the same hosts and ticks
+            done_w += 1
+            if time.perf_counter() - t0 > args.stream_seconds:
+                break
+        torch.cuda.synchronize(device)
+        secs = time.perf_counter() - t0
+        agg = torch.tensor([float(tot_samples), float(tot_lines), float(tot_bytes), float(done_w)], dtype=torch.float64,
+                           device=device)
+        tmax = torch.tensor([secs], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(agg, op=dist.ReduceOp.SUM)
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        stream_info = {"windows_per_rank": done_w, "of_windows_per_hour": 3600 // win_ticks,
+                       "samples": int(agg[0].item()), "lines": int(agg[1].item()), "bytes": int(agg[2].item()),
+                       "seconds": float(tmax[0].item()), "samples_per_s": float(agg[0].item() / tmax[0].item()),
+                       "what": "per window: kgm_replay_offsets + kgm_replay_fill (texts generated in HBM), "
+                               "kgm_upload_batch from device memory, kgm_encode_resident; sizes summed as the "
+                               "checksum, output discarded; wall clock, synchronous, one context"}
+        # the first window back into the context for the end-to-end leg's sizes
+        device_gen.window(rps[0].tick0, win_ticks).upload(mon)
+        mon.encode_resident()
+
     # ---- end to end through the C ABI with host buffers ----
     e2e_times = []
     e2e_warm = max(args.warmup, rotate)              # every context's first call allocates its pinned result buffers
@@ -656,6 +707,7 @@ def run_kgm_arm(args):
                     "note": "kgm_encode_batch with pinned host buffers: chunked H2D / k_poll / D2H overlap; "
                             "bounded below by the D2H copy of the result over PCIe (d2h_copy_alone_ms)"},
             "gpu_launches": launches_per_step * args.steps,
+            "stream": stream_info,
             "clocks": clocks.summary(),
         }
         if world > 1:
@@ -681,6 +733,9 @@ def main():
     ap.add_argument("--impl", default="kgm", choices=["kgm", "reference"])
     ap.add_argument("--config", default="config2", choices=["config1", "config2", "config3", "config4", "config5"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--stream-windows", type=int, default=900,
+                    help="config4: windows of the hour streamed after the timed region (0 = none)")
+    ap.add_argument("--stream-seconds", type=float, default=20.0, help="config4: stop streaming after this long")
     ap.add_argument("--pipeline", default="fused", choices=["fused", "staged", "fused-generic", "fused-v1", "fused-v2"])
     args = ap.parse_args()
     if args.warmup < 3:

@@ -157,7 +157,9 @@ int  kgm_encode_batch(kgm_ctx *ctx, const kgm_batch *batch, int want_host_copy, 
 
 /* The same in two steps, for callers that keep a batch resident in HBM and run it more
  * than once (bench.py's device-timed region).  kgm_encode_resident returns device
- * pointers.                                                                               */
+ * pointers.  For kgm_upload_batch the two texts (gpu_csv, apps_csv) may also be DEVICE
+ * pointers (texts produced on the GPU, e.g. by kgm_replay_fill); the offset and per-document
+ * arrays are always host memory (they are validated on the host).                          */
 int  kgm_upload_batch(kgm_ctx *ctx, const kgm_batch *batch);
 int  kgm_encode_resident(kgm_ctx *ctx, kgm_result *out);
 
@@ -281,6 +283,38 @@ void  kgm_host_free(void *p);
  * {UINT64_MAX, UINT64_MAX}: the output must not be used.  Asynchronous on `stream`.          */
 int  kgm_concat_shards(const uint8_t *slots, uint64_t stride, const int64_t *counts, uint32_t world,
                        uint8_t *out, uint64_t out_cap, uint64_t *totals_out, void *stream);
+
+/* Replay generator on the device (bench / test plumbing; no counterpart in the reference, which
+ * reads live `nvidia-smi` output, gpu.py:104-116): writes the two nvidia-smi texts of n_nodes x
+ * n_ticks polls (host-major: all ticks of host 0, then host 1, ...) straight into device memory,
+ * byte for byte what k8s-gpu-monitor_b200/kgm/replay.py make_texts() produces for the same
+ * coordinates (every value is a counter-based hash of (seed, host, gpu or process, tick)).
+ * All pointers in the spec and in the calls are DEVICE pointers on the current device.
+ *   kgm_replay_offsets  fills gpu_off / apps_off (n_docs + 1 each: exclusive byte offsets, the last
+ *                       entry = the total) from the sizes; len_scratch: 2 x n_docs words
+ *   kgm_replay_fill     writes the texts at those offsets
+ * Both are asynchronous on `stream`.                                                          */
+typedef struct {
+  uint64_t seed;
+  uint32_t n_nodes;
+  uint32_t mem_total_mib;        /* what the memory.total column prints                          */
+  const uint32_t *node_id;       /* [n_nodes] the host's number in the fleet (a hash coordinate) */
+  const uint8_t  *mig;           /* [n_nodes] 0 plain, 1 MIG parents ([N/A] utilization), 2 also MIG uuids in process rows */
+  const uint32_t *gpu_begin;     /* [n_nodes + 1] first gpu of a host in `uuid`                  */
+  const uint8_t  *uuid;          /* 40 bytes per gpu ("GPU-8-4-4-4-12"), no terminator           */
+  const uint32_t *proc_begin;    /* [n_nodes + 1] first process row of a host, rows GPU-major    */
+  const uint32_t *proc_pid;
+  const uint16_t *proc_ci;       /* container ordinal and process ordinal inside it (hash coordinates) */
+  const uint8_t  *proc_j;
+  const uint8_t  *proc_gpu;      /* gpu ordinal on the host                                      */
+  const uint8_t  *proc_name;     /* index into the process-name pool                             */
+  const uint8_t  *names;         /* process-name pool                                            */
+  const uint32_t *name_off;      /* [names + 1]                                                  */
+} kgm_replay_spec;
+int  kgm_replay_offsets(const kgm_replay_spec *spec, uint32_t tick0, uint32_t n_ticks, uint32_t *len_scratch,
+                        uint64_t *gpu_off, uint64_t *apps_off, void *stream);
+int  kgm_replay_fill(const kgm_replay_spec *spec, uint32_t tick0, uint32_t n_ticks, const uint64_t *gpu_off,
+                     const uint64_t *apps_off, uint8_t *gpu_csv, uint8_t *apps_csv, void *stream);
 
 /* Stream-ordered counters between the GPUs of one job (no counterpart in the reference).  The
  * ranks tell each other "my shard of step k has landed in your slot" and "that slot set is free

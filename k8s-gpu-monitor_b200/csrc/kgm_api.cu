@@ -167,7 +167,7 @@ int cuda_fail(kgm_ctx *c, cudaError_t e, const char *what) {
 template <class T>
 int upload(kgm_ctx *ctx, DevBuf &buf, const T *src, size_t n) {
   CU(buf.ensure(std::max<size_t>(n, 1) * sizeof(T)));
-  if (n) CU(cudaMemcpyAsync(buf.p, src, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+  if (n) CU(cudaMemcpyAsync(buf.p, src, n * sizeof(T), cudaMemcpyDefault, ctx->stream));   // (host or device source: unified addressing)
   return KGM_OK;
 }
 

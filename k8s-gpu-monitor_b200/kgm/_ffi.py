@@ -81,6 +81,14 @@ class KgmWindows(C.Structure):
                 ("m_last", C.c_void_p * 3), ("m_sum", C.c_void_p * 3), ("m_mean", C.c_void_p * 3)]
 
 
+class KgmReplaySpec(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("n_nodes", C.c_uint32), ("mem_total_mib", C.c_uint32),
+                ("node_id", C.c_void_p), ("mig", C.c_void_p), ("gpu_begin", C.c_void_p), ("uuid", C.c_void_p),
+                ("proc_begin", C.c_void_p), ("proc_pid", C.c_void_p), ("proc_ci", C.c_void_p),
+                ("proc_j", C.c_void_p), ("proc_gpu", C.c_void_p), ("proc_name", C.c_void_p),
+                ("names", C.c_void_p), ("name_off", C.c_void_p)]
+
+
 class KgmTiming(C.Structure):
     _fields_ = [
         ("h2d_ms", C.c_float), ("tokenize_ms", C.c_float), ("join_ms", C.c_float),
@@ -121,6 +129,10 @@ SIGNATURES = {
     "kgm_concat_shards": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64,
                                     C.c_void_p, C.c_void_p]),
     "kgm_window_reduce": (C.c_int, [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]),
+    "kgm_replay_offsets": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p]),
+    "kgm_replay_fill": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                  C.c_void_p, C.c_void_p]),
     "kgm_flush_l2": (C.c_int, [C.c_void_p, C.c_uint64]),
     "kgm_host_alloc": (C.c_void_p, [C.c_uint64]),
     "kgm_host_free": (None, [C.c_void_p]),
