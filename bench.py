@@ -419,6 +419,11 @@ def run_kgm_arm(args):
                 acc[k].append(val)
             done_samples += samples_step[v]
 
+    fake_push = None
+    if os.environ.get("KGM_BENCH_FAKE_PUSH") and gather is None:
+        fake_push = (torch.cuda.Stream(device),
+                     [torch.empty(((n_bytes + (1 << 20)) // 16) * 16, dtype=torch.uint8, device=device) for _ in range(rotate)])
+
     def step(i, timed):
         nonlocal done_samples
         v = i % rotate
@@ -435,6 +440,13 @@ def run_kgm_arm(args):
                 r = gather.push_step(mon)            # step's gathering rank, tell it the shard has landed
             else:
                 r = mon.encode_resident_async()
+                if fake_push is not None:            # (experiment) the copy traffic of a multi-GPU step, on one GPU
+                    side, bufs = fake_push
+                    side.wait_stream(ext[v])
+                    with torch.cuda.stream(side):
+                        src = shard.tensor_of_device_buffer(int(r.lines) - 16, bufs[v].numel(), device)
+                        bufs[v].copy_(src, non_blocking=True)
+                    ext[v].wait_stream(side) if os.environ.get("KGM_BENCH_FAKE_PUSH") == "2" else None
             if serialize:
                 last_launch[0] = torch.cuda.Event()
                 last_launch[0].record(ext[v])
