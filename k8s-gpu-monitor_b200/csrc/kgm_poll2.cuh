@@ -2,24 +2,29 @@
 // (included by kgm_kernels.cu after kgm_fused.cuh, whose look-back and generic-path functions it
 // uses).
 //
-// Documents are handed out in batch order by a ticket counter.  A regular document lives in its
-// warp's slice of shared memory (12 - 18 KB, 12 - 18 documents in flight per SM):
+// Documents are handed out in batch order by a ticket counter, 16 consecutive ones to a CTA at a
+// time (one per warp; the warps of a CTA meet again before the next 16, so they run through the
+// same code at about the same time -- the hot path is 128 KB of instructions).  A regular document
+// lives in its warp's slice of shared memory (12 - 18 KB, 16 documents in flight per SM):
 //   text windows  <- cp.async of the two nvidia-smi texts (16-byte units)     (gpu.py:104-116)
 //   rows          <- SWAR line-feed scan; one lane per row: cells, digit runs, keys, repr(mem_util)
-//   join          <- uuid -> short id against the gpu rows, pid -> container probe of the
-//                    HBM-resident table, container-major placement          (gpu.py:119-128,151,172-178)
+//   join          <- uuid -> short id against the gpu rows (key hashes by shuffle, bytes compared
+//                    once), pid -> container probe of the HBM-resident table, container-major
+//                    placement; an unknown uuid = the KeyError of gpu.py:151: node lines + status
+//                                                                          (gpu.py:119-128,151,172-178)
 //   records       <- per row the run words of its variable cells; per line: record, template
 //                    slot, length
 //   device-wide exclusive scan over documents by decoupled look-back (kgm_fused.cuh)
-//   rounds        <- up to 32 lines at a time, one lane per line: every lane streams its line's
-//                    segments (template pieces straight from the slot pool in global memory with
-//                    16-byte loads, cells from the text windows) through a pending word into the
-//                    stage, so all lanes run the same segment sequence; the warp then streams the
-//                    stage out with aligned 16-byte stores, realigned to the document's position
-//                    in the output                                          (gpu.py:136-143,206-216,240-250)
-// A document the fast path declines (any raise point of the reference, unusual bytes, duplicate
-// keys, sizes beyond the slice) is re-done from scratch by the generic per-byte code, out of
-// line, and joins the same look-back chain: same bytes either way.
+//   rounds        <- up to 32 lines of one kind at a time (pod rounds first), one lane per line: the
+//                    unrolled composer of kgm_poll2_leaf.cuh writes the line through a pending word
+//                    into the stage (template pieces from the slot pool in global memory as one
+//                    prefetched stream of 16-byte loads, cells from the text windows, constant
+//                    strings as immediates); the warp then streams the stage out with aligned
+//                    16-byte streaming stores, realigned to the document's position in the output
+//                                                                          (gpu.py:136-143,206-216,240-250)
+// A document the fast path declines (any other raise point of the reference, unusual bytes,
+// duplicate keys, sizes beyond the slice) is re-done from scratch by the generic per-byte code, out
+// of line, and joins the same look-back chain: same bytes either way.
 #pragma once
 
 #include "kgm_poll2_leaf.cuh"
