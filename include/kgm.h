@@ -233,6 +233,10 @@ typedef struct kgm_windows {
   const double   *m_mean[3];
 } kgm_windows;
 int  kgm_window_reduce(kgm_ctx *ctx, uint32_t window_ticks, int want_host_copy, kgm_windows *out);
+/* Which front end the last kgm_window_reduce took its samples from: 1 = the planning half of k_poll2
+ * (one launch over the resident texts), 0 = the staged tokenizer + join (any document the fast path
+ * declines sends the whole batch there; KGM_WINDOW_STAGED_FRONT=1 forces it); negative = KGM_E_*.  */
+int  kgm_window_front(kgm_ctx *ctx);
 
 /* Debug aid (no counterpart in the reference): when the library was built with
  * -DKGM_PROFILE_STAGES, copies the fused kernel's per-stage SM-clock sums (64 values: 32

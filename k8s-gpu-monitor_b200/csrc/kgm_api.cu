@@ -135,7 +135,8 @@ struct kgm_ctx {
   // window reductions
   uint32_t max_tick = 0;
   bool have_ticks = false;
-  DevBuf w_win_samples, w_win_groups, w_win_temp;
+  DevBuf w_win_samples, w_win_groups, w_win_temp, w_win_scal;
+  bool win_front_fused = false;            // the last kgm_window_reduce took its samples from k_poll2_samples
   HostBuf h_win_groups;
 
   // results
@@ -1007,7 +1008,7 @@ void kgm_destroy(kgm_ctx *ctx) {
                    &ctx->w_line_off, &ctx->w_out, &ctx->w_flush, &ctx->w_ticket, &ctx->w_scan,
                    &ctx->f_node_fast, &ctx->f_tb_off, &ctx->f_tb_len, &ctx->f_tb_pool, &ctx->f_pid16,
                    &ctx->f_vis_hash2, &ctx->f_node_fast2, &ctx->f_nslot_off, &ctx->f_tslot_off, &ctx->f_slot_pool, &ctx->f_ca2,
-                   &ctx->w_win_samples, &ctx->w_win_groups, &ctx->w_win_temp};
+                   &ctx->w_win_samples, &ctx->w_win_groups, &ctx->w_win_temp, &ctx->w_win_scal};
   for (DevBuf *b : dev) b->release();
   HostBuf *host[] = {&ctx->h_small, &ctx->h_lines, &ctx->h_line_off, &ctx->h_doc_line_off, &ctx->h_status,
                      &ctx->h_chunk, &ctx->h_docarr, &ctx->h_win_groups};
@@ -1532,29 +1533,62 @@ int kgm_window_reduce(kgm_ctx *ctx, uint32_t window_ticks, int want_host_copy, k
   if (ctx->max_tick / window_ticks > 0xffffu || ctx->max_tick >= (1u << 20) || ctx->batch.n_docs >= (1u << 26) ||
       ctx->fleet.n_containers >= 0x7fffffffu)
     return KGM_E_LIMIT;
-  uint32_t n_desc = 0;
-  int rc = run_plan_only(ctx, &n_desc);
-  if (rc) return rc;
   *out = kgm_windows{};
-  if (n_desc == 0) return KGM_OK;
-  // samples
-  const size_t n = n_desc;
-  const size_t sample_bytes = 6 * ((n * 8 + 255) & ~(size_t)255) + 4096;
-  CU(ctx->w_win_samples.ensure(sample_bytes));
-  Carver c{ctx->w_win_samples.as<uint8_t>()};
-  WinSamples s{};
-  s.key = c.take<uint64_t>(n); s.order = c.take<uint64_t>(n);
-  s.idx = c.take<uint32_t>(n);
-  for (int m = 0; m < 3; ++m) s.val[m] = c.take<uint32_t>(n);
-  s.node = c.take<uint32_t>(n);
-  // the batch's largest short id and its window range size the index space
-  CU(ctx->w_win_temp.ensure(256));
   uint32_t *h32 = ctx->h_small.as<uint32_t>();
-  h32[0] = 0; h32[1] = 0xffffffffu; h32[2] = 0; h32[3] = 0;
-  CU(cudaMemcpyAsync(ctx->w_win_temp.p, h32, 16, cudaMemcpyHostToDevice, ctx->stream));
-  CU(launch_window_samples(ctx->batch, ctx->work, n_desc, window_ticks, s, ctx->w_win_temp.as<uint32_t>(), ctx->stream));
-  CU(cudaMemcpyAsync(h32, ctx->w_win_temp.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
-  CU(cudaStreamSynchronize(ctx->stream));
+  auto carve_samples = [&](size_t n, WinSamples *s) -> int {
+    const size_t sample_bytes = 6 * ((n * 8 + 255) & ~(size_t)255) + 4096;
+    CU(ctx->w_win_samples.ensure(sample_bytes));
+    Carver c{ctx->w_win_samples.as<uint8_t>()};
+    s->key = c.take<uint64_t>(n); s->order = c.take<uint64_t>(n);
+    s->idx = c.take<uint32_t>(n);
+    for (int m = 0; m < 3; ++m) s->val[m] = c.take<uint32_t>(n);
+    s->node = c.take<uint32_t>(n);
+    return KGM_OK;
+  };
+  // scal: the batch's largest short id and its window range (they size the index space); [3] = documents
+  // the fused front end declined
+  CU(ctx->w_win_scal.ensure(256));
+  uint32_t *scal = ctx->w_win_scal.as<uint32_t>();
+  auto reset_scal = [&]() -> int {
+    h32[0] = 0; h32[1] = 0xffffffffu; h32[2] = 0; h32[3] = 0;
+    CU(cudaMemcpyAsync(scal, h32, 16, cudaMemcpyHostToDevice, ctx->stream));
+    return KGM_OK;
+  };
+  int rc;
+  uint32_t n_desc = 0;                                         // sample places
+  WinSamples s{};
+  // Front end 1: the planning half of k_poll2 writes the samples itself (one launch over the resident
+  // texts).  Any document it declines -> front end 2 takes the whole batch.
+  bool fused_front = ctx->poll2_ok && ctx->p2_any && ctx->pipeline != KGM_PIPELINE_STAGED &&
+                     ctx->pipeline != KGM_PIPELINE_FUSED_GENERIC && !getenv("KGM_WINDOW_STAGED_FRONT") &&
+                     (uint64_t)ctx->batch.n_docs * ctx->poll2.cap_lines < (1ull << 31);
+  ctx->win_front_fused = false;
+  if (fused_front) {
+    const uint32_t stride = ctx->poll2.cap_lines;
+    n_desc = ctx->batch.n_docs * stride;
+    if ((rc = carve_samples(n_desc, &s)) || (rc = reset_scal())) return rc;
+    WinFront wo{};
+    wo.s = s; wo.stride = stride; wo.window_ticks = window_ticks; wo.declined = scal + 3;
+    const int wpb = (int)ctx->poll2.warps;
+    const int blocks = std::max(1, std::min((int)((ctx->batch.n_docs + wpb - 1) / wpb), ctx->sms));
+    launch_poll2_samples(ctx->batch, ctx->fleet, ctx->work, ctx->fused, ctx->poll2, wo, blocks, ctx->device, ctx->stream);
+    CU(cudaGetLastError());
+    CU(launch_window_scal(s, n_desc, scal, ctx->stream));
+    CU(cudaMemcpyAsync(h32, scal, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (h32[3] != 0) fused_front = false;
+    ctx->win_front_fused = fused_front;
+  }
+  // Front end 2: the staged tokenizer + join leave the token tables and the line plan; k_win_samples
+  // reads them.
+  if (!fused_front) {
+    if ((rc = run_plan_only(ctx, &n_desc))) return rc;
+    if (n_desc == 0) return KGM_OK;
+    if ((rc = carve_samples(n_desc, &s)) || (rc = reset_scal())) return rc;
+    CU(launch_window_samples(ctx->batch, ctx->work, n_desc, window_ticks, s, scal, ctx->stream));
+    CU(cudaMemcpyAsync(h32, scal, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+  }
   if (h32[1] == 0xffffffffu) return KGM_OK;                    // no line was emitted
   WinIndex x{};
   x.n_nodes = ctx->fleet.n_nodes;
@@ -1597,6 +1631,11 @@ int kgm_window_reduce(kgm_ctx *ctx, uint32_t window_ticks, int want_host_copy, k
     out->m_last[m] = r.m_last[m]; out->m_sum[m] = r.m_sum[m]; out->m_mean[m] = r.m_mean[m];
   }
   return KGM_OK;
+}
+
+int kgm_window_front(kgm_ctx *ctx) {
+  if (!ctx) return KGM_E_INVALID;
+  return ctx->win_front_fused ? 1 : 0;
 }
 
 int kgm_debug_stage_clocks(uint64_t *out64) {

@@ -130,6 +130,9 @@ void launch_poll(const BatchDev &b, const FleetDev &f, const WorkDev &w, const F
 void launch_poll2(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P, const Poll2Params &Q,
                   int blocks, int device, cudaStream_t s);
 int poll2_smem_bytes(const Poll2Params &Q);
+struct WinFront;
+void launch_poll2_samples(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P,
+                          const Poll2Params &Q, const WinFront &wo, int blocks, int device, cudaStream_t s);
 int poll2_max_warps();                          // warps per CTA k_poll2 was compiled for
 int poll_smem_bytes(const FusedParams &P);
 int debug_stage_clocks(unsigned long long *out64);   // 0 unless built with -DKGM_PROFILE_STAGES

@@ -28,6 +28,7 @@
 #pragma once
 
 #include "kgm_poll2_leaf.cuh"
+#include "kgm_window.cuh"
 
 namespace kgm {
 namespace {
@@ -69,10 +70,24 @@ __device__ __forceinline__ void window_trim(uint8_t *dst, uint64_t lo, uint64_t 
 constexpr uint32_t CP_NONE = 0x7fffu;                // cp word: screened << 31 | crank << 16 | pos
 
 // One regular document, planned and written by one warp.  Returns false (nothing published or
-// written yet) if the generic path has to take it.
+// written yet) if the generic path has to take it.  SAMPLES: the planning half only, feeding stage 3
+// -- every line the document would emit becomes a (key, order, values) sample at wo->s[d * stride +
+// line] instead of bytes (kgm_window.cu; same values as the staged front end's k_win_samples).
+template <bool SAMPLES>
 __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P,
-                            const Poll2Params &Q, uint32_t *S, uint32_t s0, const P2Slice &sl) {
+                            const Poll2Params &Q, uint32_t *S, uint32_t s0, const P2Slice &sl, const WinFront *wo) {
   const uint32_t l = lane_id();
+  // (SAMPLES) where the document's samples go, its window, and the short id of every process row
+  const uint64_t sbase = SAMPLES ? (uint64_t)d * wo->stride : 0ull;
+  const uint32_t tick = SAMPLES ? b.doc_tick[d] : 0u, window = SAMPLES ? tick / wo->window_ticks : 0u;
+  uint8_t *sidv = reinterpret_cast<uint8_t *>(S) + sl.stage + Q.stage_bytes - Q.cap_np;
+  auto put_sample = [&](uint32_t idx, uint64_t key, uint32_t util, uint32_t mem, uint32_t power) {
+    const uint64_t i = sbase + idx;
+    wo->s.key[i] = key;
+    wo->s.order[i] = win_order(tick, d, idx);
+    wo->s.val[0][i] = util; wo->s.val[1][i] = mem; wo->s.val[2][i] = power;
+    wo->s.node[i] = b.doc_node[d];
+  };
   uint8_t *Sb = reinterpret_cast<uint8_t *>(S);
   const uint32_t half = 0;                           // (stage clocks: see STAGE_MARK in kgm_fused.cuh)
   long long stage_t = 0;
@@ -117,6 +132,15 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
       if (rok) {
         store_grec(S, sl.tg, sl.grec + GREC_BYTES * l, g, l);   // unique keys: the row index is the short id (gpu.py:119-120)
         my_hash = g.hash;
+      }
+      if (SAMPLES && rok) {                          // the node line's sample; the row's power for its process lines
+        uint32_t power = NONE32;
+        rok = g.util.len <= 9u && gpu_row_power(TG, gstart[l], gstart[l + 1] - 1u, &power);
+        if (rok) {
+          grec[GREC_WORDS * l + GREC_LINE_LEN] = power;
+          put_sample(l, win_make_key(0u, n, l, window), g.util.len ? run_u32(TG, g.util.off, g.util.len) : NONE32,
+                     g.used > (uint64_t)WIN_SAT ? WIN_SAT : (uint32_t)g.used, power);
+        }
       }
     }
     bool dup = false;                                // equal keys: last row wins (gpu.py:54) -> generic path
@@ -188,6 +212,7 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
     }
     if (valid) {
       if (sid != NONE32) store_prec(S, sl.ta, sl.prec + PREC_BYTES * r, p, grec + GREC_WORDS * sid);
+      if (SAMPLES) sidv[r] = (uint8_t)sid;
       cp[r] = (screened ? 0x80000000u : 0u) | ((emit_c == NONE32 ? CP_NONE : emit_c) << 16) | pos;
       digest[r] = dg;
     }
@@ -248,6 +273,8 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
       }
       const uint32_t ir = np + (cw & 0x7fffu) + v, idx = ng + cstart[c] + v;
       store_idle_rec(S, 0u, sl.prec + PREC_BYTES * ir, sid);
+      if (SAMPLES)                                   // gpu.py:234-250: gpu_util=0, used_memory=0
+        put_sample(idx, win_make_key(1u, gc, sid == NONE32 ? 0xffffu : sid, window), 0u, 0u, NONE32);
       plan[idx] = (uint16_t)((KIND_IDLE << 14) | ir);
       toff[idx] = f.tslot_off[gc];
       loff[idx] = f.cont_fixed[gc] + 1u + line_var_bytes<true>(prec + PREC_WORDS * ir);
@@ -257,6 +284,13 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
     const uint32_t c = (cp[r] >> 16) & 0x7fffu;
     if (c == CP_NONE) continue;
     const uint32_t gc = cb + c, idx = ng + cstart[c] + (cp[r] & 0xffffu);
+    if (SAMPLES) {
+      const uint32_t sid = sidv[r], *gr = grec + GREC_WORDS * sid, mw = prec[PREC_WORDS * r + PREC_MEM];
+      const uint32_t uw = gr[GREC_UTIL];
+      too_long |= rw_len(mw) > 9u;                   // (declines: the staged front end's saturation rules decide)
+      put_sample(idx, win_make_key(1u, gc, sid, window), rw_len(uw) ? run_u32(S, rw_off(uw), rw_len(uw)) : NONE32,
+                 rw_len(mw) && rw_len(mw) <= 9u ? run_u32(S, rw_off(mw), rw_len(mw)) : NONE32, gr[GREC_LINE_LEN]);
+    }
     plan[idx] = (uint16_t)((KIND_BUSY << 14) | r);
     toff[idx] = f.tslot_off[gc];
     loff[idx] = f.cont_fixed[gc] + 1u + line_var_bytes<true>(prec + PREC_WORDS * r);
@@ -275,6 +309,10 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
   if (__any_sync(FULL, too_long)) return false;
   if (l == 0) loff[nl] = nb;
   __syncwarp();
+  if (SAMPLES) {                                     // the planning half ends here: unused places are invalid
+    for (uint32_t i = nl + l; i < wo->stride; i += 32) wo->s.key[sbase + i] = WIN_KEY_INVALID;
+    return true;
+  }
 
   STAGE_MARK(4);                                     // containers, lines, lengths
   // ---- from here on the document is this warp's: publish its size, write its lines ----
@@ -437,14 +475,53 @@ k_poll2(const __grid_constant__ BatchDev b, const __grid_constant__ FleetDev f, 
       if (t >= b.n_docs) break;
     }
     const uint32_t d = (uint32_t)t;
-    if (P.allow_fast && p2_fast_doc(d, b, f, w, P, Q, S, s0, sl)) continue;
+    if (P.allow_fast && p2_fast_doc<false>(d, b, f, w, P, Q, S, s0, sl, nullptr)) continue;
     cp_async_wait_all();
     __syncwarp();
     p2_slow_doc(d, b, f, w, P, S + (sl.stage >> 2));
   }
 }
 
+// Stage 3's front end: the planning half of k_poll2 over every document, samples instead of bytes
+// (documents by a fixed stride, no ticket and no look-back: nothing is ordered here).  A document
+// the fast path declines is counted; the host then lets the staged front end take the batch.
+__global__ void __launch_bounds__(P2_MAX_THREADS, 1)
+k_poll2_samples(const __grid_constant__ BatchDev b, const __grid_constant__ FleetDev f, const __grid_constant__ WorkDev w,
+                const __grid_constant__ FusedParams P, const __grid_constant__ Poll2Params Q,
+                const __grid_constant__ WinFront wo) {
+  extern __shared__ __align__(16) uint32_t S[];
+  for (uint32_t i = threadIdx.x; i < ((CA2::BYTES + 15u) & ~15u) / 16; i += blockDim.x)
+    reinterpret_cast<uint4 *>(S)[i] = __ldg(f.ca2 + i);
+  __syncthreads();
+  const uint32_t warp = threadIdx.x >> 5, l = lane_id();
+  const uint32_t base = ((CA2::BYTES + 15u) & ~15u) + warp * Q.slice_bytes;
+  P2Slice sl;
+  sl.tg = base + Q.off_tg; sl.ta = base + Q.off_ta; sl.grec = base + Q.off_grec; sl.prec = base + Q.off_prec;
+  sl.cnt = base + Q.off_cnt; sl.cstart = base + Q.off_cstart; sl.plan = base + Q.off_plan; sl.loff = base + Q.off_loff;
+  sl.toff = base + Q.off_toff; sl.stage = base + Q.off_stage;
+  sl.gstart = base + Q.off_gstart; sl.pstart = base + Q.off_pstart; sl.cp = base + Q.off_cp; sl.digest = base + Q.off_digest;
+  const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(S);
+  for (uint32_t d = blockIdx.x * Q.warps + warp; d < b.n_docs; d += gridDim.x * Q.warps) {
+    if (p2_fast_doc<true>(d, b, f, w, P, Q, S, s0, sl, &wo)) continue;
+    cp_async_wait_all();
+    __syncwarp();
+    for (uint32_t i = l; i < wo.stride; i += 32) wo.s.key[(uint64_t)d * wo.stride + i] = WIN_KEY_INVALID;
+    if (l == 0) atomicAdd(wo.declined, 1u);
+  }
+}
+
 }  // namespace
+
+void launch_poll2_samples(const BatchDev &b, const FleetDev &f, const WorkDev &w, const FusedParams &P,
+                          const Poll2Params &Q, const WinFront &wo, int blocks, int device, cudaStream_t s) {
+  static int attr_bytes[64];                         // the opt-in is per device
+  const int need = poll2_smem_bytes(Q);
+  if (device < 0 || device >= 64 || need > attr_bytes[device]) {
+    cudaFuncSetAttribute(k_poll2_samples, cudaFuncAttributeMaxDynamicSharedMemorySize, need);
+    if (device >= 0 && device < 64) attr_bytes[device] = need;
+  }
+  k_poll2_samples<<<blocks, 32 * Q.warps, need, s>>>(b, f, w, P, Q, wo);
+}
 
 int poll2_max_warps() { return KGM_P2_MAX_WARPS; }
 int poll2_smem_bytes(const Poll2Params &Q) { return (int)(((CA2::BYTES + 15u) & ~15u) + Q.warps * Q.slice_bytes); }

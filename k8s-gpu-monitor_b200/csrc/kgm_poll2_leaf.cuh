@@ -614,6 +614,38 @@ KGM_HD bool parse_gpu_row2(const uint32_t *W, uint32_t s, uint32_t e, G2 &g) {
   return g.total != 0;                                            // ZeroDivisionError gpu.py:135
 }
 
+// ---- stage 3 values (window reductions; no counterpart in the reference) -----------------------
+// The integers behind a line's fields, with the staged front end's rules (kgm_window.cu
+// k_win_samples over kgm_common.cuh GpuRowScan / ProcRowScan): digits stripped, saturating.
+// int(digits) of a run of at most 9 digits at byte offset `off` of W
+KGM_HD uint32_t run_u32(const uint32_t *W, uint32_t off, uint32_t len) {
+  uint32_t v = 0;
+  for (uint32_t i = 0; i < len; ++i) v = v * 10u + (load1(W, off + i) - 48u);
+  return v;
+}
+// The 7th cell of a --query-gpu row (power.draw of an extended query; zip() drops it, gpu.py:49):
+// 0xffffffff = no such cell, no digit in it, or a value of 2^32 - 1 and more (the staged front
+// end's 32-bit saturation value is its "no value" too), else int(its digits).  False: more than 10
+// digits (the staged front end's significant-digit rule decides those).
+KGM_HD bool gpu_row_power(const uint32_t *W, uint32_t s, uint32_t e, uint32_t *out) {
+  *out = NONE32;
+  RowShape sh;
+  scan_commas<6>(W, s, e, sh);
+  if (sh.irregular || sh.ncommas < 6) return !sh.irregular;
+  uint64_t val = 0;
+  uint32_t ndig = 0;
+  for (uint32_t p = sh.comma[5] + 1u; p < e; ++p) {
+    const uint32_t c = load1(W, p);
+    if (c == 44u) break;
+    if (c - 48u <= 9u) {
+      if (++ndig > 10u) return false;
+      val = val * 10u + (c - 48u);
+    }
+  }
+  if (ndig && val < 0xffffffffull) *out = (uint32_t)val;
+  return true;
+}
+
 struct P2 {                                         // one --query-compute-apps row (gpu.py:111-116)
   uint64_t pidkey;                                  // pid cell bytes (<= 7) | len << 56; ~0 if longer
   Run pid, name[NAME_RUNS], mem, key;

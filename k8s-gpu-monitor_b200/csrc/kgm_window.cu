@@ -26,13 +26,11 @@ namespace kgm {
 namespace {
 
 constexpr uint32_t FULLMASK = 0xffffffffu;
-constexpr uint64_t KEY_INVALID = ~0ull;
+constexpr uint64_t KEY_INVALID = WIN_KEY_INVALID;
 constexpr int WIN_THREADS = 256;
-constexpr uint32_t WIN_SAT = 0xfffffffeu;            // values saturate here; 0xffffffff = "no value"
 
 __device__ __forceinline__ uint64_t make_key(uint32_t kind, uint32_t entity, uint32_t sid, uint32_t window) {
-  return ((uint64_t)kind << 63) | ((uint64_t)(entity & 0x7fffffffu) << 32) | ((uint64_t)(sid & 0xffffu) << 16) |
-         (window & 0xffffu);
+  return win_make_key(kind, entity, sid, window);
 }
 
 // One planned line -> one sample.  Lines past a document's raise point are planned but not
@@ -83,10 +81,9 @@ __global__ void k_win_samples(BatchDev b, WorkDev w, uint32_t n_desc, uint32_t w
     }
   }
   {
-    // "last" = greatest (tick, document, position in the document): 20 | 26 | 18 bits
     const uint32_t tick = d < b.n_docs ? b.doc_tick[d] : 0u;
-    const uint32_t pos = d < b.n_docs ? min(i - w.doc_desc0[d], 0x3ffffu) : 0u;
-    s.order[i] = ((uint64_t)tick << 44) | ((uint64_t)(d & 0x3ffffffu) << 18) | pos;
+    const uint32_t pos = d < b.n_docs ? i - w.doc_desc0[d] : 0u;
+    s.order[i] = win_order(tick, d, pos);
   }
   s.val[0][i] = util; s.val[1][i] = mem; s.val[2][i] = power;
   s.node[i] = node;
@@ -102,6 +99,24 @@ __global__ void k_win_init(WinGroups g, uint32_t n) {
   for (int m = 0; m < 3; ++m) {
     g.m_count[m][i] = 0; g.m_min[m][i] = 0xffffffffu; g.m_max[m][i] = 0; g.m_sum[m][i] = 0;
     g.m_order[m][i] = 0; g.m_last[m][i] = 0;
+  }
+}
+
+// scal[] (see k_win_samples) of samples that another kernel wrote (k_poll2_samples)
+__global__ void k_win_scal(const uint64_t *key, uint32_t n, uint32_t *scal) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t k = key[i];
+  const bool ok = k != KEY_INVALID;
+  const uint32_t sid = (uint32_t)(k >> 16) & 0xffffu, win = (uint32_t)k & 0xffffu;
+  const uint32_t am = __activemask();
+  const uint32_t mx_sid = __reduce_max_sync(am, ok && sid != 0xffffu ? sid : 0u);
+  const uint32_t mn_win = __reduce_min_sync(am, ok ? win : 0xffffffffu);
+  const uint32_t mx_win = __reduce_max_sync(am, ok ? win : 0u);
+  if ((threadIdx.x & 31u) == (uint32_t)__ffs(am) - 1u) {
+    atomicMax(scal + 0, mx_sid);
+    atomicMin(scal + 1, mn_win);
+    atomicMax(scal + 2, mx_win);
   }
 }
 
@@ -246,6 +261,12 @@ __global__ void k_win_final(WinGroups g, uint32_t n) {
 }
 
 }  // namespace
+
+cudaError_t launch_window_scal(const WinSamples &s, uint32_t n, uint32_t *scal, cudaStream_t st) {
+  if (!n) return cudaSuccess;
+  k_win_scal<<<(n + WIN_THREADS - 1) / WIN_THREADS, WIN_THREADS, 0, st>>>(s.key, n, scal);
+  return cudaGetLastError();
+}
 
 uint32_t window_scan_tiles(uint64_t n) { return (uint32_t)((n + SCAN_TILE - 1) / SCAN_TILE); }
 

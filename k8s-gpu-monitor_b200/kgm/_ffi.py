@@ -129,6 +129,7 @@ SIGNATURES = {
     "kgm_concat_shards": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64,
                                     C.c_void_p, C.c_void_p]),
     "kgm_window_reduce": (C.c_int, [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]),
+    "kgm_window_front": (C.c_int, [C.c_void_p]),
     "kgm_replay_offsets": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p]),
     "kgm_replay_fill": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -273,6 +273,10 @@ class Monitor:
         _check(self._lib.kgm_get_timing(self._ctx, C.byref(t)), "kgm_get_timing", self._ctx, self._lib)
         return {k: getattr(t, k) for k, _ in _ffi.KgmTiming._fields_}
 
+    def window_front(self) -> str:
+        """The front end the last window_reduce took its samples from."""
+        return {1: "k_poll2_samples", 0: "k_tokenize, k_join"}[self._lib.kgm_window_front(self._ctx)]
+
     def last_kernel(self) -> str:
         """The kernel(s) the last run went through."""
         k = self._lib.kgm_last_kernel(self._ctx)

@@ -61,8 +61,19 @@ def test_windows_of_a_clean_fleet_match_the_oracle(mon, window_ticks, power):
     res = mon.encode(rp.gpu_texts, rp.apps_texts, rp.doc_node, rp.doc_tick)
     assert not res.status.any()
     got = mon.window_reduce(window_ticks)
+    assert mon.window_front() == "k_poll2_samples"   # a clean fleet: the planning half of k_poll2 feeds stage 3
     want = _oracle_groups(rp, entries, rp.gpu_texts, rp.apps_texts, rp.doc_node, rp.doc_tick, window_ticks)
     _compare(got, want)
+    # the staged front end (tokenizer + join) gives the same groups
+    import os
+    os.environ["KGM_WINDOW_STAGED_FRONT"] = "1"
+    try:
+        staged = mon.window_reduce(window_ticks)
+        assert mon.window_front() == "k_tokenize, k_join"
+    finally:
+        del os.environ["KGM_WINDOW_STAGED_FRONT"]
+    _compare(staged, want)
+    got = mon.window_reduce(window_ticks)
     # ... and in line form (node_gpu_w / pod_gpu_w with nanosecond timestamps)
     from kgm import sink
     hosts = [s.name for s in rp.nodes]
@@ -108,6 +119,33 @@ def test_windows_with_damaged_shuffled_and_repeated_documents(mon):
     assert res.status.any() and not res.status.all()
     for w in (4, 2):
         _compare(mon.window_reduce(w), _oracle_groups(rp, entries, gt, at, dn, dt, w))
+
+
+def test_fused_front_end_with_missing_values_and_dying_documents(mon):
+    """Documents the planning half of k_poll2 takes although they are not clean: utilisation or power
+    without digits, and the KeyError of an unknown process uuid (node lines only)."""
+    rp = replay.make_replay(seed=44, nodes=6, ticks=9, gpus=8, containers=6, procs_per_container=3, idle_every=4,
+                            power=True)
+    entries = [entry_of_snap(s) for s in rp.nodes]
+    rng = random.Random(9)
+    gt, at = [], []
+    for d in range(rp.n_docs):
+        g, a = rp.gpu_texts[d], rp.apps_texts[d]
+        k = rng.randrange(5)
+        if k == 0:
+            g = g.replace(" %,", " [N/A],", 1)
+        elif k == 1:
+            g = g.replace(" W\n", " [N/A]\n", 1)
+        elif k == 2:
+            a = a + "77, x, GPU-unknown, 1 MiB\n"
+        gt.append(g); at.append(a)
+    mon.load_fleet(entries)
+    res = mon.encode(gt, at, rp.doc_node, rp.doc_tick)
+    assert res.status.any() and not res.status.all()
+    for w in (3, 9):
+        got = mon.window_reduce(w)
+        assert mon.window_front() == "k_poll2_samples"
+        _compare(got, _oracle_groups(rp, entries, gt, at, rp.doc_node, rp.doc_tick, w))
 
 
 def test_window_reduce_needs_ticks_and_a_batch(mon):

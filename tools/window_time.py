@@ -1,19 +1,23 @@
-"""Stage 3 (kgm_window_reduce) on BASELINE configs[1]: wall clock of the call with the batch
-resident, window = 10 ticks."""
+"""Wall clock of kgm_window_reduce on the resident configs[1] batch (development aid)."""
 import os, sys, time
-sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "k8s-gpu-monitor_b200"))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "k8s-gpu-monitor_b200"), os.path.join(ROOT, "tests")]
+import torch
 from kgm import monitor, replay
-from kgm.fleet import node_entry
-rp = replay.make_replay(seed=1, **replay.CONFIGS["config2"])
-entries = [node_entry(s.name, s.ps_text, s.stats_text, s.top, s.inspect, s.smi_list) for s in rp.nodes]
+from fleet_util import entry_of_snap
+rp = replay.make_replay(seed=0, **replay.CONFIGS["config2"])
 with monitor.Monitor(0) as mon:
-    mon.load_fleet(entries)
-    mon.upload(mon.make_batch(rp.gpu_texts, rp.apps_texts, rp.doc_node, rp.doc_tick))
+    mon.load_fleet([entry_of_snap(s) for s in rp.nodes])
+    batch = mon.make_batch(rp.gpu_texts, rp.apps_texts, rp.doc_node, rp.doc_tick, pinned=True)
+    mon.upload(batch)
+    mon.encode_resident()
     for w in (10, 60):
-        ts = []
-        for _ in range(8):
-            t0 = time.perf_counter()
-            out = mon.window_reduce(w)
-            ts.append(1e3 * (time.perf_counter() - t0))
-        print("window %2d ticks: %d groups, %.3f ms per call (min %.3f), %d samples" % (
-            w, out["n"], sum(ts[2:]) / 6, min(ts), int(out["count"].sum())))
+        for _ in range(3):
+            mon.window_reduce(w)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(20):
+            r = mon.window_reduce(w)
+        torch.cuda.synchronize()
+        print("window_ticks %d: %d groups, %.3f ms per call, front end %s" % (w, r["n"], (time.perf_counter() - t0) * 50,
+                                                                        mon.window_front()), flush=True)
