@@ -306,6 +306,29 @@ ROTATE = 4          # resident batches per rank, visited round-robin: 4 x 60 MB 
                     # (config3: one batch of 750 MB is larger than L2 by itself)
 
 
+def bind_near_gpu(torch, local_rank):
+    """Several ranks on one box: run on the cores of the GPU's own NUMA node, so that the pinned host buffers
+    of the end-to-end leg are allocated in the memory its PCIe link reaches without crossing sockets.
+    Returns what was done (for the bench line); does nothing when the box does not say."""
+    try:
+        p = torch.cuda.get_device_properties(local_rank)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bdf).read())
+        if node < 0:
+            return {"gpu": bdf, "numa_node": node, "bound": False}
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return {"gpu": bdf, "numa_node": node, "bound": False}
+        os.sched_setaffinity(0, cpus)
+        return {"gpu": bdf, "numa_node": node, "bound": True, "cpus": len(cpus)}
+    except Exception as e:                           # no sysfs, no such attribute: leave the process where it is
+        return {"bound": False, "why": type(e).__name__}
+
+
 def run_kgm_arm(args):
     import torch
     import torch.distributed as dist
@@ -318,6 +341,7 @@ def run_kgm_arm(args):
     json_fd = os.dup(1)
     os.dup2(2, 1)
     torch.cuda.set_device(local_rank)
+    numa = bind_near_gpu(torch, local_rank) if world > 1 and os.environ.get("KGM_BENCH_NUMA", "1") == "1" else None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     device = torch.device("cuda", local_rank)
@@ -720,6 +744,7 @@ def run_kgm_arm(args):
                             "bounded below by the D2H copy of the result over PCIe (d2h_copy_alone_ms)"},
             "gpu_launches": launches_per_step * args.steps,
             "stream": stream_info,
+            "numa": numa,
             "clocks": clocks.summary(),
         }
         if world > 1:
