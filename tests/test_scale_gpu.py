@@ -64,6 +64,9 @@ def test_config3_shape_one_streamed_batch_at_full_width(mon):
     if mon.pipeline_name == "fused":
         t = mon.timing()
         assert t["fused"] == 1 and t["slow_docs"] == 0
+        assert mon.last_kernel() == "k_poll2"        # 40 000 documents: AUTO takes the warp kernel
+    assert mon.last_kernel() == {"fused": "k_poll2", "fused-v1": "k_poll", "fused-v2": "k_poll2",
+                                 "staged": "k_tokenize, k_join, k_scan, k_encode"}[mon.pipeline_name]
 
 
 def test_config5_shape_skewed_short_lived_pods_and_mig(mon):
@@ -86,6 +89,7 @@ def test_config5_shape_skewed_short_lived_pods_and_mig(mon):
         t = mon.timing()
         # the dying documents go generic, and the few whose texts exceed a warp's slice
         assert t["fused"] == 1 and died <= t["slow_docs"] < rp.n_docs // 3
+        assert mon.last_kernel() == "k_poll"         # 480 documents, less than one wave of k_poll2: the team kernel
     if mon.pipeline_name == "fused-v2":
         # k_poll2 answers the KeyError of gpu.py:151 itself (node lines, then the status): only the
         # documents whose texts exceed a warp's slice go generic
