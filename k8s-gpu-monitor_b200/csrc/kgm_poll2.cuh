@@ -170,7 +170,7 @@ __device__ bool p2_fast_doc(uint32_t d, const BatchDev &b, const FleetDev &f, co
     uint32_t nm = 0, c_first = NONE32, sid = NONE32, emit_c = NONE32, dg = 0;
     if (valid) {
       ok = parse_proc_row2(TA, pstart[r], pstart[r + 1] - 1u, p);
-      if (ok && p.pidkey != ~0ull) pid_probe(f, n, p.pidkey, &nm, &c_first);
+      if (ok && p.pidkey != ~0ull) pid_probe2(f, n, p.pidkey, &nm, &c_first);
     }
     // first gpu row with this key hash (the hashes come from the lanes that parsed the gpu rows);
     // length and bytes are compared once, afterwards

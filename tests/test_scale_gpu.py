@@ -64,7 +64,9 @@ def test_config3_shape_one_streamed_batch_at_full_width(mon):
     if mon.pipeline_name == "fused":
         t = mon.timing()
         assert t["fused"] == 1 and t["slow_docs"] == 0
-        assert mon.last_kernel() == "k_poll2"        # 40 000 documents: AUTO takes the warp kernel
+    # one launch over the resident batch (the end-to-end call above cut it into chunks, the small ones
+    # of which AUTO gives to the team kernel): 40 000 documents -> the warp kernel
+    mon.encode_resident()
     assert mon.last_kernel() == {"fused": "k_poll2", "fused-v1": "k_poll", "fused-v2": "k_poll2",
                                  "staged": "k_tokenize, k_join, k_scan, k_encode"}[mon.pipeline_name]
 
@@ -89,6 +91,7 @@ def test_config5_shape_skewed_short_lived_pods_and_mig(mon):
         t = mon.timing()
         # the dying documents go generic, and the few whose texts exceed a warp's slice
         assert t["fused"] == 1 and died <= t["slow_docs"] < rp.n_docs // 3
+        mon.encode_resident()
         assert mon.last_kernel() == "k_poll"         # 480 documents, less than one wave of k_poll2: the team kernel
     if mon.pipeline_name == "fused-v2":
         # k_poll2 answers the KeyError of gpu.py:151 itself (node lines, then the status): only the
