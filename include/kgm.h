@@ -288,6 +288,22 @@ void  kgm_host_free(void *p);
 int  kgm_concat_shards(const uint8_t *slots, uint64_t stride, const int64_t *counts, uint32_t world,
                        uint8_t *out, uint64_t out_cap, uint64_t *totals_out, void *stream);
 
+/* Docker-side text on the device: what the reference reads from
+ * `docker inspect <container>` on every poll -- json.loads(text.replace("\n","").replace(" ",""))
+ * [0]['Config']['Labels'], the gate labels['mlgpu'] == 'mlgpu', io.kubernetes.pod.name / .namespace
+ * and the user_name split rules (gpu.py:86-88,184-199) -- for n containers at once, one thread per
+ * container.  `texts` holds the n texts back to back, off[n + 1] their byte offsets (host memory).
+ * The scanner takes a subset of what json.loads accepts (csrc/kgm_docker.cuh says which) and is exact
+ * on it; for every other container status[i] = 1 and the caller parses that text itself
+ * (kgm/fleet.py does, with json.loads: that is where the reference's raise points are classified).
+ * For status[i] = 0: gated[i]; has_pod[i]; pod / ns / user = runs of container i's text (user only
+ * for a gated container with a pod name).  Synchronous; allocates and frees its own device memory. */
+typedef struct {
+  uint8_t  *status, *gated, *has_pod;                 /* [n] each                                    */
+  uint32_t *pod_off, *pod_len, *ns_off, *ns_len, *user_off, *user_len;   /* [n] each, relative to the container's text */
+} kgm_inspect_out;
+int  kgm_inspect_labels(int device, const uint8_t *texts, const uint64_t *off, uint32_t n, const kgm_inspect_out *out);
+
 /* Replay generator on the device (bench / test plumbing; no counterpart in the reference, which
  * reads live `nvidia-smi` output, gpu.py:104-116): writes the two nvidia-smi texts of n_nodes x
  * n_ticks polls (host-major: all ticks of host 0, then host 1, ...) straight into device memory,

@@ -89,6 +89,12 @@ class KgmReplaySpec(C.Structure):
                 ("names", C.c_void_p), ("name_off", C.c_void_p)]
 
 
+class KgmInspectOut(C.Structure):
+    _fields_ = [("status", C.c_void_p), ("gated", C.c_void_p), ("has_pod", C.c_void_p), ("pod_off", C.c_void_p),
+                ("pod_len", C.c_void_p), ("ns_off", C.c_void_p), ("ns_len", C.c_void_p), ("user_off", C.c_void_p),
+                ("user_len", C.c_void_p)]
+
+
 class KgmTiming(C.Structure):
     _fields_ = [
         ("h2d_ms", C.c_float), ("tokenize_ms", C.c_float), ("join_ms", C.c_float),
@@ -130,6 +136,7 @@ SIGNATURES = {
                                     C.c_void_p, C.c_void_p]),
     "kgm_window_reduce": (C.c_int, [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]),
     "kgm_window_front": (C.c_int, [C.c_void_p]),
+    "kgm_inspect_labels": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     "kgm_replay_offsets": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p]),
     "kgm_replay_fill": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,

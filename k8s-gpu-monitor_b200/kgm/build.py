@@ -21,10 +21,10 @@ HOSTCHECK = os.path.join(ROOT, "tests", "native", "_hostcheck.so")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
-SOURCES = ["kgm_kernels.cu", "kgm_api.cu", "kgm_window.cu", "kgm_replay.cu"]
+SOURCES = ["kgm_kernels.cu", "kgm_api.cu", "kgm_window.cu", "kgm_replay.cu", "kgm_docker.cu"]
 HEADERS = ["kgm_common.cuh", "kgm_d2s.cuh", "kgm_d2s_tables.h", "kgm_device.cuh", "kgm_skeleton.h",
            "kgm_poll2_leaf.cuh", "kgm_poll2.cuh",
-           "kgm_fast.cuh", "kgm_fused.cuh", "kgm_window.cuh"]
+           "kgm_fast.cuh", "kgm_fused.cuh", "kgm_window.cuh", "kgm_docker.cuh"]
 
 
 def _stale(target, deps):

@@ -61,47 +61,121 @@ def _user_name(podname):
     return podname.split("-")[1]
 
 
-def node_entry(node_name, ps_text, stats_text, top, inspect, smi_list) -> NodeEntry:
-    """Parses one node's docker texts.  ``top`` / ``inspect`` / ``smi_list`` map a
-    container id to the text the reference's subprocess would have returned."""
+def _node_frame(node_name, ps_text, stats_text):
+    """The node-level part of node_entry: (entry, container ids in `docker stats` order); the list is
+    None if the reference dies before it looks at any container."""
     node = NodeEntry(name="%s" % (node_name,))          # '%s' % None == "None"  (gpu.py:131,137)
     try:
         ps = _keyed_rows(ps_text, ["ID", "Image", "Ports"], "ID")
         stats = _keyed_rows(stats_text, ["Container", "MemUsage", "CPUPerc"], "Container")
     except Exception as exc:                            # raised before any line (gpu.py:92-103)
         node.err_parse = _ffi.doc_code_of_exception(exc)
-        return node
+        return node, None
     for cid in stats:                                   # gpu.py:172
         if cid not in ps:
             node.err_join = _ffi.DOC_KEY_ERROR
-            return node
-    for cid in stats:                                   # gpu.py:174: docker stats order
-        ent = ContainerEntry(cid=cid)
-        node.containers.append(ent)
-        try:
-            ent.pids = top[cid].split("\n")[1:-1]       # gpu.py:177
-            squeezed = inspect[cid].replace("\n", "").replace(" ", "")   # gpu.py:87
-            labels = json.loads(squeezed)[0]["Config"]["Labels"]         # gpu.py:88,184
-            gate = "False"
-            if "mlgpu" in labels.keys():                # gpu.py:186
-                gate = labels["mlgpu"]
-            ent.gated = gate == "mlgpu"                 # gpu.py:188
-        except Exception as exc:
-            ent.err_inspect = _ffi.doc_code_of_exception(exc)
-            ent.pids = []
-            continue
-        if not ent.gated:
-            continue
-        ent.visible = str(smi_list.get(cid, "")).split()   # gpu.py:224
-        try:                                            # gpu.py:193-199 == 227-233
-            if "io.kubernetes.pod.name" in labels.keys():
-                podname = labels["io.kubernetes.pod.name"]
-                namespace = labels["io.kubernetes.pod.namespace"]
-                user = _user_name(podname)
-                ent.podname, ent.namespace, ent.user = "%s" % podname, "%s" % namespace, "%s" % user
-        except Exception as exc:
-            ent.err_emit = _ffi.doc_code_of_exception(exc)
+            return node, None
+    return node, list(stats)                            # gpu.py:174: docker stats order
+
+
+def _container_entry(cid, top, inspect, smi_list) -> ContainerEntry:
+    """One container, with json.loads and str.split themselves (every raise point classified)."""
+    ent = ContainerEntry(cid=cid)
+    try:
+        ent.pids = top[cid].split("\n")[1:-1]           # gpu.py:177
+        squeezed = inspect[cid].replace("\n", "").replace(" ", "")   # gpu.py:87
+        labels = json.loads(squeezed)[0]["Config"]["Labels"]         # gpu.py:88,184
+        gate = "False"
+        if "mlgpu" in labels.keys():                    # gpu.py:186
+            gate = labels["mlgpu"]
+        ent.gated = gate == "mlgpu"                     # gpu.py:188
+    except Exception as exc:
+        ent.err_inspect = _ffi.doc_code_of_exception(exc)
+        ent.pids = []
+        return ent
+    if not ent.gated:
+        return ent
+    ent.visible = str(smi_list.get(cid, "")).split()    # gpu.py:224
+    try:                                                # gpu.py:193-199 == 227-233
+        if "io.kubernetes.pod.name" in labels.keys():
+            podname = labels["io.kubernetes.pod.name"]
+            namespace = labels["io.kubernetes.pod.namespace"]
+            user = _user_name(podname)
+            ent.podname, ent.namespace, ent.user = "%s" % podname, "%s" % namespace, "%s" % user
+    except Exception as exc:
+        ent.err_emit = _ffi.doc_code_of_exception(exc)
+    return ent
+
+
+def node_entry(node_name, ps_text, stats_text, top, inspect, smi_list) -> NodeEntry:
+    """Parses one node's docker texts.  ``top`` / ``inspect`` / ``smi_list`` map a
+    container id to the text the reference's subprocess would have returned."""
+    node, cids = _node_frame(node_name, ps_text, stats_text)
+    if cids is not None:
+        node.containers = [_container_entry(cid, top, inspect, smi_list) for cid in cids]
     return node
+
+
+def node_entries_device(nodes, device=0):
+    """``node_entry`` for many nodes at once, the `docker inspect` texts scanned on the GPU
+    (kgm_inspect_labels: one thread per container; csrc/kgm_docker.cuh).  ``nodes`` = iterable of
+    (node_name, ps_text, stats_text, top, inspect, smi_list).  The scanner takes the texts it is exact
+    on; every other container goes through ``_container_entry`` as before.  Returns (entries, number
+    of containers the device took, number left to the host)."""
+    import ctypes as C
+    lib = _ffi.load()
+    frames, jobs, blobs = [], [], []
+    for node_name, ps_text, stats_text, top, inspect, smi_list in nodes:
+        node, cids = _node_frame(node_name, ps_text, stats_text)
+        frames.append((node, cids, top, inspect, smi_list))
+        for k, cid in enumerate(cids or []):
+            text = inspect.get(cid) if isinstance(inspect, dict) else None
+            if isinstance(text, str) and isinstance(top.get(cid) if isinstance(top, dict) else None, str):
+                try:
+                    raw = text.encode("ascii")           # (anything else is the host's: the scanner takes ASCII only)
+                except UnicodeEncodeError:
+                    continue
+                jobs.append((len(frames) - 1, k))
+                blobs.append(raw)
+    n = len(jobs)
+    fields = None
+    if n:
+        off = np.zeros(n + 1, np.uint64)
+        np.cumsum([len(b) for b in blobs], out=off[1:])
+        texts = np.frombuffer(b"".join(blobs) + b"\0", np.uint8)
+        u8 = [np.zeros(n, np.uint8) for _ in range(3)]
+        u32 = [np.zeros(n, np.uint32) for _ in range(6)]
+        out = _ffi.KgmInspectOut(*[a.ctypes.data for a in u8 + u32])
+        rc = lib.kgm_inspect_labels(int(device), texts.ctypes.data, off.ctypes.data, n, C.byref(out))
+        if rc != _ffi.KGM_OK:
+            raise RuntimeError("kgm_inspect_labels failed: %d" % rc)
+        fields = (u8, u32)
+    taken = {}
+    for j, (fi, k) in enumerate(jobs):
+        u8, u32 = fields
+        if u8[0][j]:
+            continue
+        raw = blobs[j]
+        cut = lambda o, ln: raw[int(o):int(o) + int(ln)].decode("ascii")
+        taken[(fi, k)] = (bool(u8[1][j]), bool(u8[2][j]), cut(u32[0][j], u32[1][j]), cut(u32[2][j], u32[3][j]),
+                          cut(u32[4][j], u32[5][j]))
+    entries = []
+    for fi, (node, cids, top, inspect, smi_list) in enumerate(frames):
+        for k, cid in enumerate(cids or []):
+            got = taken.get((fi, k))
+            if got is None:
+                node.containers.append(_container_entry(cid, top, inspect, smi_list))
+                continue
+            gated, has_pod, pod, ns, user = got
+            ent = ContainerEntry(cid=cid, gated=gated)
+            ent.pids = top[cid].split("\n")[1:-1]       # gpu.py:177
+            if gated:
+                ent.visible = str(smi_list.get(cid, "")).split()   # gpu.py:224
+                if has_pod:
+                    ent.podname, ent.namespace, ent.user = pod, ns, user
+            node.containers.append(ent)
+        entries.append(node)
+    return entries, len(taken), sum(len(c or []) for _, c, _, _, _ in frames) - len(taken)
 
 
 class _Strings:

@@ -198,3 +198,17 @@ def p2_gpu_row(row: bytes, shift=0):
 
 def key_hash_bytes(b: bytes) -> int:
     return lib().hc_key_hash_bytes(b, len(b))
+
+
+def inspect_fields(text: bytes):
+    """kgm_docker.cuh inspect_fields: None if the scanner leaves the container to the host, else
+    (gated, podname or None, namespace or None, user or None) -- user only for a gated container."""
+    out = (C.c_uint32 * 9)()
+    buf = (C.c_ubyte * max(len(text), 1)).from_buffer_copy(text or b"\0")
+    lib().hc_inspect_fields(buf, C.c_uint32(len(text)), out)
+    if out[0]:
+        return None
+    cut = lambda o, n: text[o:o + n].decode()
+    gated, has_pod = bool(out[1]), bool(out[2])
+    return (gated, cut(out[3], out[4]) if has_pod else None, cut(out[5], out[6]) if has_pod else None,
+            cut(out[7], out[8]) if gated and has_pod else None)

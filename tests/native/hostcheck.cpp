@@ -8,6 +8,7 @@
 
 #include "../../k8s-gpu-monitor_b200/csrc/kgm_common.cuh"
 #include "../../k8s-gpu-monitor_b200/csrc/kgm_skeleton.h"
+#include "../../k8s-gpu-monitor_b200/csrc/kgm_docker.cuh"
 
 using namespace kgm;
 
@@ -365,6 +366,13 @@ int hc_p2_gpu_row(const uint8_t *row, uint32_t row_len, uint32_t shift, uint32_t
   for (int i = 0; i < 5; ++i) { out[2 * i] = runs[i].off - shift; out[2 * i + 1] = runs[i].len; }
   u64out[0] = g.hash; u64out[1] = g.total; u64out[2] = g.used;
   return 1;
+}
+
+// kgm_docker.cuh: one container's `docker inspect` text -> {status, gated, has_pod, pod off/len, ns off/len, user off/len}
+void hc_inspect_fields(const uint8_t *t, uint32_t n, uint32_t *out) {
+  const dk::Fields f = dk::inspect_fields(t, n);
+  out[0] = f.status; out[1] = f.gated; out[2] = f.has_pod; out[3] = f.pod_off; out[4] = f.pod_len;
+  out[5] = f.ns_off; out[6] = f.ns_len; out[7] = f.user_off; out[8] = f.user_len;
 }
 
 uint64_t hc_key_hash_bytes(const uint8_t *p, uint32_t n) { return fast::key_hash_bytes(p, n); }
