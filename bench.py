@@ -394,7 +394,8 @@ def run_kgm_arm(args):
     n_bytes, n_lines = sizes[0]
     gather = (shard.ShardGather(max(s[0] for s in sizes) + (1 << 20), device,
                                  push=os.environ.get("KGM_SHARD_PUSH", "1") == "1",
-                                 rotate_root=os.environ.get("KGM_GATHER_ROTATE", "1") == "1") if world > 1 else None)
+                                 rotate_root=os.environ.get("KGM_GATHER_ROTATE", "1") == "1", contexts=rotate)
+              if world > 1 else None)
 
     def sync_all():
         torch.cuda.synchronize(device)

@@ -345,7 +345,9 @@ int  kgm_replay_fill(const kgm_replay_spec *spec, uint32_t tick0, uint32_t n_tic
  *                            with release: signals from different streams may arrive out of order)
  *   kgm_stream_wait_flags    holds `stream` until each of the n <= 32 consecutive counters at `flags`
  *                            has reached `value` (wrap-safe comparison; a one-warp kernel that polls)
- * All pointers are device pointers valid on the current device.                              */
+ * All pointers are device pointers valid on the current device.  With KGM_FLAG_MEMOPS=1 in the
+ * environment both use stream memory operations (cuStreamWriteValue32 / cuStreamWaitValue32) instead of
+ * kernels; a signal is then a plain store, so every signalling stream needs a counter of its own.  */
 #define KGM_MAX_FLAG_TARGETS 16
 int  kgm_stream_signal_flags(void *stream, uint32_t *const *targets, uint32_t n, uint32_t value);
 int  kgm_stream_wait_flags(void *stream, const uint32_t *flags, uint32_t n, uint32_t value);

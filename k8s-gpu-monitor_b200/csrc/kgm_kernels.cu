@@ -849,8 +849,43 @@ __global__ void k_wait_flags(const uint32_t *flags, uint32_t n, uint32_t value) 
 }  // namespace
 }  // namespace kgm
 
+// KGM_FLAG_MEMOPS=1: stream memory operations (cuStreamWriteValue32 / cuStreamWaitValue32) instead of the
+// one-warp kernels: no SM is needed, so the flags do not wait for room beside the persistent poll kernel.
+// A write is a plain store, not a max: the caller then has to give every stream that signals its own
+// counter (kgm/shard.py does: one per rank and context).  Whatever the driver declines falls back to
+// the kernels.
+#include <cuda.h>
+namespace kgm {
+namespace {
+typedef CUresult (*MemOp32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+struct MemOps {
+  MemOp32 write = nullptr, wait = nullptr;
+  bool on = false;
+  MemOps() {
+    const char *env = getenv("KGM_FLAG_MEMOPS");
+    if (!env || atoi(env) == 0) return;
+    cudaDriverEntryPointQueryResult q;
+    void *w = nullptr, *v = nullptr;
+    if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &w, cudaEnableDefault, &q) != cudaSuccess || !w) return;
+    if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &v, cudaEnableDefault, &q) != cudaSuccess || !v) return;
+    write = reinterpret_cast<MemOp32>(w); wait = reinterpret_cast<MemOp32>(v);
+    on = true;
+  }
+};
+const MemOps &memops() { static MemOps m; return m; }
+}  // namespace
+}  // namespace kgm
+
 extern "C" int kgm_stream_signal_flags(void *stream, uint32_t *const *targets, uint32_t n, uint32_t value) {
   if (!targets || n == 0 || n > KGM_MAX_FLAG_TARGETS) return KGM_E_INVALID;
+  if (kgm::memops().on) {
+    bool all = true;
+    for (uint32_t i = 0; i < n && all; ++i)
+      all = targets[i] && kgm::memops().write(static_cast<CUstream>(stream), reinterpret_cast<CUdeviceptr>(targets[i]), value,
+                                               CU_STREAM_WRITE_VALUE_DEFAULT) == CUDA_SUCCESS;
+    if (all) return KGM_OK;
+    cudaGetLastError();
+  }
   kgm::FlagTargets t{};
   for (uint32_t i = 0; i < n; ++i) {
     if (!targets[i] || (reinterpret_cast<uintptr_t>(targets[i]) & 3)) return KGM_E_INVALID;
@@ -862,6 +897,14 @@ extern "C" int kgm_stream_signal_flags(void *stream, uint32_t *const *targets, u
 
 extern "C" int kgm_stream_wait_flags(void *stream, const uint32_t *flags, uint32_t n, uint32_t value) {
   if (!flags || n == 0 || n > 32 || (reinterpret_cast<uintptr_t>(flags) & 3)) return KGM_E_INVALID;
+  if (kgm::memops().on) {
+    bool all = true;
+    for (uint32_t i = 0; i < n && all; ++i)                // (int32_t)(*addr - value) >= 0, like k_wait_flags
+      all = kgm::memops().wait(static_cast<CUstream>(stream), reinterpret_cast<CUdeviceptr>(flags + i), value,
+                               CU_STREAM_WAIT_VALUE_GEQ) == CUDA_SUCCESS;
+    if (all) return KGM_OK;
+    cudaGetLastError();
+  }
   kgm::k_wait_flags<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(flags, n, value);
   return cudaGetLastError() == cudaSuccess ? KGM_OK : KGM_E_CUDA;
 }

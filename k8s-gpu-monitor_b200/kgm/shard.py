@@ -99,8 +99,11 @@ class ShardGather:
     gaps with the library's kgm_concat_shards kernel.  ``finish`` waits for every transfer."""
 
     def __init__(self, cap_bytes: int, device, group=None, host_counts=False, push=False,
-                 rotate_root=False):
+                 rotate_root=False, contexts=1):
         self.group, self.device = group, device
+        # push mode: how many library contexts the caller visits in turn (step k runs on context
+        # k mod contexts, on every rank alike); every (rank, context) gets its own "landed" counter
+        self.contexts = max(1, int(contexts))
         self.rotate_root = bool(rotate_root)
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.cap = int(cap_bytes)
@@ -126,7 +129,18 @@ class ShardGather:
             if push:
                 self._open_push()
 
-    FLAG_BYTES = 256                                 # per gathering rank: landed[world] (u32) at 0, ack (u32) at 128
+    # per gathering rank: landed[contexts][world] (u32; one counter per writing stream, so that a plain
+    # store is as good as an atomic max), then ack (u32)
+    @property
+    def FLAG_BYTES(self):
+        return (4 * (self.contexts * self.world + 1) + 255) // 256 * 256
+
+    def _ack_idx(self):
+        return self.contexts * self.world
+
+    def _landed_idx(self, k, rank):
+        return (k % self.contexts) * self.world + rank
+
 
     def _open_push(self):
         """Push mode: every gathering rank owns PUSH_SETS sets of fixed-stride slots plus a block
@@ -221,17 +235,17 @@ class ShardGather:
         root, uses = self.push_root(k), self._uses(k)
         slot = self.push_bufs[root].data_ptr() + self._push_offset(k) + self.rank * self.stride
         j = k - self.push_ahead
-        wait_flag, wait_value = (self._flag_ptr(self.push_root(j), 32), self._uses(j) + 1) if j >= 0 else (0, 0)
-        res = mon.push_step(slot, self.stride, wait_flag, wait_value, self._flag_ptr(root, self.rank), uses + 1,
+        wait_flag, wait_value = (self._flag_ptr(self.push_root(j), self._ack_idx()), self._uses(j) + 1) if j >= 0 else (0, 0)
+        res = mon.push_step(slot, self.stride, wait_flag, wait_value, self._flag_ptr(root, self._landed_idx(k, self.rank)), uses + 1,
                             copy_engine=self.copy_engine)
         self._packed = False
         self.last_root = root
         if self.rank == root:
             # this rank gathers the step: all shards landed -> acknowledge, on the gather's own stream
             st = C.c_void_p(self.stream.cuda_stream)
-            rc = self._lib.kgm_stream_wait_flags(st, C.c_void_p(self._flag_ptr(root, 0)), self.world,
+            rc = self._lib.kgm_stream_wait_flags(st, C.c_void_p(self._flag_ptr(root, self._landed_idx(k, 0))), self.world,
                                                  (uses + 1) & 0xFFFFFFFF)
-            ack = (C.c_void_p * 1)(self._flag_ptr(root, 32))
+            ack = (C.c_void_p * 1)(self._flag_ptr(root, self._ack_idx()))
             rc = rc or self._lib.kgm_stream_signal_flags(st, ack, 1, (uses + 1) & 0xFFFFFFFF)
             if rc != 0:
                 raise RuntimeError("flag kernels failed: %d" % rc)

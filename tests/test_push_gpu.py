@@ -47,7 +47,7 @@ def _worker(rank, world, port, steps, q):
             m.encode_resident()                          # sizes the workspace
             mons.append(m)
         cap = int(mons[0].encode_resident().n_bytes) + (1 << 16)
-        gather = shard.ShardGather(cap, device, push=True, rotate_root=True)
+        gather = shard.ShardGather(cap, device, push=True, rotate_root=True, contexts=NCTX)
         assert gather.mode == "push", "CUDA IPC between the ranks is needed"
         pending = [False] * NCTX
         for k in range(steps):
