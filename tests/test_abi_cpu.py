@@ -37,6 +37,8 @@ def test_version_strings_and_struct_layout_without_a_gpu():
     assert C.sizeof(_ffi.KgmBatch) == 56
     assert C.sizeof(_ffi.KgmResult) == 56
     assert C.sizeof(_ffi.KgmTiming) == 48
+    assert C.sizeof(_ffi.KgmReplaySpec) == 8 + 4 + 4 + 12 * 8
+    assert C.sizeof(_ffi.KgmInspectOut) == 9 * 8
     assert C.sizeof(_ffi.KgmFleet) == 8 + 16 + 8 * 3 + 8 + 8 * 3 + 16 * 4 + 8 + 16 + 8 + 16
 
 
