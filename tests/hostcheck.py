@@ -47,7 +47,7 @@ def scan_gpu_row(row: bytes):
     u64 = (C.c_uint64 * 4)()
     lib().hc_scan_gpu_row(row + b"\0" * 16, 0, len(row), out, u64)
     return dict(ncells=out[0], flags=out[1], key_lo=out[2], cell_end=list(out[3:9]), nd=list(out[9:13]),
-                util=out[13], parse_error=out[14], node_error=out[15],
+                util=out[13], parse_error=out[14], node_error=out[15], power=out[16],
                 key_hash=u64[0], mem_total=u64[1], mem_used=u64[2])
 
 
@@ -212,3 +212,10 @@ def inspect_fields(text: bytes):
     gated, has_pod = bool(out[1]), bool(out[2])
     return (gated, cut(out[3], out[4]) if has_pod else None, cut(out[5], out[6]) if has_pod else None,
             cut(out[7], out[8]) if gated and has_pod else None)
+
+
+def p2_gpu_power(row: bytes, shift=0):
+    """gpu_row_power of kgm_poll2_leaf.cuh: the value (0xffffffff = none), or None if it declines."""
+    out = C.c_uint32()
+    ok = lib().hc_p2_gpu_power(row, C.c_uint32(len(row)), C.c_uint32(shift), C.byref(out))
+    return out.value if ok else None

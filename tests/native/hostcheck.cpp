@@ -39,6 +39,7 @@ void hc_scan_gpu_row(const uint8_t *text, uint32_t lo, uint32_t hi, uint32_t *ou
   out[k++] = r.util;
   out[k++] = parse_error_of(r.flags, r.ncells, 1);
   out[k++] = node_error_of(r);
+  out[k++] = r.power;
   u64out[0] = r.key_hash; u64out[1] = r.mem_total; u64out[2] = r.mem_used;
 }
 
@@ -373,6 +374,13 @@ void hc_inspect_fields(const uint8_t *t, uint32_t n, uint32_t *out) {
   const dk::Fields f = dk::inspect_fields(t, n);
   out[0] = f.status; out[1] = f.gated; out[2] = f.has_pod; out[3] = f.pod_off; out[4] = f.pod_len;
   out[5] = f.ns_off; out[6] = f.ns_len; out[7] = f.user_off; out[8] = f.user_len;
+}
+
+// kgm_poll2_leaf.cuh gpu_row_power (stage 3's fused front end): 1 + the value in *out, or 0 = declined
+int hc_p2_gpu_power(const uint8_t *row, uint32_t row_len, uint32_t shift, uint32_t *out) {
+  std::vector<uint8_t> pool(64, 0);
+  P2Mem m = p2_make(row, row_len, shift, row, 0, 0, pool, 0, 16);
+  return p2::gpu_row_power(m.words.data() + m.tg / 4, shift, shift + row_len, out) ? 1 : 0;
 }
 
 uint64_t hc_key_hash_bytes(const uint8_t *p, uint32_t n) { return fast::key_hash_bytes(p, n); }

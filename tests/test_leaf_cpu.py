@@ -380,3 +380,27 @@ def test_p2_lines_are_the_generic_lines_at_every_alignment(jobs):
             assert got == want and planned == len(want) and guards
             checked += 1
     assert checked > 1200
+
+
+def test_p2_power_cell_is_the_staged_scanner_s_value():
+    """Stage 3's fused front end reads the 7th --query-gpu cell itself (gpu_row_power); whatever it
+    takes is what the staged scanner (GpuRowScan) and k_win_samples make of the same row."""
+    rng = random.Random(77)
+    WIN_SAT, NONE = 0xFFFFFFFE, 0xFFFFFFFF
+    base = "GPU-3a6c7f0e-1c2d-4e5f-8a9b-0c1d2e3f4a5b, 41 %, 17 %, 183359 MiB, 20480 MiB, 162879 MiB"
+    cells = ["", ", 415.27 W", ", [N/A]", ", 0.00 W", ", 1000 W", ", 4294967295 W", ", 4294967294 W", ", 42949672.96 W",
+             ", 99999999999 W", ", 1.2.3.4 W, extra", ", 7 W,", ",5", ", 12345678901"]
+    checked = 0
+    for _ in range(300):
+        cell = rng.choice(cells) if rng.random() < 0.7 else ", %s W" % "".join(rng.choice("0123456789.") for _ in range(rng.randrange(1, 13)))
+        row = (base + cell).encode()
+        got = hc.p2_gpu_power(row, rng.randrange(16))
+        staged = hc.scan_gpu_row(row)["power"]
+        want = min(staged, WIN_SAT) if staged != NONE else NONE      # k_win_samples
+        if got is None:
+            seventh = cell.split(",")[1] if cell else ""
+            assert sum(ch.isdigit() for ch in seventh) > 10, cell
+        else:
+            assert got == want, (cell, got, want)
+            checked += 1
+    assert checked > 200
