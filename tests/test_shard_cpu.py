@@ -150,3 +150,29 @@ def test_push_mode_slot_arithmetic():
                     # set's last use)
                     assert k - max(ahead) >= last_use[(root, base)]
                 last_use[(root, base)] = k
+
+
+def test_push_mode_counter_arithmetic():
+    """Every (rank, context) pair has its own "landed" counter on the gathering rank (so a plain
+    store is as good as an atomic max), the acknowledgement counter lies behind them, a counter's
+    values only grow, and every rank waits on the counters the writers of the same step raise."""
+    from kgm.shard import ShardGather
+    for world in (2, 3, 4, 8):
+        for contexts in (1, 2, 4, 8):
+            gs = []
+            for r in range(world):
+                g = ShardGather.__new__(ShardGather)
+                g.world, g.rank, g.rotate_root, g.contexts = world, r, True, contexts
+                gs.append(g)
+            g0 = gs[0]
+            assert 4 * (g0._ack_idx() + 1) <= g0.FLAG_BYTES and g0.FLAG_BYTES % 256 == 0
+            last = {}                                    # (root, counter index) -> last value written
+            for k in range(5 * world * contexts):
+                root, value = g0.push_root(k), g0._uses(k) + 1
+                idx = [g._landed_idx(k, g.rank) for g in gs]
+                assert len(set(idx)) == world and max(idx) < g0._ack_idx()
+                # the gathering rank waits on `world` consecutive counters: exactly the writers' ones
+                assert idx == list(range(g0._landed_idx(k, 0), g0._landed_idx(k, 0) + world))
+                for i in idx:
+                    assert last.get((root, i), 0) < value     # written by one (rank, context) stream, in its order
+                    last[(root, i)] = value
